@@ -1,0 +1,1799 @@
+// dsb_core.cuh -- the per-read classifier as warp-uniform device code (sm_100a).
+//
+// Execution model: ONE WARP PER READ.  Every function below is written so that all 32 lanes of
+// the warp execute the same instruction stream on the same values ("warp-uniform"): loads of a
+// common address are one broadcast transaction, stores of a common value to a common address
+// are benign, and control flow never diverges.  Inner loops that are worth spreading over the
+// lanes are specialised under DSB_DEVICE_CODE (ballots / shuffles) and fall back to the plain
+// loop otherwise.  Because the uniform form is ordinary C++, the same header also compiles with
+// g++ for the host-side simulator in tests/hostsim (test infrastructure: it lets parity be
+// debugged where no GPU exists; the product never links it).
+//
+// What it computes: the reference's classify_seq (reference src/cly.c:3059-3127) and everything
+// below it, with the reference's C integer semantics kept type-for-type.
+// Each function cites the reference lines it restates.  Data structures are our own:
+// index-linked fixed arenas instead of pointers/kvec, a 64-symbol FM block read with 128-bit
+// loads instead of the 168-byte block + 64 KiB popcount LUT, a direct (head,next) 9-mer table.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define DSB_HD __host__ __device__ __forceinline__
+#define DSB_HDN __host__ __device__ __noinline__
+#else
+#define DSB_HD static inline
+#define DSB_HDN static
+#endif
+#if defined(__CUDA_ARCH__)
+#define DSB_DEVICE_CODE 1
+#endif
+
+// ------------------------------------------------------------------------------------------
+// constants of the reference algorithm
+// ------------------------------------------------------------------------------------------
+#define DSB_FORWARD 1            // src/lib/utils.h:66
+#define DSB_REVERSE 0            // src/lib/utils.h:67
+#define DSB_L_PRE_IDX 13         // src/idx.h:58
+#define DSB_PRE_IDX_MASK 0x3FFFFFFu
+#define DSB_SA_MASK 0x7          // src/bwt.h:7
+#define DSB_SA_OFF 3
+#define DSB_MIN_UNI_L 35         // src/idx.h:40
+#define DSB_LV_L 12              // src/cly.c:699
+#define DSB_LV_ERROR 4           // src/cly.c:493
+#define DSB_MIN_S_1 12           // src/cly.c:691
+#define DSB_MIN_S_2 20           // src/cly.c:692
+#define DSB_STEP_EK 3            // src/cly.c:969
+#define DSB_SEED_RANGE 100       // src/cly.c (SEED_RANGE)
+#define DSB_SP_SET_MAX 500       // src/cly.c:1482-1483
+#define DSB_KMER9 9              // S_A_KEMR_L src/cly.c:1707
+#define DSB_MIN_SCORE_MEM 12     // src/cly.c:1708
+#define DSB_OVER_SEARCH 50       // OVER_SEARCH_M2 src/cly.c:2221
+#define DSB_SMS_OVERLAP 6        // src/cly.c:2437-2438
+#define DSB_PRIMARY 1
+#define DSB_SECONDARY 2
+#define DSB_SUPPLEMENTARY 3
+
+#define DSB_HEAD_PAD 64          // bytes kept before F[0] (chunk-header model)
+#define DSB_TAIL_PAD 64          // bytes kept after R[L-1] (buffer-history model)
+
+// ------------------------------------------------------------------------------------------
+// device-resident index view
+// ------------------------------------------------------------------------------------------
+// FM block: 64 BWT symbols.  cnt[c] = number of symbol c (A,C,G,T) in BWT[0, 64*blk);
+// sym[w] holds symbols 16w..16w+15, 4 bits each, symbol i at bits 4*(i&15) -- the same nibble
+// order as the reference's little-endian u16 words (src/bwt.c:52), so bytes copy over verbatim.
+struct __attribute__((aligned(64))) DsbFmBlock {
+    uint64_t cnt[4];
+    uint64_t sym[4];
+};
+
+struct DsbIndexView {
+    const DsbFmBlock *fm;
+    uint64_t n_fm_blocks;
+    uint64_t rank[6];
+    uint64_t dollar_pos;
+    const uint64_t *lut;          // 2^26+1
+    const uint64_t *sa;           // lo32 unitig_ID, hi32 offset
+    uint64_t sa_n;
+    const uint8_t *ek0, *ek1;
+    uint64_t ek_mask;
+    int32_t ek_len;               // k
+    int32_t single_base_max;
+    const uint64_t *unitig;       // lo32 ref_list, hi32 length
+    uint64_t n_unitig;
+    const uint64_t *ref_pos;      // bits 0-39 global_offset, 40-62 ref_ID, 63 direction
+    const uint8_t *ref_bin;
+    uint64_t ref_bin_n;
+    const uint64_t *ref_off;
+    const uint64_t *ref_len;
+    uint64_t n_ref;
+    const int32_t *q_mem;         // [2000]
+    const int32_t *q_lv;          // [20][20]
+    int32_t filter_min_length, filter_min_score, filter_min_score_lv3;
+};
+
+// ------------------------------------------------------------------------------------------
+// per-read working structures (our layout; field meaning follows src/cly.h)
+// ------------------------------------------------------------------------------------------
+struct DsbSeed {                  // CLY_seed src/cly.h:27-32
+    uint32_t offset;
+    uint32_t len;
+    uint32_t top;
+};
+
+struct DsbAnchor {                // Anchor + Anchor_map src/cly.h:34-61 (fields that are read back)
+    uint32_t ref_ID;
+    uint32_t ref_offset;
+    uint32_t index_in_read;
+    int32_t  pre;                 // chain_anchor_pre as an index, -1 = NULL
+    uint16_t mtch_len;
+    int16_t  score;
+    uint8_t  direction;
+    uint8_t  useless;             // anchor_useless
+    uint8_t  duplicate;
+    uint8_t  pad;
+};
+
+struct DsbChain {                 // chain_item src/cly.h:69-89
+    uint32_t ref_ID;
+    int32_t  q_t_dis;
+    uint32_t sum_score;
+    uint32_t anchor_number;
+    uint32_t t_st, t_ed, q_st, q_ed;
+    uint32_t indel;
+    int32_t  cur;                 // chain_anchor_cur as an index
+    uint8_t  direction;
+    uint8_t  with_top;
+    uint8_t  primary;
+    uint8_t  pri_index;
+};
+
+struct DsbSms {                   // spd_match src/cly.h:128-134
+    uint32_t t_pos, q_pos, len, score;
+};
+
+struct DsbMem {                   // MEM_rst src/cly.c:614-622
+    int32_t  match_len;
+    int32_t  sa_sp_l;
+    uint64_t sp;
+    uint64_t sa_sp;
+    int32_t  read_offset;
+    int32_t  pad;
+};
+
+struct DsbScHash {                // seed_con_hash src/cly.h:120-125
+    uint16_t next;
+    uint16_t seed_ID;             // 15 bits
+    uint8_t  s_or_e;
+    uint8_t  pad;
+};
+
+struct DsbStats {
+    unsigned long long occ, lut, sa, unitig, refpos, ref_bytes, mem_search, map_seed, sdp_win, slow;
+};
+
+// Everything one warp needs while it owns a read.  Pointers reference the warp's private slice
+// of the global scratch arena (L1/L2 resident while in use).
+struct DsbWork {
+    const DsbIndexView *ix;
+    // the read: bin[-DSB_HEAD_PAD .. 2L+DSB_TAIL_PAD), F at 0, R at L (src/cly.c:1242,1250)
+    uint8_t *bin;
+    uint32_t L;
+    uint32_t is_2g;               // buff->max_read_l < 510 after this read (src/cly.c:2953-2955)
+    const uint8_t *exist[2];      // [0] forward strand k-mer exist bytes, [1] reverse
+    // islands
+    DsbSeed *seeds[2];            // [0] forward, [1] reverse
+    uint32_t n_seeds[2];
+    uint32_t total_score[2];
+    // anchors / chains
+    DsbAnchor *anchors, *anchors_tmp;
+    uint32_t n_anchor, cap_anchor;
+    DsbChain *chains, *chains_tmp;
+    uint32_t n_chain, cap_chain;
+    uint32_t *sort_a, *sort_b;    // index buffers for the merge sort, cap_anchor each
+    int32_t *score_v;             // 1024 ints (M3 DP)
+    uint64_t *sp_set;             // 500
+    DsbMem *mems;                 // 256
+    // scoring
+    DsbSms *sms;
+    uint32_t n_sms, cap_sms;
+    uint32_t *h_head[2];          // [0] forward strand table, [1] reverse; 2^key_len entries
+    uint32_t *h_next[2];          // L entries
+    uint32_t *h_kmer[2];          // L entries
+    DsbScHash *sc_hash;           // 256 + 2*400
+    uint8_t *ref_mid;             // 2000+64  : sdp_middle window  (persistent per warp)
+    uint8_t *ref_ext;             // 1000+64+64 : right / left window
+    uint32_t fast_classify;
+    uint32_t overflow;            // set when an arena was too small -> batch is re-run bigger
+    DsbStats st;
+};
+
+#define DSB_MAX(a, b) (((a) > (b)) ? (a) : (b))     // src/lib/utils.h:61-64 (same macro shapes:
+#define DSB_MIN(a, b) (((a) < (b)) ? (a) : (b))     //  mixed signed/unsigned operands convert
+#define DSB_ABS(a) (((a) > 0) ? (a) : (-(a)))       //  exactly as in the reference)
+#define DSB_ABS_U(a, b) (((a) > (b)) ? ((a) - (b)) : ((b) - (a)))
+
+// ------------------------------------------------------------------------------------------
+// FM index: rank query on the 64-symbol block (restates occ, src/bwt.c:43-65)
+// ------------------------------------------------------------------------------------------
+// number of nibbles equal to c among the low `n` nibbles (n in [0,16]) of w
+DSB_HD uint32_t dsb_nib_eq_count(uint64_t w, uint32_t c, uint32_t n)
+{
+    uint64_t x = w ^ (0x1111111111111111ull * (uint64_t)c);   // matching nibbles become 0
+    x |= x >> 2;
+    x |= x >> 1;                                              // bit0 of each nibble = (nibble != 0)
+    x = ~x & 0x1111111111111111ull;
+    if (n < 16) x &= (1ull << (4 * n)) - 1ull;
+#if defined(DSB_DEVICE_CODE)
+    return (uint32_t)__popcll(x);
+#else
+    return (uint32_t)__builtin_popcountll(x);
+#endif
+}
+
+// occ(bt, r, &c): *c == 0xff means "use the symbol at row r" (written back to *c).
+// Returns the count of *c in BWT[0, r)  (r exclusive), or dollar_pos when
+// the symbol at r is '$'.  The caller adds rank[*c].
+DSB_HD uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
+{
+    const DsbIndexView *ix = w->ix;
+    const uint64_t blk = r >> 6;
+    const uint32_t in = (uint32_t)(r & 63);
+    const DsbFmBlock *b = ix->fm + blk;
+    w->st.occ++;
+#if defined(DSB_DEVICE_CODE)
+    const uint4 *p = reinterpret_cast<const uint4 *>(b);
+    uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
+    uint64_t cnt[4] = {((uint64_t)v0.y << 32) | v0.x, ((uint64_t)v0.w << 32) | v0.z,
+                       ((uint64_t)v1.y << 32) | v1.x, ((uint64_t)v1.w << 32) | v1.z};
+    uint64_t sym[4] = {((uint64_t)v2.y << 32) | v2.x, ((uint64_t)v2.w << 32) | v2.z,
+                       ((uint64_t)v3.y << 32) | v3.x, ((uint64_t)v3.w << 32) | v3.z};
+#else
+    const uint64_t *cnt = b->cnt;
+    const uint64_t *sym = b->sym;
+#endif
+    if (*c == 0xff) {
+        *c = (uint8_t)((sym[in >> 4] >> ((in & 15) << 2)) & 0xf);
+        if (*c == 5) return ix->dollar_pos;
+    }
+    const uint32_t cc = *c;
+    uint64_t base;
+    if (cc < 4) {
+        base = cnt[cc];
+    } else {
+        // '#': everything before the block that is not A/C/G/T/$
+        const uint64_t start = blk << 6;
+        base = start - (cnt[0] + cnt[1] + cnt[2] + cnt[3]) - ((ix->dollar_pos < start) ? 1 : 0);
+    }
+    uint32_t k = 0;
+    const uint32_t full = in >> 4;
+    for (uint32_t i = 0; i < 4; i++) {
+        if (i < full) k += dsb_nib_eq_count(sym[i], cc, 16);
+        else if (i == full) k += dsb_nib_eq_count(sym[i], cc, in & 15);
+    }
+    return base + k;
+}
+
+// ------------------------------------------------------------------------------------------
+// 2-bit reference fetch (restates get_ref, src/cly.c:434-461)
+// forward: bases uni_offset .. uni_offset+length-1; reverse: uni_offset down to uni_offset-length+1
+// ------------------------------------------------------------------------------------------
+DSB_HD uint8_t dsb_ref_base(const DsbIndexView *ix, uint64_t pos)
+{
+    const uint64_t byte = pos >> 2;
+    // the reference reads whatever lies beyond the array; we define those bases as 'A'
+    uint8_t v = (byte < ix->ref_bin_n) ? ix->ref_bin[byte] : (uint8_t)0;
+    return (uint8_t)((v >> ((3 - (uint32_t)(pos & 3)) << 1)) & 3);
+}
+
+DSB_HD void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t length, bool is_forward)
+{
+    const DsbIndexView *ix = w->ix;
+    w->st.ref_bytes += (length + 3) >> 2;
+#if defined(DSB_DEVICE_CODE)
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t k = lane; k < length; k += 32)
+        dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
+    __syncwarp();
+#else
+    for (uint32_t k = 0; k < length; k++)
+        dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
+#endif
+}
+
+// ------------------------------------------------------------------------------------------
+// Landau-Vishkin semi-global extension with at most 4 edits (restates lv_extd, src/cly.c:505-604)
+// The reference plants '#' / '$' sentinels in place and restores them; we work on private copies.
+// Both strings always have the same length here (every call site passes len, len).
+// Returns the edit distance, or `len` when no alignment with <= 4 edits exists.
+// ------------------------------------------------------------------------------------------
+DSB_HD int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len)
+{
+    if (len <= 0) return 0;                   // returns 0 whatever the bytes are
+    uint8_t rbuf[8 + DSB_LV_L + 2], qbuf[8 + DSB_LV_L + 2];
+    uint8_t *ref = rbuf + 8, *query = qbuf + 8;
+    for (int i = 0; i < 8; i++) { rbuf[i] = 0xE0; qbuf[i] = 0xD0; }   // never equal to anything
+    for (int i = 0; i < len; i++) { ref[i] = ref_in[i]; query[i] = query_in[i]; }
+    const int32_t ref_length = len, query_length = len;
+    ref[ref_length] = '#';
+    query[query_length] = '$';
+    int32_t mn_d[14], ed_d[14];
+    int32_t *mn = mn_d + DSB_LV_ERROR + 1, *ed = ed_d + DSB_LV_ERROR + 1;
+    int32_t prev_mn, cur_mn, next_mn, prev_ed, cur_ed, next_ed;
+    int32_t best_score = query_length;
+    for (int i = -DSB_LV_ERROR - 1; i <= DSB_LV_ERROR + 1; i++) {
+        mn[i] = -1;
+        ed[i] = (i > 0) ? i : -i;
+    }
+    mn[DSB_LV_ERROR + 2] = -1; ed[DSB_LV_ERROR + 2] = DSB_LV_ERROR + 2;   // read but never used
+    for (int i = 0; i <= DSB_LV_ERROR; i++) {
+        prev_mn = -1;
+        cur_mn = i - 1;
+        next_mn = mn[-i + 1];
+        prev_ed = i + 1;
+        cur_ed = i;
+        next_ed = ed[-i + 1];
+        for (int j = -i; j <= DSB_LV_ERROR; j++) {
+            if (cur_mn + j < ref_length - 1) {
+                int m = cur_mn + 1 - cur_ed;
+                mn[j] = cur_mn + 1;
+                ed[j] = cur_ed + 1;
+                if (m < next_mn + 1 - next_ed) {
+                    mn[j] = next_mn + 1;
+                    ed[j] = next_ed + 1;
+                    m = next_mn - next_ed;
+                }
+                if (m < prev_mn - prev_ed) {
+                    mn[j] = prev_mn + 1;
+                    ed[j] = prev_ed + 1;
+                }
+            } else {
+                int m = cur_mn - cur_ed;
+                mn[j] = cur_mn;
+                ed[j] = cur_ed + 1;
+                if (m < prev_mn - prev_ed) {
+                    mn[j] = prev_mn;
+                    ed[j] = prev_ed + 1;
+                    m = prev_mn - prev_ed;
+                }
+                if (m < next_mn + 1 - next_ed) {
+                    mn[j] = next_mn + 1;
+                    ed[j] = next_ed + 1;
+                }
+            }
+            int mn_j = DSB_MIN(mn[j], query_length);
+            mn_j = DSB_MIN(mn_j, ref_length - j);
+            for (; ref[mn_j + j] == query[mn_j]; mn_j++) {}
+            mn[j] = mn_j;
+            if (query[mn_j] == '$' || ref[mn_j + j] == '#') {
+                best_score = DSB_MIN(ed[j] - 1, best_score);
+                if (j <= i + 1) return best_score;
+            }
+            prev_mn = cur_mn; cur_mn = next_mn; next_mn = mn[j + 2];
+            prev_ed = cur_ed; cur_ed = next_ed; next_ed = ed[j + 2];
+        }
+    }
+    return best_score;
+}
+
+// ------------------------------------------------------------------------------------------
+// exist-k-mer probe (restates store_kmers src/cly.c:359-397, get_exist_kmer src/cly.c:951-967,
+// hash64_1/2 src/lib/utils.c:1067-1091).  Evaluated for EVERY k-mer position by the exist
+// kernel (one thread per position); the island scan below then replays the reference's
+// data-dependent probe order over the precomputed bits, which is equivalent because the probe
+// is a pure function of the k-mer.
+// ------------------------------------------------------------------------------------------
+DSB_HD uint64_t dsb_hash64_1(uint64_t key)
+{
+    key = (~key + (key << 21));
+    key = key ^ key >> 24;
+    key = ((key + (key << 3)) + (key << 8));
+    key = key ^ key >> 14;
+    key = ((key + (key << 2)) + (key << 4));
+    key = key ^ key >> 28;
+    key = (key + (key << 31));
+    return key;
+}
+
+DSB_HD uint64_t dsb_hash64_2(uint64_t key)
+{
+    key += ~(key << 32);
+    key ^= (key >> 22);
+    key += ~(key << 13);
+    key ^= (key >> 8);
+    key += (key << 3);
+    key ^= (key >> 15);
+    key += ~(key << 27);
+    key ^= (key >> 31);
+    return key;
+}
+
+// exist bit of the k-mer starting at s[0]; probes counts first/second table probes.
+DSB_HD uint8_t dsb_exist_kmer(const DsbIndexView *ix, const uint8_t *s, uint32_t *probes0, uint32_t *probes1)
+{
+    const int k = ix->ek_len;
+    int cnt[4] = {0, 0, 0, 0};
+    uint64_t kmer = 0;
+    for (int i = 0; i < k; i++) {
+        const uint8_t b = s[i] & 3;
+        cnt[b]++;
+        kmer = (kmer << 2) | b;
+    }
+    const int m = ix->single_base_max;
+    if (cnt[0] >= m || cnt[1] >= m || cnt[2] >= m || cnt[3] >= m) return 0;   // low complexity -> k-mer 0
+    if (kmer == 0) return 0;
+    const uint64_t h1 = dsb_hash64_1(kmer) & ix->ek_mask;
+    (*probes0)++;
+    if (((ix->ek0[h1 >> 3] >> (7 - (h1 & 7))) & 1) == 0) return 0;
+    const uint64_t h2 = dsb_hash64_2(kmer) & ix->ek_mask;
+    (*probes1)++;
+    return (uint8_t)((ix->ek1[h2 >> 3] >> (7 - (h2 & 7))) & 1);
+}
+
+// ------------------------------------------------------------------------------------------
+// islands (restates search_exist_kmer_M2 src/cly.c:1066-1155 and the `top` marking of
+// get_seed_vector_M2 src/cly.c:1157-1229).  ex[i] = exist bit of k-mer i, n = L-k+1.
+// ------------------------------------------------------------------------------------------
+DSB_HD void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
+{
+    const uint8_t *ex = w->exist[strand];
+    const uint32_t n = w->L - (uint32_t)w->ix->ek_len + 1;
+    DsbSeed *sv = w->seeds[strand];
+    uint32_t ns = 0;
+    if (strand == 0) {
+        for (uint32_t i = DSB_STEP_EK - 1; i < n; i += DSB_STEP_EK) {
+            if (ex[i] != 1) continue;
+            uint32_t offset = i, len = 1;
+            for (int j = 1; j < DSB_STEP_EK; ++j) {
+                if (ex[i - j] == 1) { offset--; len++; } else break;
+            }
+            for (uint32_t j = 1; i + j < n; ++j) {
+                if (ex[i + j] == 1) { len++; if (len > 60) break; } else break;
+            }
+            sv[ns].offset = offset;
+            sv[ns].len = len;
+            ns++;
+            i = offset + len;
+        }
+    } else {
+        for (int i = (int)(n - DSB_STEP_EK); i >= 0; i -= DSB_STEP_EK) {
+            if (ex[i] != 1) continue;
+            uint32_t offset = (uint32_t)i, len = 1;
+            for (int j = 1; j < DSB_STEP_EK; ++j) {
+                if (ex[i + j] == 1) { offset++; len++; } else break;
+            }
+            for (int j = 1; j <= i; ++j) {
+                if (ex[i - j] == 1) { len++; if (len > 60) break; } else break;
+            }
+            sv[ns].offset = offset - len + 1;
+            sv[ns].len = len;
+            ns++;
+            i = (int)(offset - len);
+        }
+    }
+    // top 1 island per 100 bp window (replayed literally)
+    uint32_t total = 0, max_index = 0, max_length = 0, index_end = DSB_SEED_RANGE;
+    for (uint32_t m = 0; m < ns; m++) {
+        sv[m].top = 0;
+        const uint32_t key = (strand == 0) ? sv[m].offset : (n - sv[m].offset - sv[m].len);
+        if (key < index_end) {
+            if (max_length < sv[m].len) { max_length = sv[m].len; max_index = m; }
+            sv[max_index].top = 0;
+        } else {
+            sv[max_index].top = 1;
+            index_end += DSB_SEED_RANGE;
+            total += max_length;
+            max_index = m;
+            max_length = sv[m].len;
+        }
+    }
+    sv[max_index].top = 1;      // also executed with ns == 0 in the reference (harmless there too)
+    total += max_length;
+    w->n_seeds[strand] = ns;
+    w->total_score[strand] = total;
+}
+
+// ------------------------------------------------------------------------------------------
+// FM seeding (restates sp_set_insert src/cly.c:1281-1293, bwt_single_search :1339-1378,
+// bwt_MEM_search :1383-1442)
+// ------------------------------------------------------------------------------------------
+struct DsbSpSet { uint64_t *set; int l, m; };
+
+// insert fails (returns 0) when the row is already present; the list silently empties when
+// full
+DSB_HD int dsb_sp_set_insert(uint64_t node, DsbSpSet *s)
+{
+    if (s->l == s->m) s->l = 0;
+    uint64_t *set = s->set;
+#if defined(DSB_DEVICE_CODE)
+    const uint32_t lane = threadIdx.x & 31;
+    bool found = false;
+    for (int i = lane; i < s->l; i += 32) found |= (set[i] == node);
+    if (__any_sync(0xffffffffu, found)) return 0;
+    if (lane == 0) set[s->l] = node;
+    __syncwarp();
+#else
+    for (int i = 0; i < s->l; i++)
+        if (set[i] == node) return 0;
+    set[s->l] = node;
+#endif
+    s->l++;
+    return 1;
+}
+
+// single-row LF walk to the left while the BWT symbol equals the next read base.
+// `str` points at the next base to compare (moving towards index 0).
+DSB_HD void dsb_single_search(DsbWork *w, uint64_t sp, const uint8_t *str, int max_match_len,
+                              DsbSpSet *sp_set, DsbMem *m)
+{
+    const uint64_t *rank = w->ix->rank;
+    uint64_t new_sp, sa_sp = 0xffffffffffffffffull;
+    int match_len = 0, sa_sp_l = 0;
+    while (1) {
+        if (match_len >= max_match_len) break;
+        if ((sp & DSB_SA_MASK) == 0) { sa_sp = sp; sa_sp_l = 0; }
+        else sa_sp_l--;
+        uint8_t c = 0xff;
+        new_sp = dsb_occ(w, sp, &c);
+        new_sp += rank[c];
+        if (c != *str) break;
+        match_len++;
+        str--;
+        if (dsb_sp_set_insert(new_sp, sp_set) == 0) { m->match_len = -1000; return; }
+        sp = new_sp;
+    }
+    m->sp = sp;
+    m->match_len = match_len;
+    m->sa_sp = sa_sp;
+    m->sa_sp_l = sa_sp_l;
+}
+
+// `str` points at the LAST base of the exist-k-mer; pre_v is the value of its last 13 bases.
+DSB_HD int dsb_mem_search(DsbWork *w, const uint8_t *str, uint64_t pre_v, int max_rst, int l_min_mth,
+                          int l_max_mth, DsbSpSet *sp_set, DsbMem *mem)
+{
+    const uint64_t *rank = w->ix->rank;
+    int n_rst = 0;
+    w->st.mem_search++;
+    w->st.lut++;
+    uint64_t sp = w->ix->lut[pre_v], ep = w->ix->lut[pre_v + 1], new_sp, new_ep;
+    str -= DSB_L_PRE_IDX;
+    int match_len = DSB_L_PRE_IDX;
+    uint8_t c;
+    while (1) {
+        c = *str;
+        str--;
+        new_sp = rank[c] + dsb_occ(w, sp, &c);
+        new_ep = rank[c] + dsb_occ(w, ep, &c);
+        if (match_len >= l_min_mth - 1) {
+            if (new_sp + (uint64_t)(int64_t)max_rst >= new_ep) break;
+            if (match_len >= l_max_mth) return 0;
+        }
+        if (new_sp + 1 >= new_ep) break;
+        match_len++;
+        sp = new_sp;
+        ep = new_ep;
+    }
+    if (new_sp >= new_ep) return 0;
+    if (new_sp + 1 == new_ep) {
+        if (dsb_sp_set_insert(new_sp, sp_set) == 0) return 0;
+        dsb_single_search(w, new_sp, str, DSB_MAX(0, l_max_mth - match_len), sp_set, mem + n_rst);
+        mem[n_rst].match_len += match_len + 1;
+        if (mem[n_rst].match_len >= l_min_mth) n_rst++;
+    } else {
+        for (uint64_t c_sp = new_sp; c_sp < new_ep; c_sp++) {
+            if (dsb_sp_set_insert(c_sp, sp_set) == 0) continue;
+            dsb_single_search(w, c_sp, str, DSB_MAX(0, l_max_mth - match_len), sp_set, mem + n_rst);
+            mem[n_rst].match_len += match_len + 1;
+            if (mem[n_rst].match_len >= l_min_mth) n_rst++;
+        }
+    }
+    return n_rst;
+}
+
+// ------------------------------------------------------------------------------------------
+// seed -> unitig -> reference anchors (restates get_uni src/cly.c:466-491, get_new_ed :624-689,
+// map_seed :701-934)
+// ------------------------------------------------------------------------------------------
+// returns the unitig index; *global_offset / *uni_offset as in the reference
+DSB_HD uint64_t dsb_get_uni(DsbWork *w, uint64_t bwt_pos, int search_l, uint64_t *global_offset, uint32_t *uni_offset_)
+{
+    const DsbIndexView *ix = w->ix;
+    const uint64_t sa = ix->sa[bwt_pos >> DSB_SA_OFF];
+    w->st.sa++;
+    uint64_t uni = (uint32_t)sa;
+    uint32_t uni_offset = (uint32_t)(sa >> 32) + (uint32_t)search_l + 1;
+    if (search_l > 0) {
+        for (;;) {
+            const uint32_t ulen = (uint32_t)(ix->unitig[uni] >> 32);
+            w->st.unitig++;
+            if (uni_offset < ulen) break;
+            uni_offset -= (ulen + 1);
+            uni++;
+        }
+    }
+    // the reference's other branch (`uni_offset < 0` on an unsigned) is dead code
+    const uint32_t ref_list = (uint32_t)ix->unitig[uni];
+    w->st.unitig++;
+    w->st.refpos++;
+    *global_offset = (ix->ref_pos[ref_list] & 0xFFFFFFFFFFull) + uni_offset;
+    *uni_offset_ = uni_offset;
+    return uni;
+}
+
+// q_b = strand base pointer (index 0 = first base of the strand)
+DSB_HD void dsb_get_new_ed(DsbWork *w, uint32_t *e_d, uint32_t *len_, uint32_t *l_mem_ext, int32_t q_off,
+                           uint64_t t_off, uint32_t l_read, const uint8_t *q_b, bool is_fwd)
+{
+    uint8_t q_buff[13], t_buff[13];
+    const uint8_t *q = q_buff;
+    uint8_t *t = t_buff;
+    uint32_t len, max_len;
+    if (is_fwd) {
+        if (q_off < 0) q_off = 0;
+        max_len = (uint32_t)q_off;
+        len = DSB_MIN(12u, max_len);
+        for (uint8_t k = 0; k < len; k++) q_buff[k] = q_b[q_off - k];
+    } else {
+        max_len = l_read - (uint32_t)q_off;
+        len = DSB_MIN(12u, max_len);
+        q = q_b + q_off;
+    }
+    dsb_get_ref(w, t, t_off, len, !is_fwd);
+    if (len > 0 && t[0] == q[0]) {
+        uint32_t mtc;
+        do {
+            for (mtc = 0; mtc < len; mtc++)
+                if (t[mtc] != q[mtc]) break;
+            if (mtc > 0) {
+                *l_mem_ext += mtc;
+                max_len -= mtc;
+                len = DSB_MIN(12u, max_len);
+                if (is_fwd) {
+                    q_off -= (int32_t)mtc;
+                    t_off -= mtc;
+                    for (uint8_t k = 0; k < len; k++) q_buff[k] = q_b[q_off - k];
+                } else {
+                    t_off += mtc;
+                    q += mtc;
+                }
+                dsb_get_ref(w, t, t_off, len, !is_fwd);
+            }
+        } while (mtc > 0);
+    }
+    *e_d = (uint32_t)dsb_lv_extd(t, q, (int32_t)len);
+    *len_ = len;
+}
+
+DSB_HD void dsb_push_anchor(DsbWork *w, const DsbAnchor *a)
+{
+    if (w->n_anchor >= w->cap_anchor) { w->overflow = 1; return; }
+    w->anchors[w->n_anchor++] = *a;
+}
+
+// returns the best anchor score produced by this MEM
+DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32_t read_L, uint8_t direction)
+{
+    const DsbIndexView *ix = w->ix;
+    const int32_t *Q_MEM = ix->q_mem;
+    const int32_t *Q_LV = ix->q_lv;       // Q_LV[d][l] = Q_LV[d*20 + l]
+    uint64_t b_p = m_r->sp;
+    int32_t q_off = m_r->read_offset;
+    uint32_t l_m = (uint32_t)m_r->match_len;
+    bool have_uni = false;
+    uint64_t uni = 0;
+    uint32_t uni_len = 0;
+    uint32_t u_off = 0;
+    uint64_t t_off = 0;
+    uint32_t l_pre = 0, l_suf = 0, d_pre = 0, d_suf = 0;
+    int32_t s = 0, max_s = 0;
+    w->st.map_seed++;
+    do {
+        uint8_t q_pre[DSB_LV_L + 1], t_pre[DSB_LV_L + 1], t_suf[DSB_LV_L + 1];
+        const uint8_t *q_suf;
+        // the reference leaves q_pre uninitialised when the MEM starts at read base 0 and then
+        // compares q_pre[0] (src/cly.c:727-757 with l_pre = 0 -> s_l); we define it as a mismatch
+        for (int k = 0; k <= DSB_LV_L; k++) { q_pre[k] = 0xF1; t_pre[k] = 0xF2; t_suf[k] = 0xF3; }
+        l_pre = (uint32_t)DSB_MIN(q_off + 1, DSB_LV_L);
+        for (uint8_t k = 0; k < l_pre; k++) q_pre[k] = q_b[q_off - k];
+        int s_l = 0;
+        if (m_r->sa_sp != 0xffffffffffffffffull) {
+            uni = dsb_get_uni(w, m_r->sa_sp, m_r->sa_sp_l, &t_off, &u_off);
+            have_uni = true;
+        } else {
+            uint8_t c;
+            uint64_t new_sp;
+            while (1) {
+                if ((b_p & DSB_SA_MASK) == 0) break;
+                c = 0xff;
+                new_sp = dsb_occ(w, b_p, &c);
+                new_sp += ix->rank[c];
+                if (c == 4) break;
+                t_pre[s_l++] = c;
+                b_p = new_sp;
+                if (s_l >= (int)l_pre) break;
+            }
+            if ((b_p & DSB_SA_MASK) == 0) {
+                uni = dsb_get_uni(w, b_p, s_l, &t_off, &u_off);
+                have_uni = true;
+            } else
+                l_pre = (uint32_t)s_l;
+        }
+        if (have_uni) {
+            uni_len = (uint32_t)(ix->unitig[uni] >> 32);
+            if (uni_len < DSB_MIN_UNI_L) break;
+            l_pre = DSB_MIN(l_pre, u_off);
+            dsb_get_ref(w, t_pre, t_off - 1, l_pre, false);
+        }
+        d_pre = (uint32_t)dsb_lv_extd(t_pre, q_pre, (int32_t)l_pre);
+        s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+        if (s < DSB_MIN_S_1 && l_pre == DSB_LV_L && !have_uni) { s = 0; break; }
+        if (!have_uni) {
+            while (b_p & DSB_SA_MASK) {
+                uint8_t c = 0xff;
+                b_p = dsb_occ(w, b_p, &c);
+                b_p += ix->rank[c];
+                s_l++;
+            }
+            uni = dsb_get_uni(w, b_p, s_l, &t_off, &u_off);
+            have_uni = true;
+            uni_len = (uint32_t)(ix->unitig[uni] >> 32);
+            if (uni_len < DSB_MIN_UNI_L) { s = 0; break; }
+        }
+        int32_t q_off_r = q_off + (int32_t)l_m + 1;
+        uint32_t l_max_suf = DSB_MIN(uni_len - u_off - l_m, read_L - (uint32_t)q_off_r);
+        if (l_max_suf != 0) {
+            l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
+            q_suf = q_b + q_off_r;
+            dsb_get_ref(w, t_suf, t_off + l_m, l_suf, true);
+            if (t_suf[0] == q_suf[0]) {
+                uint32_t mtc;
+                do {
+                    for (mtc = 0; mtc < l_suf; mtc++)
+                        if (t_suf[mtc] != q_suf[mtc]) break;
+                    if (mtc > 0) {
+                        l_m += mtc;
+                        s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+                        l_max_suf -= mtc;
+                        l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
+                        q_suf += mtc;
+                        dsb_get_ref(w, t_suf, t_off + l_m, l_suf, true);
+                    }
+                } while (mtc > 0);
+            }
+            d_suf = (uint32_t)dsb_lv_extd(t_suf, q_suf, (int32_t)l_suf);
+            s += Q_LV[d_suf * 20 + l_suf];
+        } else
+            l_suf = d_suf = 0;
+        if (s <= DSB_MIN_S_2 && l_suf == DSB_LV_L) { s = 0; break; }
+    } while (0);
+
+    if (s > 0) {
+        // Anchor_map a_m = {l_m, s, l_pre, d_pre, l_suf, d_suf} with the reference's field widths
+        uint16_t am_mtch = (uint16_t)l_m;
+        int16_t am_score = (int16_t)s;
+        uint8_t am_left_len = (uint8_t)l_pre, am_left_ED = (uint8_t)d_pre;
+        uint8_t am_rigt_len = (uint8_t)l_suf, am_rigt_ED = (uint8_t)d_suf;
+        const uint32_t rp_s = (uint32_t)ix->unitig[uni], rp_e = (uint32_t)ix->unitig[uni + 1];
+        w->st.unitig++;
+        const bool ref_search_l = (l_pre < DSB_LV_L || d_pre == 0);
+        const bool ref_search_r = (l_suf < DSB_LV_L || d_suf == 0);
+        if ((int64_t)rp_e - (int64_t)rp_s > 50) {
+            if (!((int64_t)rp_e - (int64_t)rp_s < 1000)) return 50;
+        }
+        for (uint32_t rp = rp_s; rp < rp_e; rp++) {
+            const uint64_t rpv = ix->ref_pos[rp];
+            w->st.refpos++;
+            const uint64_t r_global = rpv & 0xFFFFFFFFFFull;
+            const uint32_t r_ref_ID = (uint32_t)((rpv >> 40) & 0x7FFFFF);
+            uint32_t ed_l, ed_r, len_l, len_r;
+            uint32_t l_m_ext_l = 0, l_m_ext_r;
+            if (ref_search_l || ref_search_r) {
+                if (ref_search_l) {
+                    dsb_get_new_ed(w, &ed_l, &len_l, &l_m_ext_l, q_off, r_global + u_off - 1, read_L, q_b, true);
+                    am_left_len = (uint8_t)len_l;
+                    am_left_ED = (uint8_t)ed_l;
+                }
+                am_mtch = (uint16_t)(l_m + l_m_ext_l);
+                if (ref_search_r) {
+                    l_m_ext_r = 0;
+                    dsb_get_new_ed(w, &ed_r, &len_r, &l_m_ext_r, q_off + (int32_t)l_m + 1, r_global + u_off + l_m,
+                                   read_L, q_b, false);
+                    am_rigt_len = (uint8_t)len_r;
+                    am_rigt_ED = (uint8_t)ed_r;
+                    am_mtch = (uint16_t)(am_mtch + l_m_ext_r);
+                }
+                am_score = (int16_t)(Q_MEM[am_mtch] + Q_LV[am_left_ED * 20 + am_left_len] +
+                                     Q_LV[am_rigt_ED * 20 + am_rigt_len]);
+                if (am_score < DSB_MIN_S_2) continue;
+            }
+            max_s = DSB_MAX(max_s, (int32_t)am_score);
+            DsbAnchor a;
+            a.direction = direction;
+            a.index_in_read = (uint32_t)(q_off + 1) - l_m_ext_l;
+            const uint64_t g = r_global + u_off - l_m_ext_l;
+            a.ref_ID = r_ref_ID;
+            a.ref_offset = (uint32_t)(g - ix->ref_off[r_ref_ID]);
+            a.mtch_len = am_mtch;
+            a.score = am_score;
+            a.pre = -1;
+            a.useless = 0;
+            a.duplicate = 0;
+            a.pad = 0;
+            dsb_push_anchor(w, &a);
+        }
+    }
+    return max_s;
+}
+
+// ------------------------------------------------------------------------------------------
+// seeding drivers (restates fast_classify src/cly.c:1473-1541, slow_classify :1545-1606)
+// ------------------------------------------------------------------------------------------
+// value of the 13 bases ending at str[0] (== kmer & PRE_IDX_MASK for every k-mer that passed the
+// complexity filter, which all island k-mers did)
+DSB_HD uint64_t dsb_prefix13(const uint8_t *str)
+{
+    uint64_t v = 0;
+    for (int i = DSB_L_PRE_IDX - 1; i >= 0; i--) v = (v << 2) | (uint64_t)(str[-i] & 3);
+    return v;
+}
+
+DSB_HD void dsb_mark_useless(DsbWork *w, uint32_t a_b, uint32_t a_e)
+{
+    int top_score = 35;
+    for (uint32_t i = a_b; i < a_e; i++) top_score = DSB_MAX(top_score, (int)w->anchors[i].score);
+    for (uint32_t i = a_b; i < a_e; i++) w->anchors[i].useless = (w->anchors[i].score < top_score) ? 1 : 0;
+}
+
+// strand: 0 forward, 1 reverse (index into w->seeds / bin halves)
+DSB_HDN void dsb_fast_classify(DsbWork *w, int strand)
+{
+    const int l_ek = w->ix->ek_len;
+    const int min_index = 21 - l_ek;                      // MIN_MEM_LEN_FAST - l_ek
+    const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
+    const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
+    DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX};
+    DsbMem *m_r = w->mems;
+    const DsbSeed *sv = w->seeds[strand];
+    const uint32_t nsv = w->n_seeds[strand];
+    for (uint32_t ci = 0; ci < nsv; ci++) {
+        if (sv[ci].top == 0) continue;
+        sp_set.l = 0;
+        const uint32_t a_b_idx = w->n_anchor;
+        for (int j = (int)sv[ci].len - 1; j >= min_index;) {
+            const int kmer_index = (int)sv[ci].offset + j;
+            const int string_index = kmer_index + l_ek - 1;
+            const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
+            const int n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
+            if (n_mem == 0) { j -= 2; continue; }
+            j -= 3;
+            int max_score = 0;
+            for (int mi = 0; mi < n_mem; mi++) {
+                m_r[mi].read_offset = string_index - m_r[mi].match_len;
+                const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, direction);
+                max_score = DSB_MAX(c_score, max_score);
+            }
+            if (max_score > 35) j -= 7;
+            if (max_score > 256) {
+                if (max_score > 512) ci++;
+                break;
+            }
+        }
+        dsb_mark_useless(w, a_b_idx, w->n_anchor);
+    }
+}
+
+// stable insertion sort of the MEM list by match_len descending: equivalent to the reference's
+// qsort (glibc merge sort, consistent comparator MEM_rst_cmp_by_match_len src/cly.c:1325-1328)
+DSB_HD void dsb_sort_mems(DsbMem *m, int n)
+{
+    for (int i = 1; i < n; i++) {
+        DsbMem key = m[i];
+        int j = i - 1;
+        while (j >= 0 && m[j].match_len < key.match_len) { m[j + 1] = m[j]; j--; }
+        m[j + 1] = key;
+    }
+}
+
+DSB_HDN void dsb_slow_classify(DsbWork *w, int strand)
+{
+    const int l_ek = w->ix->ek_len;
+    const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
+    const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
+    DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX};
+    DsbMem *mem_rst = w->mems;
+    const DsbSeed *sv = w->seeds[strand];
+    const uint32_t nsv = w->n_seeds[strand];
+    for (uint32_t i = 0; i < nsv; i++) {
+        if ((int)(sv[i].len) < 3 && sv[0].top == 0) continue;          // first seed's top
+        const int min_match_len = DSB_MIN(20 - 1, l_ek + 1);
+        sp_set.l = 0;
+        int mem_rst_num = 0;
+        for (int j = (int)sv[i].len - 1; j >= 1; j -= 2) {
+            const int k_idx = (int)sv[i].offset + j;
+            const int s_idx = k_idx + l_ek - 1;
+            const uint64_t pre_v = dsb_prefix13(bin_read + s_idx);
+            const int n_mem = dsb_mem_search(w, bin_read + s_idx, pre_v, 8, min_match_len, s_idx, &sp_set,
+                                             mem_rst + mem_rst_num);
+            for (int t = mem_rst_num; t < mem_rst_num + n_mem; t++)
+                mem_rst[t].read_offset = k_idx + l_ek - 1 - mem_rst[t].match_len;
+            mem_rst_num += n_mem;
+        }
+        if (mem_rst_num == 0) continue;
+        if (mem_rst_num > 1) dsb_sort_mems(mem_rst, mem_rst_num);
+        const uint32_t a_b_idx = w->n_anchor;
+        const int max_search = DSB_MIN(mem_rst_num, 8);
+        for (int t = 0; t < max_search; t++) dsb_map_seed(w, mem_rst + t, bin_read, w->L, direction);
+        dsb_mark_useless(w, a_b_idx, w->n_anchor);
+    }
+    w->fast_classify = 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// glibc-2.39 qsort replica.  The reference sorts with comparators that are not all consistent
+// (SURVEY.md 0-9, 7.3-2), so the RESULT depends on the algorithm: glibc's qsort here is the
+// top-down merge sort of msort.c -- split n1 = n/2, n2 = n-n1, sort both halves, merge taking
+// the LEFT element when cmp(left, right) <= 0.  We sort an index permutation with exactly that
+// recursion tree (explicit stack) and the caller applies the permutation.
+//   cmp(ctx, i, j) must return the reference comparator's value for elements i and j.
+// ------------------------------------------------------------------------------------------
+template <typename Cmp>
+DSB_HD void dsb_msort_idx(uint32_t *idx, uint32_t *tmp, uint32_t n, Cmp cmp)
+{
+    for (uint32_t i = 0; i < n; i++) idx[i] = i;
+    if (n <= 1) return;
+    // post-order walk of the split tree
+    uint32_t st_b[40], st_n[40];
+    uint8_t st_state[40];
+    int sp = 0;
+    st_b[0] = 0; st_n[0] = n; st_state[0] = 0;
+    while (sp >= 0) {
+        const uint32_t b = st_b[sp], nn = st_n[sp];
+        if (nn <= 1) { sp--; continue; }
+        const uint32_t n1 = nn / 2, n2 = nn - n1;
+        if (st_state[sp] == 0) {
+            st_state[sp] = 1;
+            sp++; st_b[sp] = b; st_n[sp] = n1; st_state[sp] = 0;
+            continue;
+        }
+        if (st_state[sp] == 1) {
+            st_state[sp] = 2;
+            sp++; st_b[sp] = b + n1; st_n[sp] = n2; st_state[sp] = 0;
+            continue;
+        }
+        // merge [b, b+n1) and [b+n1, b+nn)
+        uint32_t i1 = b, e1 = b + n1, i2 = b + n1, e2 = b + nn, o = 0;
+        while (i1 < e1 && i2 < e2) {
+            if (cmp(idx[i1], idx[i2]) <= 0) tmp[o++] = idx[i1++];
+            else tmp[o++] = idx[i2++];
+        }
+        while (i1 < e1) tmp[o++] = idx[i1++];
+        for (uint32_t k = 0; k < o; k++) idx[b + k] = tmp[k];   // the rest of the right run is in place
+        sp--;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// chaining (restates chain_insert_meta src/cly.c:71-111, chain_insert_M2 :200-223,
+// chain_insert_M3 :237-322, chain_cmp_by_score :37-51, resolve_tree :325-348)
+// ------------------------------------------------------------------------------------------
+DSB_HD DsbChain *dsb_push_chain(DsbWork *w)
+{
+    if (w->n_chain >= w->cap_chain) { w->overflow = 1; return w->chains + (w->cap_chain - 1); }
+    return w->chains + (w->n_chain++);
+}
+
+DSB_HD void dsb_chain_insert_meta(DsbWork *w, uint32_t ai, DsbChain *c, bool new_chain, int dis_minus)
+{
+    DsbAnchor *anchor = w->anchors + ai;
+    const uint32_t ref_l = anchor->ref_offset;
+    const uint32_t ref_r = ref_l + anchor->mtch_len;
+    const uint32_t read_l = anchor->index_in_read;
+    const uint32_t read_r = read_l + anchor->mtch_len;
+    if (new_chain) {
+        anchor->pre = -1;
+        c->ref_ID = anchor->ref_ID;
+        c->direction = anchor->direction;
+        c->q_t_dis = (int32_t)(anchor->ref_offset - anchor->index_in_read);
+        c->t_st = ref_l;
+        c->t_ed = ref_r;
+        c->q_st = read_l;
+        c->q_ed = read_r;
+        c->with_top = !anchor->useless;
+        c->anchor_number = 1;
+        c->sum_score = (anchor->duplicate) ? 1 : (uint32_t)(int32_t)anchor->score;
+        c->indel = 0;
+        c->cur = (int32_t)ai;
+    } else {
+        c->with_top |= (!anchor->useless);
+        if (c->q_ed >= read_r) return;
+        c->t_ed = DSB_MAX(ref_r, c->t_ed);
+        c->q_ed = read_r;
+        anchor->pre = c->cur;
+        c->cur = (int32_t)ai;
+        c->q_t_dis = (int32_t)(anchor->ref_offset - anchor->index_in_read);
+        c->indel += (uint32_t)dis_minus;
+        c->anchor_number++;
+        c->sum_score += (anchor->duplicate) ? 1 : (uint32_t)(int32_t)anchor->score;
+    }
+}
+
+DSB_HD void dsb_chain_insert_M2(DsbWork *w, uint32_t ai)
+{
+    const DsbAnchor *anchor = w->anchors + ai;
+    const uint8_t direction = anchor->direction;
+    const uint32_t ref_ID = anchor->ref_ID;
+    const int32_t dis = (int32_t)(anchor->ref_offset - anchor->index_in_read);
+    int dis_minus = 0;
+    for (uint32_t ci = 0; ci < w->n_chain; ci++) {
+        DsbChain *c_s = w->chains + ci;
+        if (c_s->direction == direction && c_s->ref_ID == ref_ID &&
+            (dis_minus = DSB_ABS(dis - c_s->q_t_dis)) < 30 &&
+            DSB_ABS_U(c_s->t_ed, anchor->ref_offset) < 400) {
+            dsb_chain_insert_meta(w, ai, c_s, false, dis_minus);
+            return;
+        }
+    }
+    DsbChain *nc = dsb_push_chain(w);
+    nc->primary = 0; nc->pri_index = 0;
+    dsb_chain_insert_meta(w, ai, nc, true, dis_minus);
+}
+
+DSB_HDN void dsb_chain_insert_M3(DsbWork *w)
+{
+    const uint32_t n = w->n_anchor;
+    // stable sort by (ref_ID, direction, ref_offset): Anchor_cmp_by_chr_ID_and_pos returns a>b
+    {
+        const DsbAnchor *A = w->anchors;
+        dsb_msort_idx(w->sort_a, w->sort_b, n, [A](uint32_t i, uint32_t j) -> int {
+            const DsbAnchor *a = A + i, *b = A + j;
+            if (a->ref_ID != b->ref_ID) return a->ref_ID > b->ref_ID;
+            if (a->direction != b->direction) return a->direction > b->direction;
+            return a->ref_offset > b->ref_offset;
+        });
+        for (uint32_t i = 0; i < n; i++) w->anchors_tmp[i] = w->anchors[w->sort_a[i]];
+        for (uint32_t i = 0; i < n; i++) w->anchors[i] = w->anchors_tmp[i];
+    }
+    DsbAnchor *A = w->anchors;
+    int32_t *score_v = w->score_v;
+    for (uint32_t chr_st = 0; chr_st < n;) {
+        uint32_t chr_ed = chr_st + 1;
+        const uint32_t ref_ID = A[chr_st].ref_ID;
+        const uint32_t direction = A[chr_st].direction;
+        for (; chr_ed < n && A[chr_ed].ref_ID == ref_ID && A[chr_ed].direction == direction &&
+               A[chr_ed].ref_offset - A[chr_ed - 1].ref_offset < 2000; chr_ed++) {}
+        if (chr_ed - chr_st > 1024) chr_ed = chr_st + 1024;
+        int32_t max_anchor = -1;
+        int max_score = 0, anchor_max_score;
+        for (uint32_t c_a = chr_st; c_a < chr_ed; c_a++) {
+            A[c_a].pre = -1;
+            anchor_max_score = A[c_a].score;
+            const uint32_t max_t = A[c_a].ref_offset + 3;
+            const uint32_t max_q = A[c_a].index_in_read + 3;
+            for (int32_t pre = (int32_t)c_a - 1; pre >= (int32_t)chr_st; pre--) {
+                const DsbAnchor *p = A + pre;
+                if (p->index_in_read + p->mtch_len > max_q) continue;
+                if (p->ref_offset + p->mtch_len > max_t) continue;
+                if (p->index_in_read + 1000 < max_q) break;
+                if (p->ref_offset + 1000 < max_t) break;
+                const int indel = (int)(p->index_in_read - p->ref_offset - (max_q - max_t));
+                const int ABS_indel = DSB_ABS(indel);
+                if (ABS_indel > 200) continue;
+                const int new_score = (int)(score_v[pre - (int32_t)chr_st] + A[c_a].mtch_len - (ABS_indel >> 4) -
+                                            ((max_q - p->index_in_read) >> 8));
+                if (new_score > anchor_max_score) {
+                    anchor_max_score = new_score;
+                    A[c_a].pre = pre;
+                }
+            }
+            score_v[c_a - chr_st] = anchor_max_score;
+            if (max_score < anchor_max_score) {
+                max_score = anchor_max_score;
+                max_anchor = (int32_t)c_a;
+            }
+        }
+        // the reference dereferences max_anchor unconditionally; every anchor score is >= 20 so
+        // max_anchor is always set
+        if (max_anchor < 0) max_anchor = (int32_t)chr_st;
+        int sum_INDEL = 0, anchor_number = 1;
+        int32_t pre = max_anchor;
+        int sum_score = (A[max_anchor].duplicate) ? 1 : A[max_anchor].score;
+        bool with_top = !A[max_anchor].useless;
+        for (; A[pre].pre != -1; anchor_number++) {               // replayed literally
+            const int32_t pre_ = A[pre].pre;
+            sum_INDEL += (int)((A[pre].index_in_read - A[pre_].index_in_read) - (A[pre].ref_offset - A[pre_].ref_offset));
+            with_top |= (!A[pre].useless);
+            sum_score += (A[pre].duplicate) ? 1 : A[pre].score;
+            pre = pre_;
+        }
+        DsbChain *nc = dsb_push_chain(w);
+        nc->ref_ID = ref_ID;
+        nc->direction = (uint8_t)direction;
+        nc->q_t_dis = (int32_t)(A[max_anchor].ref_offset - A[max_anchor].index_in_read);
+        nc->t_st = A[pre].ref_offset;
+        nc->t_ed = A[max_anchor].ref_offset + A[max_anchor].mtch_len;
+        nc->q_st = A[pre].index_in_read;
+        nc->q_ed = A[max_anchor].index_in_read + A[max_anchor].mtch_len;
+        nc->with_top = with_top;
+        nc->anchor_number = (uint32_t)anchor_number;
+        nc->sum_score = (uint32_t)sum_score;
+        nc->indel = (uint32_t)sum_INDEL;
+        nc->cur = max_anchor;
+        nc->primary = 0; nc->pri_index = 0;
+        chr_st = chr_ed;
+    }
+}
+
+DSB_HD void dsb_apply_chain_perm(DsbWork *w, uint32_t n)
+{
+    for (uint32_t i = 0; i < n; i++) w->chains_tmp[i] = w->chains[w->sort_a[i]];
+    for (uint32_t i = 0; i < n; i++) w->chains[i] = w->chains_tmp[i];
+}
+
+DSB_HDN void dsb_resolve_tree(DsbWork *w)
+{
+    w->n_chain = 0;
+    if (w->n_anchor < 50)
+        for (uint32_t ai = 0; ai < w->n_anchor; ai++) dsb_chain_insert_M2(w, ai);
+    else
+        dsb_chain_insert_M3(w);
+    if (w->n_chain > 1) {
+        const DsbChain *C = w->chains;
+        dsb_msort_idx(w->sort_a, w->sort_b, w->n_chain, [C](uint32_t i, uint32_t j) -> int {
+            const DsbChain *a = C + i, *b = C + j;
+            if (a->with_top != b->with_top) return (a->with_top) ? (-1) : (1);
+            int score_a = (int)(a->sum_score + ((a->q_ed - a->q_st) << 1));
+            score_a -= (int)(a->indel << 2);
+            int score_b = (int)(b->sum_score + ((b->q_ed - b->q_st) << 1));
+            score_b -= (int)(b->indel << 2);
+            if (score_a < score_b) return 1;
+            if (score_a > score_b) return -1;
+            return 0;
+        });
+        dsb_apply_chain_perm(w, w->n_chain);
+    }
+    uint32_t rst_num = DSB_MIN(5u, w->n_chain);
+    while (rst_num < w->n_chain && w->chains[rst_num].with_top == 1) rst_num++;
+    w->n_chain = rst_num;
+}
+
+// ------------------------------------------------------------------------------------------
+// read 9-mer table (restates build_hash_table_M2 src/cly.c:2168-2219).  The reference appends
+// each position to the tail of its bucket chain, so a bucket lists positions in ascending
+// order; we keep that order with head/next arrays filled from the highest position down.
+// Bucket key = low key_len bits of the 18-bit 9-mer; entries store pos+1, 0 terminates.
+// ------------------------------------------------------------------------------------------
+DSB_HD uint32_t dsb_kmer9(const uint8_t *s)
+{
+    uint32_t v = 0;
+    for (int i = 0; i < DSB_KMER9; i++) v = (v << 2) | (uint32_t)(s[i] & 3);
+    return v;
+}
+
+DSB_HDN int dsb_build_read_hash(DsbWork *w)
+{
+    int both_dir = 0;
+    for (uint32_t i = 0; i < w->n_chain; i++) {
+        both_dir |= (w->chains[i].direction == DSB_FORWARD) ? 0x2 : 0x1;
+        if (both_dir == 3) break;
+    }
+    const int q_len = (int)w->L;
+    int key_len = 10;
+    for (; key_len < 18; key_len++)
+        if ((int)(1u << key_len) >= q_len) break;
+    const uint32_t key_mask = (1u << key_len) - 1u;
+    const uint32_t n_pos = (uint32_t)(q_len - DSB_KMER9 + 1);
+    for (int c_dir = 2; c_dir >= 1; c_dir--) {
+        if ((c_dir & both_dir) == 0) continue;
+        const int strand = (c_dir == 2) ? 0 : 1;
+        const uint8_t *q = w->bin + (strand ? w->L : 0);
+        uint32_t *head = w->h_head[strand], *next = w->h_next[strand], *kmer = w->h_kmer[strand];
+#if defined(DSB_DEVICE_CODE)
+        const uint32_t lane = threadIdx.x & 31;
+        for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
+        for (uint32_t p = lane; p < n_pos; p += 32) kmer[p] = dsb_kmer9(q + p);
+        __syncwarp();
+        if (lane == 0) {
+            for (uint32_t p = n_pos; p-- > 0;) {
+                const uint32_t key = kmer[p] & key_mask;
+                next[p] = head[key];
+                head[key] = p + 1;
+            }
+        }
+        __syncwarp();
+#else
+        for (uint32_t i = 0; i <= key_mask; i++) head[i] = 0;
+        for (uint32_t p = n_pos; p-- > 0;) {
+            kmer[p] = dsb_kmer9(q + p);
+            const uint32_t key = kmer[p] & key_mask;
+            next[p] = head[key];
+            head[key] = p + 1;
+        }
+#endif
+    }
+    return key_len;
+}
+
+// ------------------------------------------------------------------------------------------
+// match blocks between a reference window and the read (restates MEM_search src/cly.c:1805-1813
+// and sdp_match :2330-2435).  q_str = strand base pointer; t_str = window with readable margins.
+// ------------------------------------------------------------------------------------------
+DSB_HD int dsb_run_len(const uint8_t *q, const uint8_t *t, bool forward, int max)
+{
+    int len = 0;
+    if (forward) for (; len < max && *q++ == *t++; len++) {}
+    else for (; len < max && *q-- == *t--; len++) {}
+    return len;
+}
+
+DSB_HD void dsb_push_sms(DsbWork *w, uint32_t t_pos, uint32_t q_pos, uint32_t len)
+{
+    if (w->n_sms >= w->cap_sms) { w->overflow = 1; return; }
+    DsbSms *p = w->sms + (w->n_sms++);
+    p->t_pos = t_pos; p->q_pos = q_pos; p->len = len;
+}
+
+DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8_t *q_str, const uint8_t *t_str,
+                           uint32_t t_len, int key_len, int strand, uint32_t t_st, bool is_forward)
+{
+    const uint32_t key_mask = (1u << key_len) - 1u;
+    const uint32_t t_kmer_num = t_len - DSB_KMER9 + 1;
+    const uint32_t *head = w->h_head[strand], *nxt = w->h_next[strand], *hk = w->h_kmer[strand];
+    w->st.sdp_win++;
+    if (is_forward) {
+        for (int i = 4; (uint32_t)i < t_kmer_num; i += 4) {
+            const uint8_t *c_t_str = t_str + i;
+            const uint32_t kmer = dsb_kmer9(c_t_str);
+            uint32_t node = head[kmer & key_mask];
+            while (node != 0) {
+                const uint32_t q_pos = node - 1;
+                if (hk[q_pos] == kmer && q_pos >= q_bg && q_pos <= q_ed) {
+                    const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, 4);
+                    if (back_len < 4 || i == 4) {
+                        uint32_t max_search = q_ed - q_pos - 1;
+                        max_search = DSB_MIN(max_search, t_len - (uint32_t)i - 1) + DSB_OVER_SEARCH;
+                        const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, (int)max_search);
+                        const int total_len = back_len + forward_len + 1;
+                        if (total_len >= 4)
+                            dsb_push_sms(w, (uint32_t)(i - back_len) + t_st, q_pos - (uint32_t)back_len, (uint32_t)total_len);
+                    }
+                }
+                node = nxt[q_pos];
+            }
+        }
+    } else {
+        for (int i = 4; (uint32_t)i < t_kmer_num; i += 4) {
+            const long c_off = (long)t_len - DSB_KMER9 - (long)i;       // c_t_str - t_str
+            const uint8_t *c_t_str = t_str + c_off;
+            const uint32_t kmer = dsb_kmer9(c_t_str);
+            uint32_t node = head[kmer & key_mask];
+            while (node != 0) {
+                const uint32_t q_pos = node - 1;
+                if (hk[q_pos] == kmer && q_pos >= q_bg && q_pos <= q_ed) {
+                    const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, 4);
+                    if (forward_len < 4 || i == 4) {
+                        uint32_t max_search = q_pos;
+                        max_search = (uint32_t)(DSB_MIN((long)max_search, c_off)) + DSB_OVER_SEARCH;
+                        const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, (int)max_search);
+                        const int total_len = back_len + forward_len + 1;
+                        if (total_len >= 4)
+                            dsb_push_sms(w, (uint32_t)(c_off - back_len + (long)t_st), q_pos - (uint32_t)back_len, (uint32_t)total_len);
+                    }
+                }
+                node = nxt[q_pos];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// diagonal hash of chain ends (restates sc_hash_idx src/cly.c:1686-1705) and chain merging
+// (combine_chain :1758-1803)
+// ------------------------------------------------------------------------------------------
+DSB_HD void dsb_sc_hash_idx(DsbWork *w)
+{
+    DsbScHash *h = w->sc_hash;
+    for (int i = 0; i < 256; i++) { h[i].next = 0; h[i].seed_ID = 0; h[i].s_or_e = 0; }
+    int con = 256;
+    for (uint32_t ci = 0; ci < w->n_chain; ci++) {
+        const DsbChain *c_h = w->chains + ci;
+        for (int i = 1; i >= 0; i--) {
+            uint16_t c_key = (uint16_t)(((i == 1) ? (c_h->t_st - c_h->q_st) : (c_h->t_ed - c_h->q_ed)) & 0xff);
+            while (h[c_key].next != 0) c_key = h[c_key].next;
+            h[c_key].seed_ID = (uint16_t)((ci + 1) & 0x7fff);
+            h[c_key].s_or_e = (uint8_t)i;
+            h[c_key].next = (uint16_t)con;
+            h[con++].next = 0;
+        }
+    }
+}
+
+// returns the index of the absorbed chain or -1
+DSB_HD int dsb_combine_chain(DsbWork *w, int chain_ID, int dis, bool isleft, int c_q_pos)
+{
+    const DsbScHash *h = w->sc_hash;
+    uint16_t key = (uint16_t)(dis & 0xff);
+    DsbChain *c_h = w->chains + chain_ID;
+    while (h[key].next != 0) {
+        const uint16_t seed_ID = h[key].seed_ID;
+        DsbChain *c = w->chains + ((int)seed_ID - 1);
+        const int dis_con = (int)((isleft) ? (c->t_ed - c->q_ed) : (c->t_st - c->q_st));
+        const int q_pos_con = (int)((!isleft) ? (c->q_st) : (c->q_ed - DSB_KMER9));
+        if (dis == dis_con && c_h != c && (int)isleft != (int)h[key].s_or_e &&
+            DSB_ABS_U(c_q_pos, q_pos_con) < 8 && c_h->ref_ID == c->ref_ID &&
+            c_h->direction == c->direction && c->sum_score != 0 && (int)seed_ID - 1 > chain_ID) {
+            c_h->sum_score += c->sum_score;
+            c_h->anchor_number += c->anchor_number;
+            c_h->indel += c->indel;
+            c_h->q_st = DSB_MIN(c_h->q_st, c->q_st);
+            c_h->t_st = DSB_MIN(c_h->t_st, c->t_st);
+            c_h->q_ed = DSB_MAX(c_h->q_ed, c->q_ed);
+            c_h->t_ed = DSB_MAX(c_h->t_ed, c->t_ed);
+            c->sum_score = 0;
+            c->t_st = c->t_ed = c->q_st = c->q_ed = 0;
+            return (int)seed_ID - 1;
+        }
+        key = h[key].next;
+    }
+    return -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// chain re-scoring by sparse DP over match blocks (restates sdp_middle_M2 src/cly.c:2439-2525,
+// sdp_right_M2 :2527-2672, sdp_left_M2 :2674-2814, get_score_M2 :2816-2844)
+//
+// Bytes the reference reads without having written them (window tails on its stack,
+// src/cly.c:2467,2537,2683) are defined here as 0xFE = "never equal to a base", which is what
+// the reference source does when built with -ftrivial-auto-var-init=pattern (oracle/Makefile
+// target ref_pinit); DESIGN.md explains how reads that depend on those bytes are identified.
+// ------------------------------------------------------------------------------------------
+#define DSB_UNINIT 0xFE
+
+DSB_HD void dsb_fill(uint8_t *p, uint32_t n, uint8_t v)
+{
+#if defined(DSB_DEVICE_CODE)
+    for (uint32_t i = threadIdx.x & 31; i < n; i += 32) p[i] = v;
+    __syncwarp();
+#else
+    for (uint32_t i = 0; i < n; i++) p[i] = v;
+#endif
+}
+
+DSB_HDN int dsb_sdp_middle(DsbWork *w, int32_t c_a, const uint8_t *q_str, int strand, int key_len)
+{
+    const DsbIndexView *ix = w->ix;
+    const DsbAnchor *A = w->anchors;
+    int score = 10000;
+    const uint64_t t_offset = ix->ref_off[A[c_a].ref_ID];
+    while (c_a != -1) {
+        const int32_t pre_a = A[c_a].pre;
+        if (pre_a != -1) {
+            const int pre_mch = A[pre_a].mtch_len;
+            const int pre_refoffset = (int)(A[pre_a].ref_offset - 3);
+            const int total_ref_len = (int)(A[c_a].ref_offset - (uint32_t)(pre_refoffset + pre_mch) + 3);
+            w->n_sms = 0;
+            dsb_push_sms(w, A[pre_a].ref_offset, A[pre_a].index_in_read, (uint32_t)(A[pre_a].mtch_len - DSB_KMER9 + 1));
+            w->sms[0].score = (uint32_t)score;
+            if (total_ref_len > 12) {
+                if (total_ref_len >= 2000) { w->overflow = 2; return 0; }    // reference: xassert -> abort (src/cly.c:2468)
+                uint8_t *ref = w->ref_mid;
+                const uint64_t ref_offset = (uint64_t)(int64_t)(pre_refoffset) + t_offset + (uint64_t)(int64_t)pre_mch;
+                dsb_get_ref(w, ref, ref_offset, (uint32_t)total_ref_len, true);
+                dsb_fill(ref + total_ref_len, 64, DSB_UNINIT);
+                dsb_sdp_match(w, A[pre_a].index_in_read + (uint32_t)pre_mch - 8, A[c_a].index_in_read - 1, q_str, ref,
+                              (uint32_t)total_ref_len, key_len, strand, (uint32_t)(pre_refoffset + pre_mch), true);
+            }
+            dsb_push_sms(w, A[c_a].ref_offset, A[c_a].index_in_read, (uint32_t)(A[c_a].mtch_len - DSB_KMER9 + 1));
+            if (w->n_sms > 1) {
+                DsbSms *S = w->sms;
+                for (uint32_t ci = 1; ci < w->n_sms; ci++) {
+                    DsbSms *c_spd = S + ci;
+                    int max_score = (int)c_spd->len;
+                    const uint32_t max_q = c_spd->q_pos + DSB_SMS_OVERLAP;
+                    const uint32_t max_t = c_spd->t_pos + DSB_SMS_OVERLAP;
+                    for (int32_t pi = (int32_t)ci - 1; pi >= 0; pi--) {
+                        const DsbSms *p = S + pi;
+                        const int pre_q_ed = (int)(p->q_pos + p->len + DSB_KMER9 - 1);
+                        const int pre_t_ed = (int)(p->t_pos + p->len + DSB_KMER9 - 1);
+                        if ((uint32_t)pre_q_ed > max_q) continue;
+                        if ((uint32_t)pre_t_ed > max_t) continue;
+                        const int indel = (int)(p->q_pos - p->t_pos - (max_q - max_t));
+                        const int ABS_indel = DSB_ABS(indel);
+                        if (ABS_indel > 200) continue;
+                        int new_score = (int)(p->score + c_spd->len - (uint32_t)(ABS_indel >> 3));
+                        if ((uint32_t)pre_q_ed > c_spd->q_pos || (uint32_t)pre_t_ed > c_spd->t_pos) {
+                            const int overlap_q = (int)((uint32_t)pre_q_ed - c_spd->q_pos);
+                            const int overlap_t = (int)((uint32_t)pre_t_ed - c_spd->t_pos);
+                            new_score -= DSB_MAX(overlap_q, overlap_t);
+                        }
+                        max_score = DSB_MAX(max_score, new_score);
+                    }
+                    score = DSB_MAX(max_score, score);
+                    c_spd->score = (uint32_t)max_score;
+                }
+            }
+        } else
+            score += A[c_a].mtch_len - DSB_KMER9 + 1;
+        c_a = pre_a;
+    }
+    return score - 10000;
+}
+
+DSB_HDN int dsb_sdp_right(DsbWork *w, const uint8_t *q_str, int strand, int key_len, int chain_ID, uint32_t l_read,
+                          int score_ori)
+{
+    const DsbIndexView *ix = w->ix;
+    score_ori += 10000;
+    int total_max_score = score_ori;
+    int max_sms_id = 0;
+    DsbChain *c_h = w->chains + chain_ID;
+    w->n_sms = 0;
+    uint8_t *ref = w->ref_ext;
+    dsb_fill(ref, 1000, DSB_UNINIT);                                   // uint8_t ref[1000] (src/cly.c:2537)
+    dsb_push_sms(w, c_h->t_ed, c_h->q_ed, (uint32_t)(1 - DSB_KMER9));
+    w->sms[0].score = (uint32_t)score_ori;
+    uint32_t current_sms = 1;
+    const uint64_t t_offset_global = ix->ref_off[c_h->ref_ID];
+    const uint64_t t_length = ix->ref_len[c_h->ref_ID];
+    uint32_t c_t_offset = c_h->t_ed - 3;
+    int last_search = 0;
+    while (1) {
+        if (w->overflow) break;
+        if (w->n_sms == current_sms) {
+            const uint32_t next_step = (uint32_t)(t_length - c_t_offset);
+            if (next_step < DSB_MIN_SCORE_MEM) break;
+            uint32_t max_search_ref;
+            if (l_read - c_h->q_ed < 600) {
+                if (last_search) break;
+                last_search = 1;
+                max_search_ref = l_read - c_h->q_ed + 60;
+            } else
+                max_search_ref = (uint32_t)(t_length - c_t_offset);
+            max_search_ref = DSB_MIN(600u, max_search_ref);
+            dsb_get_ref(w, ref, c_t_offset + t_offset_global, max_search_ref + DSB_OVER_SEARCH, true);
+            int search_q_ed = (int)w->sms[max_sms_id].q_pos + 1000;
+            search_q_ed = (int)DSB_MIN((uint32_t)search_q_ed, l_read);         // MIN(int, uint32): unsigned
+            const int search_q_st = (int)DSB_MAX((uint32_t)(search_q_ed - 2000), c_h->q_st - 8);   // MAX(int, uint32): unsigned
+            dsb_sdp_match(w, (uint32_t)search_q_st, (uint32_t)search_q_ed, q_str, ref, max_search_ref, key_len, strand,
+                          c_t_offset, true);
+            c_t_offset += max_search_ref - DSB_KMER9 - 3;
+            if (w->n_sms == current_sms) break;
+            if (w->sms[current_sms].t_pos > w->sms[max_sms_id].t_pos + 1000) break;
+        }
+        DsbSms *c_sms = w->sms + current_sms++;
+        int max_score = (int)c_sms->len;
+        const uint32_t max_pre_q = c_sms->q_pos + DSB_SMS_OVERLAP;
+        const uint32_t max_pre_t = c_sms->t_pos + DSB_SMS_OVERLAP;
+        for (int32_t pi = (int32_t)current_sms - 2; pi >= 0; pi--) {
+            const DsbSms *p = w->sms + pi;
+            const int pre_q_ed = (int)(p->q_pos + p->len + DSB_KMER9 - 1);
+            const int pre_t_ed = (int)(p->t_pos + p->len + DSB_KMER9 - 1);
+            if ((uint32_t)pre_q_ed > max_pre_q) continue;
+            if ((uint32_t)pre_t_ed > max_pre_t) continue;
+            if (p->t_pos + 600 < max_pre_t) break;
+            const int indel = (int)(p->q_pos - p->t_pos - (max_pre_q - max_pre_t));
+            const int ABS_indel = DSB_ABS(indel);
+            if (ABS_indel > 200) continue;
+            int new_score = (int)(p->score + c_sms->len - (uint32_t)(ABS_indel >> 3));
+            if ((uint32_t)pre_q_ed > c_sms->q_pos || (uint32_t)pre_t_ed > c_sms->t_pos) {
+                const int overlap_q = (int)((uint32_t)pre_q_ed - c_sms->q_pos);
+                const int overlap_t = (int)((uint32_t)pre_t_ed - c_sms->t_pos);
+                new_score -= DSB_MAX(overlap_q, overlap_t);
+            }
+            max_score = DSB_MAX(max_score, new_score);
+        }
+        c_sms->score = (uint32_t)max_score;
+        if (c_sms->len >= 8) {
+            const uint32_t cs_len = c_sms->len;     // c_sms is invalidated by the nested sdp_middle
+            const int comb = dsb_combine_chain(w, chain_ID, (int)(c_sms->t_pos - c_sms->q_pos), false, (int)c_sms->q_pos);
+            if (comb >= 0) {
+                total_max_score = (int)((uint32_t)DSB_MAX(score_ori, max_score) - cs_len +
+                                        (uint32_t)dsb_sdp_middle(w, w->chains[comb].cur, q_str, strand, key_len));
+                score_ori = total_max_score;
+                max_sms_id = 0;
+                w->n_sms = 0;
+                dsb_push_sms(w, c_h->t_ed, c_h->q_ed, (uint32_t)(-DSB_KMER9));
+                w->sms[0].score = (uint32_t)total_max_score;
+                current_sms = 1;
+                c_t_offset = c_h->t_ed;
+                continue;
+            }
+        }
+        if (total_max_score < max_score) {
+            total_max_score = max_score;
+            max_sms_id = (int)current_sms - 1;
+        }
+        if (c_sms->t_pos > w->sms[max_sms_id].t_pos + 1000) break;
+    }
+    c_h->q_ed = w->sms[max_sms_id].q_pos + w->sms[max_sms_id].len + DSB_KMER9;
+    c_h->t_ed = w->sms[max_sms_id].t_pos + w->sms[max_sms_id].len + DSB_KMER9;
+    return total_max_score - 10000;
+}
+
+DSB_HDN int dsb_sdp_left(DsbWork *w, const uint8_t *q_str, int strand, int key_len, int chain_ID, uint32_t l_read,
+                         int score_ori)
+{
+    const DsbIndexView *ix = w->ix;
+    (void)l_read;
+    score_ori += 10000;
+    int total_max_score = score_ori;
+    int max_sms_id = 0;
+    DsbChain *c_h = w->chains + chain_ID;
+    w->n_sms = 0;
+    uint8_t *ref = w->ref_ext;
+    dsb_fill(ref, 1000, DSB_UNINIT);                                   // uint8_t ref[1000] (src/cly.c:2683)
+    dsb_push_sms(w, c_h->t_st, c_h->q_st, DSB_UNINIT * 0x01010101u);   // len is never written nor read there
+    w->sms[0].score = (uint32_t)score_ori;
+    uint32_t current_sms = 1;
+    const uint64_t t_offset_global = ix->ref_off[c_h->ref_ID];
+    uint32_t c_t_offset = c_h->t_st + 3;
+    int last_search = 0;
+    while (1) {
+        if (w->overflow) break;
+        if (w->n_sms == current_sms) {
+            const uint32_t next_step = c_t_offset;
+            if (next_step < DSB_MIN_SCORE_MEM) break;
+            uint32_t max_search_ref;
+            if (c_h->q_st < 600) {
+                if (last_search) break;
+                last_search = 1;
+                max_search_ref = c_h->q_st + 60;
+            } else
+                max_search_ref = c_t_offset;
+            max_search_ref = DSB_MIN(600u, max_search_ref);
+            if (t_offset_global == 0 && c_t_offset < DSB_OVER_SEARCH + max_search_ref)   // "bug" branch, SURVEY.md Q24
+                dsb_get_ref(w, ref, c_t_offset + t_offset_global - max_search_ref, max_search_ref, true);
+            else
+                dsb_get_ref(w, ref, c_t_offset + t_offset_global - max_search_ref - DSB_OVER_SEARCH,
+                            max_search_ref + DSB_OVER_SEARCH, true);
+            int search_q_st = (int)w->sms[max_sms_id].q_pos - 1000;
+            search_q_st = DSB_MAX(search_q_st, 0);
+            const int search_q_ed = (int)DSB_MIN((uint32_t)(search_q_st + 2000), c_h->q_st - 1);   // MIN(int, uint32): unsigned
+            dsb_sdp_match(w, (uint32_t)search_q_st, (uint32_t)search_q_ed, q_str, ref + DSB_OVER_SEARCH, max_search_ref,
+                          key_len, strand, c_t_offset - max_search_ref, false);
+            c_t_offset = c_t_offset - max_search_ref + DSB_KMER9 + 3;
+            if (w->n_sms == current_sms) break;
+            if (w->sms[current_sms].t_pos + 1000 < w->sms[max_sms_id].t_pos) break;
+        }
+        DsbSms *c_sms = w->sms + current_sms++;
+        int max_score = (int)c_sms->len;
+        const uint32_t min_pre_q = c_sms->q_pos + c_sms->len - DSB_SMS_OVERLAP + DSB_KMER9 - 1;
+        const uint32_t min_pre_t = c_sms->t_pos + c_sms->len - DSB_SMS_OVERLAP + DSB_KMER9 - 1;
+        for (int32_t pi = (int32_t)current_sms - 2; pi >= 0; pi--) {
+            const DsbSms *p = w->sms + pi;
+            if (p->q_pos < min_pre_q) continue;
+            if (p->t_pos < min_pre_t) continue;
+            if (min_pre_t + 600 < p->t_pos) break;
+            const int indel = (int)(p->q_pos - p->t_pos - (min_pre_q - min_pre_t));
+            const int ABS_indel = DSB_ABS(indel);
+            if (ABS_indel > 200) continue;
+            int new_score = (int)(p->score + c_sms->len - (uint32_t)(ABS_indel >> 3));
+            if (min_pre_q + DSB_SMS_OVERLAP > p->q_pos || min_pre_t + DSB_SMS_OVERLAP > p->t_pos) {
+                const int overlap_q = (int)(min_pre_q + DSB_SMS_OVERLAP - p->q_pos);
+                const int overlap_t = (int)(min_pre_t + DSB_SMS_OVERLAP - p->t_pos);
+                new_score -= DSB_MAX(overlap_q, overlap_t);
+            }
+            max_score = DSB_MAX(max_score, new_score);
+        }
+        c_sms->score = (uint32_t)max_score;
+        if (c_sms->len >= 8) {
+            const uint32_t cs_len = c_sms->len;
+            const int comb = dsb_combine_chain(w, chain_ID, (int)(c_sms->t_pos - c_sms->q_pos), true,
+                                               (int)(c_sms->q_pos + c_sms->len));
+            if (comb >= 0) {
+                total_max_score = (int)((uint32_t)DSB_MAX(score_ori, max_score) - cs_len +
+                                        (uint32_t)dsb_sdp_middle(w, w->chains[comb].cur, q_str, strand, key_len));
+                score_ori = total_max_score;
+                max_sms_id = 0;
+                w->n_sms = 0;
+                dsb_push_sms(w, c_h->t_st, c_h->q_st, DSB_UNINIT * 0x01010101u);
+                w->sms[0].score = (uint32_t)total_max_score;
+                current_sms = 1;
+                c_t_offset = c_h->t_st;
+                continue;
+            }
+        }
+        if (total_max_score < max_score) {
+            total_max_score = max_score;
+            max_sms_id = (int)current_sms - 1;
+        }
+        if (c_sms->t_pos + 1000 < w->sms[max_sms_id].t_pos) break;
+    }
+    c_h->q_st = w->sms[max_sms_id].q_pos;
+    c_h->t_st = w->sms[max_sms_id].t_pos;
+    return total_max_score - 10000;
+}
+
+DSB_HDN void dsb_get_score(DsbWork *w)
+{
+    const int key_len = dsb_build_read_hash(w);
+    for (uint32_t i = 0; i < w->n_chain; i++) {
+        if (w->chains[i].sum_score == 0) continue;
+        const int strand = (w->chains[i].direction == DSB_FORWARD) ? 0 : 1;
+        const uint8_t *q_str = w->bin + (strand ? w->L : 0);
+        int score = dsb_sdp_middle(w, w->chains[i].cur, q_str, strand, key_len);
+        score = dsb_sdp_right(w, q_str, strand, key_len, (int)i, w->L, score);
+        score = dsb_sdp_left(w, q_str, strand, key_len, (int)i, w->L, score);
+        w->chains[i].sum_score = (uint32_t)score;
+        if (w->overflow) return;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// filter / merge / rank (restates delete_small_score_rst src/cly.c:2878-2988 with its
+// comparators chain_cmp_by_pos :2848-2865 and chain_cmp_by_MEM_score :53-63)
+// ------------------------------------------------------------------------------------------
+DSB_HDN void dsb_delete_small_score_rst(DsbWork *w)
+{
+    if (w->n_chain == 0) return;
+    if (w->n_chain > 200) {
+        uint32_t rst_num = 200;
+        for (; rst_num < w->n_chain && w->chains[rst_num].sum_score > 50; rst_num++) {}
+        w->n_chain = rst_num;
+    }
+    w->n_chain = DSB_MIN(400u, w->n_chain);
+    const uint32_t l_read = w->L;
+    dsb_sc_hash_idx(w);
+    dsb_get_score(w);
+    if (w->overflow) return;
+    const uint32_t n = w->n_chain;
+    DsbChain *C = w->chains;
+    if (n > 1) {
+        const DsbChain *CC = C;
+        dsb_msort_idx(w->sort_a, w->sort_b, n, [CC](uint32_t i, uint32_t j) -> int {
+            const DsbChain *a = CC + i, *b = CC + j;
+            if (a->ref_ID > b->ref_ID) return 1;
+            if (a->ref_ID < b->ref_ID) return -1;
+            if (a->t_st > b->t_st) return 1;
+            if (a->t_st < b->t_st) return -1;
+            if (a->sum_score < b->sum_score) return 1;
+            if (a->sum_score > b->sum_score) return -1;
+            return 0;
+        });
+        dsb_apply_chain_perm(w, n);
+    }
+    for (uint32_t ci = 0; ci + 1 < n; ci++) {
+        DsbChain *c_c = C + ci;
+        if (c_c->sum_score == 0) continue;
+        for (uint32_t ni = ci + 1; ni < n; ni++) {
+            DsbChain *next_c = C + ni;
+            if (c_c->ref_ID == next_c->ref_ID) {
+                if (c_c->direction != next_c->direction) continue;
+                if (next_c->sum_score == 0) continue;
+                if (next_c->t_st < c_c->t_st + 5 && next_c->q_st < c_c->q_st + 5 && next_c->sum_score < c_c->sum_score + 5) {
+                    next_c->sum_score = 0;
+                    next_c->q_ed = next_c->q_st;
+                    next_c->t_ed = next_c->t_st;
+                    continue;
+                }
+                const int dis_t = (int)(next_c->t_st - c_c->t_ed);
+                const int dis_q = (int)(next_c->q_st - c_c->q_ed);
+                const int dis_t_q = DSB_ABS(dis_t - dis_q);
+                if ((dis_t > -20 && dis_t < 1000 && dis_q > -20 && dis_q < 1000) && dis_t_q < 200) {
+                    c_c->t_ed = DSB_MAX(c_c->t_ed, next_c->t_ed);
+                    c_c->q_ed = DSB_MAX(c_c->q_ed, next_c->q_ed);
+                    c_c->sum_score += next_c->sum_score;
+                    next_c->sum_score = 0;
+                    next_c->q_ed = next_c->q_st;
+                    next_c->t_ed = next_c->t_st;
+                }
+            } else
+                break;
+        }
+    }
+    // buff->max_read_l is a running maximum over the worker's history; the host evaluates it in
+    // read order and ships the outcome of `max_read_l < 510` with the read
+    if (w->is_2g) {
+        for (uint32_t ci = 0; ci < n; ci++) {
+            const int score = (int)(C[ci].sum_score + ((C[ci].q_ed - C[ci].q_st) >> 5));
+            if (score < 26) C[ci].sum_score = 0;
+        }
+    } else if (l_read < 310) {
+        for (uint32_t ci = 0; ci < n; ci++) {
+            const int score = (int)(C[ci].sum_score + ((C[ci].q_ed - C[ci].q_st) >> 5));
+            if (score < 30) C[ci].sum_score = 0;
+        }
+    } else {
+        const DsbIndexView *ix = w->ix;
+        for (uint32_t ci = 0; ci < n; ci++) {
+            const int score = (int)(C[ci].sum_score + ((C[ci].q_ed - C[ci].q_st) >> 5));
+            // `q_ed - q_st < filter_min_length` compares uint32 with int: unsigned
+            if (score < ix->filter_min_score_lv3 &&
+                ((C[ci].q_ed - C[ci].q_st) < (uint32_t)ix->filter_min_length || score < ix->filter_min_score))
+                C[ci].sum_score = 0;
+        }
+    }
+    if (n > 1) {
+        const DsbChain *CC = C;
+        dsb_msort_idx(w->sort_a, w->sort_b, n, [CC](uint32_t i, uint32_t j) -> int {
+            const DsbChain *a = CC + i, *b = CC + j;
+            const int score_a = (int)(a->sum_score << 5);
+            const int score_b = (int)(b->sum_score << 5);
+            if (score_a < score_b) return 1;
+            if (score_a > score_b) return -1;
+            return (int)(a->sum_score % 2);
+        });
+        dsb_apply_chain_perm(w, n);
+    }
+    uint32_t k = 0;
+    for (; k < n; k++)
+        if (C[k].sum_score == 0) break;
+    w->n_chain = k;
+}
+
+// ------------------------------------------------------------------------------------------
+// PRIMARY / SECONDARY / SUPPLEMENTARY (restates detect_primary src/cly.c:2990-3053)
+// ------------------------------------------------------------------------------------------
+DSB_HDN void dsb_detect_primary(DsbWork *w)
+{
+    const uint32_t n_hit = w->n_chain;
+    if (n_hit == 0) return;
+    DsbChain *hit = w->chains;
+    const uint32_t read_len = w->L;
+    // primary_v[800] / primary_v_idx[800] of the reference live in the (now free) sort buffers
+    int32_t *primary_v = (int32_t *)w->sort_a;
+    uint8_t *primary_v_idx = (uint8_t *)w->sort_b;
+    int n_primary_v = 1;
+    hit[0].pri_index = primary_v_idx[0] = 0;
+    primary_v[0] = 0;
+    hit[0].primary = DSB_PRIMARY;
+    for (uint32_t i = 0; i < n_hit; i++)
+        if (hit[i].q_st > 4294960000u) hit[i].q_st = 0;
+    for (uint32_t ci = 1; ci < n_hit; ci++) {
+        DsbChain *c_hit = hit + ci;
+        bool overlap = false;
+        for (int i = 0; i < n_primary_v; i++) {
+            const DsbChain *P = hit + primary_v[i];
+            int primary_st, primary_ed;
+            if (P->direction == c_hit->direction) {
+                primary_st = (int)P->q_st;
+                primary_ed = (int)P->q_ed;
+            } else {
+                primary_st = (int)(read_len - P->q_ed);
+                primary_ed = (int)(read_len - P->q_st);
+            }
+            const uint32_t overlap_st = DSB_MAX(c_hit->q_st, (uint32_t)primary_st);   // MAX(uint32,int): unsigned
+            const uint32_t overlap_ed = DSB_MIN(c_hit->q_ed, (uint32_t)primary_ed);
+            if ((overlap_st < overlap_ed) && (((overlap_ed - overlap_st) << 1) >= (c_hit->q_ed - c_hit->q_st)))
+                overlap = true;
+            if (overlap) {
+                c_hit->primary = DSB_SECONDARY;
+                c_hit->pri_index = ++primary_v_idx[i];
+                const int max_gap = (int)DSB_MAX((P->sum_score >> 6), 5u);
+                if (c_hit->sum_score + (uint32_t)max_gap > P->sum_score) c_hit->pri_index = 1;
+                if (primary_v_idx[i] == 255) primary_v_idx[i] = 254;
+                break;
+            }
+        }
+        if (!overlap) {
+            c_hit->primary = DSB_SUPPLEMENTARY;
+            c_hit->pri_index = primary_v_idx[n_primary_v] = 0;
+            primary_v[n_primary_v++] = (int32_t)ci;
+            if (n_primary_v > 750) n_primary_v = 750;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// per-read driver (restates getIsland's strand ordering src/cly.c:1256-1261 and classify_seq
+// src/cly.c:3059-3127).  On entry w->bin / w->exist / arenas are set; on exit w->chains[0..n_chain)
+// are the reported hits in output order.
+// ------------------------------------------------------------------------------------------
+DSB_HDN void dsb_classify_read(DsbWork *w)
+{
+    w->n_anchor = 0;
+    w->n_chain = 0;
+    w->fast_classify = 1;
+    if (w->L < 40) return;                                                  // MIN_READ_LEN
+    dsb_islands(w, 0);
+    dsb_islands(w, 1);
+    // search_dir[0] = forward unless the reverse strand scores strictly higher
+    int dir0 = 0, dir1 = 1;
+    if (w->total_score[0] < w->total_score[1]) { dir0 = 1; dir1 = 0; }
+    const uint32_t s0 = w->total_score[dir0], s1 = w->total_score[dir1];
+    const bool both_direction = ((s0 - s1) <= (s0 >> 3));
+    dsb_fast_classify(w, dir0);
+    if (both_direction) dsb_fast_classify(w, dir1);
+    dsb_resolve_tree(w);
+    bool run_slow_mode = false;
+    if (w->n_chain <= 0)
+        run_slow_mode = true;
+    else if (w->chains[0].anchor_number < 5) {                              // super_repeat is always 0
+        run_slow_mode = true;
+        if (w->L <= 300 && w->chains[0].sum_score > 200) run_slow_mode = false;
+    }
+    if (run_slow_mode && !w->overflow) {
+        w->st.slow++;
+        w->n_anchor = 0;
+        dsb_slow_classify(w, dir0);
+        dsb_resolve_tree(w);
+        if (both_direction || w->n_chain <= 0 || (w->chains[0].anchor_number < 5)) {
+            dsb_slow_classify(w, dir1);                                     // appends
+            dsb_resolve_tree(w);
+        }
+    }
+    if (w->overflow) return;
+    dsb_delete_small_score_rst(w);
+    if (w->overflow) return;
+    dsb_detect_primary(w);
+}

@@ -1,0 +1,207 @@
+/* dsb_fastq.c -- FASTQ / FASTA record reader with the semantics of the reference's kseq
+ * (reference src/lib/utils.c:841-977): the header starts at the next '>' or '@' byte, the name
+ * ends at the first isspace() byte, sequence lines are concatenated until a line starts with
+ * '>', '+' or '@', the quality is read until it is at least as long as the sequence.
+ * Input is a gzip-transparent stream (file) or a memory block (the API's in-memory mode, which
+ * the reference round-trips through tmpfile()+gzdopen(), src/cly_mt.c:1048-1062).
+ */
+#include "dsb_host.h"
+#include <ctype.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+#include <zlib.h>
+
+#define FQ_BUFSIZE (1 << 20)
+
+struct dsb_fq {
+    gzFile gz;                 /* stream mode */
+    FILE *tmp;                 /* gzip-in-memory goes through a temp file like the reference */
+    const unsigned char *mem;  /* memory mode */
+    uint64_t mem_n, mem_pos;
+    unsigned char *buf;
+    int begin, end, is_eof;
+    int last_char;
+    /* pending record when the caller's buffer was too small */
+    int have_pending;
+    dsb_strbuf p_name, p_seq, p_qual;
+    int p_is_fastq;
+    int64_t p_ret;
+};
+
+static int fq_fill(dsb_fq *f)
+{
+    f->begin = 0;
+    if (f->gz) {
+        f->end = gzread(f->gz, f->buf, FQ_BUFSIZE);
+        if (f->end < 0) f->end = 0;
+    } else {
+        uint64_t left = f->mem_n - f->mem_pos;
+        int n = (left > FQ_BUFSIZE) ? FQ_BUFSIZE : (int)left;
+        memcpy(f->buf, f->mem + f->mem_pos, (size_t)n);
+        f->mem_pos += (uint64_t)n;
+        f->end = n;
+    }
+    if (f->end < FQ_BUFSIZE) f->is_eof = 1;
+    return f->end;
+}
+
+static inline int fq_getc(dsb_fq *f)
+{
+    if (f->is_eof && f->begin >= f->end) return -1;
+    if (f->begin >= f->end) {
+        if (fq_fill(f) == 0) return -1;
+    }
+    return (int)f->buf[f->begin++];
+}
+
+static void sb_need(dsb_strbuf *s, size_t extra)
+{
+    if (s->m - s->l < extra + 1) {
+        size_t m = s->l + extra + 1;
+        m = m + (m >> 1) + 64;
+        s->s = (char *)dsb_xrealloc(s->s, m);
+        s->m = m;
+    }
+}
+
+/* delimiter: 0 = isspace, otherwise the byte.  returns length or -1 at end of input */
+static int64_t fq_getuntil(dsb_fq *f, int delimiter, dsb_strbuf *str, int *dret, int append)
+{
+    if (dret) *dret = 0;
+    if (!append) str->l = 0;
+    if (f->begin >= f->end && f->is_eof) return -1;
+    for (;;) {
+        int i;
+        if (f->begin >= f->end) {
+            if (!f->is_eof) {
+                if (fq_fill(f) == 0) break;
+            } else
+                break;
+        }
+        if (delimiter) {
+            unsigned char *p = (unsigned char *)memchr(f->buf + f->begin, delimiter, (size_t)(f->end - f->begin));
+            i = p ? (int)(p - f->buf) : f->end;
+        } else {
+            for (i = f->begin; i < f->end; ++i)
+                if (isspace(f->buf[i])) break;
+        }
+        sb_need(str, (size_t)(i - f->begin));
+        memcpy(str->s + str->l, f->buf + f->begin, (size_t)(i - f->begin));
+        str->l += (size_t)(i - f->begin);
+        f->begin = i + 1;
+        if (i < f->end) {
+            if (dret) *dret = f->buf[i];
+            break;
+        }
+    }
+    sb_need(str, 0);
+    str->s[str->l] = 0;
+    return (int64_t)str->l;
+}
+
+static dsb_fq *fq_new(void)
+{
+    dsb_fq *f = (dsb_fq *)dsb_xcalloc(1, sizeof *f);
+    f->buf = (unsigned char *)dsb_xmalloc(FQ_BUFSIZE);
+    return f;
+}
+
+dsb_fq *dsb_fq_open_path(const char *path)
+{
+    dsb_fq *f = fq_new();
+    f->gz = gzopen(path, "r");
+    if (!f->gz) dsb_fatal("cannot open reads file %s", path);
+    gzbuffer(f->gz, 1 << 20);
+    return f;
+}
+
+dsb_fq *dsb_fq_open_mem(const char *buf, uint64_t n)
+{
+    dsb_fq *f = fq_new();
+    if (n >= 2 && (unsigned char)buf[0] == 0x1f && (unsigned char)buf[1] == 0x8b) {
+        f->tmp = tmpfile();
+        if (!f->tmp) dsb_fatal("tmpfile() failed");
+        if (fwrite(buf, 1, n, f->tmp) != n) dsb_fatal("short write to temp file");
+        rewind(f->tmp);
+        f->gz = gzdopen(dup(fileno(f->tmp)), "r");
+        if (!f->gz) dsb_fatal("gzdopen failed");
+    } else {
+        f->mem = (const unsigned char *)buf;
+        f->mem_n = n;
+    }
+    return f;
+}
+
+void dsb_fq_close(dsb_fq *f)
+{
+    if (!f) return;
+    if (f->gz) gzclose(f->gz);
+    if (f->tmp) fclose(f->tmp);
+    free(f->buf);
+    free(f->p_name.s);
+    free(f->p_seq.s);
+    free(f->p_qual.s);
+    free(f);
+}
+
+/* kseq_read (src/lib/utils.c:939-977) into the pending buffers */
+static int64_t fq_read_record(dsb_fq *f)
+{
+    int c;
+    f->p_is_fastq = 0;
+    if (f->last_char == 0) {
+        while ((c = fq_getc(f)) != -1 && c != '>' && c != '@') {}
+        if (c == -1) return -1;
+        f->last_char = c;
+    }
+    f->p_seq.l = f->p_qual.l = 0;
+    if (fq_getuntil(f, 0, &f->p_name, &c, 0) < 0) return -1;
+    if (c != '\n') {
+        /* comment: skipped (the reference stores it but never prints it) */
+        dsb_strbuf junk = {NULL, 0, 0};
+        fq_getuntil(f, '\n', &junk, NULL, 0);
+        free(junk.s);
+    }
+    while ((c = fq_getc(f)) != -1 && c != '>' && c != '+' && c != '@') {
+        sb_need(&f->p_seq, 1);
+        f->p_seq.s[f->p_seq.l++] = (char)c;
+        fq_getuntil(f, '\n', &f->p_seq, NULL, 1);
+    }
+    if (c == '>' || c == '@') f->last_char = c;
+    sb_need(&f->p_seq, 0);
+    f->p_seq.s[f->p_seq.l] = 0;
+    if (c != '+') return (int64_t)f->p_seq.l;         /* FASTA */
+    f->p_is_fastq = 1;
+    while ((c = fq_getc(f)) != -1 && c != '\n') {}
+    if (c == -1) return -2;
+    while (fq_getuntil(f, '\n', &f->p_qual, NULL, 1) >= 0 && f->p_qual.l < f->p_seq.l) {}
+    f->last_char = 0;
+    if (f->p_seq.l != f->p_qual.l) return -2;
+    return (int64_t)f->p_seq.l;
+}
+
+int64_t dsb_fq_next(dsb_fq *f, dsb_strbuf *name, char *seq_out, uint64_t cap, dsb_strbuf *qual, int *is_fastq)
+{
+    if (!f->have_pending) {
+        f->p_ret = fq_read_record(f);
+        if (f->p_ret < 0) return f->p_ret;
+        f->have_pending = 1;
+    }
+    if ((uint64_t)f->p_seq.l > cap) return -3;
+    f->have_pending = 0;
+    name->l = 0;
+    sb_need(name, f->p_name.l);
+    memcpy(name->s, f->p_name.s, f->p_name.l + 1);
+    name->l = f->p_name.l;
+    memcpy(seq_out, f->p_seq.s, f->p_seq.l);
+    if (qual) {
+        qual->l = 0;
+        sb_need(qual, f->p_qual.l);
+        if (f->p_is_fastq) memcpy(qual->s, f->p_qual.s, f->p_qual.l);
+        qual->l = f->p_is_fastq ? f->p_qual.l : 0;
+        qual->s[qual->l] = 0;
+    }
+    if (is_fastq) *is_fastq = f->p_is_fastq;
+    return f->p_ret;
+}
