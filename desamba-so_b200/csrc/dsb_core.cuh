@@ -271,6 +271,13 @@ DSB_HD void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t 
     const DsbIndexView *ix = w->ix;
     w->st.ref_bytes += (length + 3) >> 2;
 #if defined(DSB_DEVICE_CODE)
+    // Short fetches (the 12-base LV windows) land in thread-private arrays, so every lane fills its
+    // own copy; long windows always land in the warp's scratch slice and are spread over the lanes.
+    if (length <= 16) {
+        for (uint32_t k = 0; k < length; k++)
+            dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
+        return;
+    }
     const uint32_t lane = threadIdx.x & 31;
     for (uint32_t k = lane; k < length; k += 32)
         dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);

@@ -1,0 +1,548 @@
+// dsb_cuda.cu -- sm_100a kernels + the C-ABI of include/dsb_cuda.h (libdsb_cuda.so).
+//
+// Three kernels per batch, all integer / byte work bounded by random HBM sector traffic
+// (DESIGN.md "kernels"):
+//   k_encode   : ASCII -> 2-bit codes, both strands, plus the head/tail margins of the history model
+//   k_exist    : one thread per k-mer position and strand: rolling-free k-mer, low-complexity mask,
+//                two hash probes into the exist-k-mer bit tables (reference src/cly.c:951-967)
+//   k_classify : persistent grid, ONE WARP PER READ pulling reads from an atomic queue; runs
+//                dsb_classify_read (dsb_core.cuh) = islands -> FM seeding -> LV anchors -> chaining
+//                -> sparse match-block scoring -> filters -> PRI/SEC/SUP
+// There is no CPU path in this file: every entry point fails with an error when CUDA fails.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include <mutex>
+#include <atomic>
+#include <algorithm>
+#include "dsb_cuda.h"
+#include "dsb_core.cuh"
+#include "dsb_layout.cuh"
+
+#define DSB_CLASSIFY_THREADS 128
+
+static thread_local std::string g_err;
+static std::atomic<int> g_launches{0};
+
+static int fail(const char *what, cudaError_t e)
+{
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return -1;
+}
+#define CU(call)                                        \
+    do {                                                \
+        cudaError_t e_ = (call);                        \
+        if (e_ != cudaSuccess) return fail(#call, e_);  \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------
+// device-side control block of a batch
+// ------------------------------------------------------------------------------------------
+struct DsbCtrl {
+    uint32_t next_read;      // work queue head of k_classify
+    uint32_t n_hits;         // hit arena allocator
+    uint32_t overflow;       // bit0 arena too small, bit1 reference would abort, bit2 hit arena too small
+    uint32_t pad;
+    dsb_counters counters;
+};
+
+struct dsb_index {
+    int dev;
+    DsbIndexView v;                 // pointers are DEVICE pointers
+    std::vector<void *> allocs;
+    uint64_t bytes;
+    int sm_count;
+};
+
+struct dsb_slot {
+    dsb_index *ix;
+    cudaStream_t stream;
+    uint64_t max_bases;
+    uint32_t max_reads;
+    // pinned host staging
+    char *h_seq;
+    dsb_read_desc *h_desc;
+    uint8_t *h_edge;
+    dsb_read_result *h_results;
+    dsb_hit *h_hits;
+    DsbCtrl *h_ctrl;
+    uint32_t *h_order;
+    // device
+    char *d_seq;
+    dsb_read_desc *d_desc;
+    uint8_t *d_edge;
+    uint8_t *d_bin;
+    uint8_t *d_exist;
+    dsb_read_result *d_results;
+    dsb_hit *d_hits;
+    DsbCtrl *d_ctrl;
+    uint32_t *d_order;
+    uint8_t *d_scratch;
+    size_t scratch_bytes;
+    uint32_t cap_hits, h_cap_hits;
+    uint32_t cap_anchor, cap_sms;
+    DsbScratchDims dims;
+    int n_warps, blocks, threads;
+    // state of the batch in flight
+    uint32_t n_reads;
+    uint64_t n_bases;
+    uint32_t Lmax;
+    bool in_flight;
+    cudaEvent_t ev[6];              // 0 start, 1 after H2D+encode, 2 after exist, 3 after classify, 4 end
+    float ms_total, ms_exist, ms_classify;
+};
+
+// ------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------
+// one block per read: 2-bit codes of both strands + the margins shipped by the host
+__global__ void __launch_bounds__(256) k_encode(const char *__restrict__ seq, const dsb_read_desc *__restrict__ desc,
+                                                const uint8_t *__restrict__ edge, uint8_t *__restrict__ bin,
+                                                uint32_t n_reads)
+{
+    for (uint32_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
+        const dsb_read_desc d = desc[r];
+        const uint32_t L = d.len;
+        uint8_t *b = bin + dsb_bin_off(d.seq_off, r);
+        const uint8_t *e = edge + (size_t)r * (DSB_HEAD_BYTES + DSB_TAIL_BYTES);
+        uint8_t *F = b + DSB_HEAD_PAD, *R = F + L;
+        if (threadIdx.x < DSB_HEAD_PAD) b[threadIdx.x] = e[threadIdx.x];
+        if (threadIdx.x < DSB_TAIL_PAD) R[L + threadIdx.x] = e[DSB_HEAD_BYTES + threadIdx.x];
+        const char *s = seq + d.seq_off;
+        for (uint32_t p = threadIdx.x; p < L; p += blockDim.x) {
+            const uint8_t c = dsb_encode_base((uint8_t)s[p]);
+            F[p] = c;
+            R[L - 1 - p] = (uint8_t)(3 - c);
+        }
+    }
+}
+
+// one block per read, one thread per (strand, k-mer position)
+__global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexView ix,
+                                               const dsb_read_desc *__restrict__ desc, const uint8_t *__restrict__ bin,
+                                               uint8_t *__restrict__ exist, uint32_t n_reads, DsbCtrl *ctrl)
+{
+    uint32_t p0 = 0, p1 = 0;
+    const uint32_t k = (uint32_t)ix.ek_len;
+    for (uint32_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
+        const dsb_read_desc d = desc[r];
+        const uint32_t L = d.len;
+        if (L < 40) continue;                                   // never classified (src/cly.c:3084)
+        const uint8_t *F = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
+        uint8_t *ex = exist + 2 * d.seq_off;
+        const uint32_t n = L - k + 1;
+        for (uint32_t t = threadIdx.x; t < 2 * n; t += blockDim.x) {
+            const uint32_t strand = (t >= n) ? 1u : 0u;
+            const uint32_t p = t - strand * n;
+            ex[strand * L + p] = dsb_exist_kmer(&ix, F + strand * L + p, &p0, &p1);
+        }
+    }
+    // block-level reduction of the probe counters
+    for (int o = 16; o > 0; o >>= 1) {
+        p0 += __shfl_down_sync(0xffffffffu, p0, o);
+        p1 += __shfl_down_sync(0xffffffffu, p1, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (p0) atomicAdd((unsigned long long *)&ctrl->counters.exist_probes0, (unsigned long long)p0);
+        if (p1) atomicAdd((unsigned long long *)&ctrl->counters.exist_probes1, (unsigned long long)p1);
+    }
+}
+
+// persistent: every warp pulls the next read of the (longest-first) order until none is left
+__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
+    const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, const uint32_t *__restrict__ order,
+    uint8_t *__restrict__ bin, const uint8_t *__restrict__ exist, uint8_t *__restrict__ scratch,
+    const __grid_constant__ DsbScratchDims dims, dsb_read_result *__restrict__ results, dsb_hit *__restrict__ hits,
+    uint32_t cap_hits, uint32_t n_reads, DsbCtrl *ctrl)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    DsbWork w;
+    memset(&w, 0, sizeof w);
+    w.ix = &ix;
+    dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
+    for (;;) {
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&ctrl->next_read, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot >= n_reads) break;
+        const uint32_t r = order[slot];
+        const dsb_read_desc d = desc[r];
+        w.bin = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
+        w.L = d.len;
+        w.is_2g = (d.flags & DSB_READ_2G) ? 1u : 0u;
+        w.exist[0] = exist + 2 * d.seq_off;
+        w.exist[1] = w.exist[0] + d.len;
+        w.overflow = 0;
+        memset(&w.st, 0, sizeof w.st);
+        dsb_classify_read(&w);
+        __syncwarp();
+        uint32_t hit_off = 0;
+        if (lane == 0) {
+            if (w.overflow) atomicOr(&ctrl->overflow, w.overflow);
+            else if (w.n_chain) hit_off = atomicAdd(&ctrl->n_hits, w.n_chain);
+        }
+        hit_off = __shfl_sync(0xffffffffu, hit_off, 0);
+        if (w.overflow) continue;
+        if (hit_off + w.n_chain > cap_hits) {
+            if (lane == 0) atomicOr(&ctrl->overflow, 4u);
+            continue;
+        }
+        for (uint32_t c = lane; c < w.n_chain; c += 32) {
+            const DsbChain &ch = w.chains[c];
+            dsb_hit h;
+            h.ref_ID = ch.ref_ID; h.t_st = ch.t_st; h.t_ed = ch.t_ed; h.q_st = ch.q_st; h.q_ed = ch.q_ed;
+            h.sum_score = ch.sum_score; h.indel = ch.indel; h.anchor_number = ch.anchor_number;
+            h.direction = ch.direction; h.primary = ch.primary; h.pri_index = ch.pri_index;
+            h.with_top_anchor = ch.with_top;
+            hits[hit_off + c] = h;
+        }
+        if (lane == 0) {
+            dsb_read_result rr;
+            rr.hit_off = hit_off; rr.n_hit = w.n_chain; rr.fast_classify = w.fast_classify; rr.n_anchor = w.n_anchor;
+            results[r] = rr;
+            dsb_counters *cn = &ctrl->counters;
+#define DSB_ADD(field, val) if (val) atomicAdd((unsigned long long *)&cn->field, (unsigned long long)(val))
+            DSB_ADD(occ_queries, w.st.occ); DSB_ADD(lut_lookups, w.st.lut); DSB_ADD(sa_lookups, w.st.sa);
+            DSB_ADD(unitig_reads, w.st.unitig); DSB_ADD(refpos_reads, w.st.refpos);
+            DSB_ADD(ref_window_bytes, w.st.ref_bytes); DSB_ADD(mem_searches, w.st.mem_search);
+            DSB_ADD(map_seeds, w.st.map_seed); DSB_ADD(sdp_windows, w.st.sdp_win);
+            DSB_ADD(anchors, w.n_anchor); DSB_ADD(slow_reads, w.st.slow);
+#undef DSB_ADD
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// C-ABI: index
+// ------------------------------------------------------------------------------------------
+template <typename T>
+static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_zero, const T **out)
+{
+    void *d = nullptr;
+    const size_t bytes = (size_t)(count + extra_zero) * sizeof(T);
+    CU(cudaMalloc(&d, bytes ? bytes : 16));
+    ix->allocs.push_back(d);
+    if (count) CU(cudaMemcpy(d, src, (size_t)count * sizeof(T), cudaMemcpyHostToDevice));
+    if (extra_zero) CU(cudaMemset((char *)d + (size_t)count * sizeof(T), 0, (size_t)extra_zero * sizeof(T)));
+    ix->bytes += bytes;
+    *out = (const T *)d;
+    return 0;
+}
+
+extern "C" {
+
+const char *dsb_last_error(void) { return g_err.c_str(); }
+int dsb_kernel_launch_count(void) { return g_launches.load(); }
+
+int dsb_gpu_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { fail("cudaGetDeviceCount", e); return 0; }
+    return n;
+}
+
+void dsb_index_free(dsb_index *ix)
+{
+    if (!ix) return;
+    cudaSetDevice(ix->dev);
+    for (void *p : ix->allocs) cudaFree(p);
+    delete ix;
+}
+
+int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
+{
+    *out = nullptr;
+    CU(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) {
+        g_err = "device is not sm_100-class; this library carries sm_100a code only";
+        return -1;
+    }
+    dsb_index *ix = new dsb_index();
+    ix->dev = dev;
+    ix->bytes = 0;
+    ix->sm_count = prop.multiProcessorCount;
+    DsbIndexView &v = ix->v;
+    memset(&v, 0, sizeof v);
+    int rc = 0;
+    {   // FM index: re-block on the host into 64-symbol / 64-byte blocks, then one copy
+        const uint64_t nblk = dsb_fm_blocks_needed(h->bwt_bytes);
+        std::vector<DsbFmBlock> fm(nblk);
+        uint64_t bad = 0;
+        dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, fm.data(), &bad);
+        if (bad) {
+            g_err = "FM blocks whose stored '#' count differs from the derived one: index not supported";
+            delete ix;
+            return -1;
+        }
+        v.n_fm_blocks = nblk;
+        rc |= upload(ix, fm.data(), nblk, 1, &v.fm);
+    }
+    memcpy(v.rank, h->rank, sizeof v.rank);
+    v.dollar_pos = h->dollar_pos;
+    rc |= upload(ix, h->hash_index, (1ull << 26) + 1, 1, &v.lut);
+    rc |= upload(ix, h->sa_taxon, h->sa_n, 1, &v.sa);
+    v.sa_n = h->sa_n;
+    rc |= upload(ix, h->e_kmer0, h->e_kmer_size, 0, &v.ek0);
+    rc |= upload(ix, h->e_kmer1, h->e_kmer_size, 0, &v.ek1);
+    int k;
+    uint64_t mask;
+    dsb_ekmer_params(h->e_kmer_size, &k, &mask);
+    v.ek_mask = mask;
+    v.ek_len = k;
+    v.single_base_max = (int)(0.8 * k);              // src/idx.c:981
+    rc |= upload(ix, h->unitig, h->n_unitig, 2, &v.unitig);
+    v.n_unitig = h->n_unitig;
+    rc |= upload(ix, h->ref_pos, h->n_ref_pos, 2, &v.ref_pos);
+    rc |= upload(ix, h->ref_bin, h->ref_bin_n, 64, &v.ref_bin);
+    v.ref_bin_n = h->ref_bin_n;
+    rc |= upload(ix, h->ref_seq_offset, h->n_ref, 1, &v.ref_off);
+    rc |= upload(ix, h->ref_seq_len, h->n_ref, 1, &v.ref_len);
+    v.n_ref = h->n_ref;
+    rc |= upload(ix, h->q_mem, 2000, 0, &v.q_mem);
+    rc |= upload(ix, h->q_lv, 400, 0, &v.q_lv);
+    v.filter_min_length = h->filter_min_length;
+    v.filter_min_score = h->filter_min_score;
+    v.filter_min_score_lv3 = h->filter_min_score_lv3;
+    if (rc) { dsb_index_free(ix); return -1; }
+    // the classifier's frames are deep (LV tables, merge-sort stacks): give them room
+    cudaDeviceSetLimit(cudaLimitStackSize, 8192);
+    *out = ix;
+    return 0;
+}
+
+uint64_t dsb_index_device_bytes(const dsb_index *ix) { return ix ? ix->bytes : 0; }
+
+// ------------------------------------------------------------------------------------------
+// C-ABI: slots (one CUDA stream + pinned staging + device buffers)
+// ------------------------------------------------------------------------------------------
+static int ensure_scratch(dsb_slot *s, uint32_t Lmax)
+{
+    DsbScratchDims d;
+    dsb_scratch_dims(&d, Lmax, s->cap_anchor, s->cap_sms);
+    const size_t need = d.bytes * (size_t)s->n_warps;
+    if (need > s->scratch_bytes) {
+        if (s->d_scratch) CU(cudaFree(s->d_scratch));
+        s->d_scratch = nullptr;
+        s->scratch_bytes = 0;
+        CU(cudaMalloc((void **)&s->d_scratch, need));
+        s->scratch_bytes = need;
+    }
+    s->dims = d;
+    return 0;
+}
+
+static int ensure_hits(dsb_slot *s, uint32_t cap)
+{
+    if (cap > s->cap_hits) {
+        if (s->d_hits) CU(cudaFree(s->d_hits));
+        s->d_hits = nullptr;
+        s->cap_hits = 0;
+        CU(cudaMalloc((void **)&s->d_hits, (size_t)cap * sizeof(dsb_hit)));
+        s->cap_hits = cap;
+    }
+    return 0;
+}
+
+void dsb_slot_free(dsb_slot *s)
+{
+    if (!s) return;
+    cudaSetDevice(s->ix->dev);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    cudaFreeHost(s->h_seq); cudaFreeHost(s->h_desc); cudaFreeHost(s->h_edge); cudaFreeHost(s->h_results);
+    cudaFreeHost(s->h_hits); cudaFreeHost(s->h_ctrl); cudaFreeHost(s->h_order);
+    cudaFree(s->d_seq); cudaFree(s->d_desc); cudaFree(s->d_edge); cudaFree(s->d_bin); cudaFree(s->d_exist);
+    cudaFree(s->d_results); cudaFree(s->d_hits); cudaFree(s->d_ctrl); cudaFree(s->d_order); cudaFree(s->d_scratch);
+    for (int i = 0; i < 6; i++) if (s->ev[i]) cudaEventDestroy(s->ev[i]);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    delete s;
+}
+
+int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_slot **out)
+{
+    *out = nullptr;
+    CU(cudaSetDevice(ix->dev));
+    dsb_slot *s = new dsb_slot();
+    memset((void *)s, 0, sizeof *s);
+    s->ix = ix;
+    s->max_bases = max_bases;
+    s->max_reads = max_reads;
+    const size_t edge_bytes = (size_t)max_reads * (DSB_HEAD_BYTES + DSB_TAIL_BYTES);
+    int rc = 0;
+#define TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rc = fail(#call, e_); goto done; } } while (0)
+    TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 6; i++) TRY(cudaEventCreate(&s->ev[i]));
+    TRY(cudaHostAlloc((void **)&s->h_seq, max_bases + 64, cudaHostAllocDefault));
+    TRY(cudaHostAlloc((void **)&s->h_desc, (size_t)max_reads * sizeof(dsb_read_desc), cudaHostAllocDefault));
+    TRY(cudaHostAlloc((void **)&s->h_edge, edge_bytes, cudaHostAllocDefault));
+    TRY(cudaHostAlloc((void **)&s->h_results, (size_t)max_reads * sizeof(dsb_read_result), cudaHostAllocDefault));
+    TRY(cudaHostAlloc((void **)&s->h_ctrl, sizeof(DsbCtrl), cudaHostAllocDefault));
+    TRY(cudaHostAlloc((void **)&s->h_order, (size_t)max_reads * 4, cudaHostAllocDefault));
+    TRY(cudaMalloc((void **)&s->d_seq, max_bases + 64));
+    TRY(cudaMalloc((void **)&s->d_desc, (size_t)max_reads * sizeof(dsb_read_desc)));
+    TRY(cudaMalloc((void **)&s->d_edge, edge_bytes));
+    TRY(cudaMalloc((void **)&s->d_bin, dsb_bin_bytes(max_bases, max_reads)));
+    TRY(cudaMalloc((void **)&s->d_exist, 2 * max_bases + 64));
+    TRY(cudaMalloc((void **)&s->d_results, (size_t)max_reads * sizeof(dsb_read_result)));
+    TRY(cudaMalloc((void **)&s->d_ctrl, sizeof(DsbCtrl)));
+    TRY(cudaMalloc((void **)&s->d_order, (size_t)max_reads * 4));
+    {
+        // persistent grid: as many warps as the device keeps resident
+        int per_sm = 0;
+        TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_classify, DSB_CLASSIFY_THREADS, 0));
+        if (per_sm < 1) per_sm = 1;
+        const char *e = getenv("DSB_BLOCKS_PER_SM");
+        if (e && atoi(e) > 0 && atoi(e) < per_sm) per_sm = atoi(e);
+        s->threads = DSB_CLASSIFY_THREADS;
+        s->blocks = per_sm * ix->sm_count;
+        s->n_warps = s->blocks * (DSB_CLASSIFY_THREADS / 32);
+    }
+    s->cap_anchor = 2048;
+    s->cap_sms = 8192;
+    if (ensure_hits(s, max_reads * 8u + 4096u)) { rc = -1; goto done; }
+    s->h_cap_hits = s->cap_hits;
+    TRY(cudaHostAlloc((void **)&s->h_hits, (size_t)s->h_cap_hits * sizeof(dsb_hit), cudaHostAllocDefault));
+#undef TRY
+done:
+    if (rc) { dsb_slot_free(s); return rc; }
+    *out = s;
+    return 0;
+}
+
+int dsb_slot_staging(dsb_slot *s, char **seq, dsb_read_desc **desc, uint8_t **edge)
+{
+    *seq = s->h_seq;
+    *desc = s->h_desc;
+    *edge = s->h_edge;
+    return 0;
+}
+
+// kernels of one batch, inputs already on the device
+static int launch_kernels(dsb_slot *s)
+{
+    const uint32_t n = s->n_reads;
+    CU(cudaMemsetAsync(s->d_ctrl, 0, sizeof(DsbCtrl), s->stream));
+    const int sm = s->ix->sm_count;
+    const uint32_t grid_r = n < (uint32_t)(sm * 8) ? n : (uint32_t)(sm * 8);
+    k_encode<<<grid_r, 256, 0, s->stream>>>(s->d_seq, s->d_desc, s->d_edge, s->d_bin, n);
+    CU(cudaEventRecord(s->ev[1], s->stream));
+    k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
+    CU(cudaEventRecord(s->ev[2], s->stream));
+    k_classify<<<s->blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
+                                                       s->dims, s->d_results, s->d_hits, s->cap_hits, n, s->d_ctrl);
+    CU(cudaEventRecord(s->ev[3], s->stream));
+    CU(cudaGetLastError());
+    g_launches += 3;
+    CU(cudaMemcpyAsync(s->h_ctrl, s->d_ctrl, sizeof(DsbCtrl), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaMemcpyAsync(s->h_results, s->d_results, (size_t)n * sizeof(dsb_read_result), cudaMemcpyDeviceToHost, s->stream));
+    return 0;
+}
+
+int dsb_slot_submit(dsb_slot *s, uint32_t n_reads, uint64_t n_bases)
+{
+    if (n_reads == 0 || n_reads > s->max_reads || n_bases > s->max_bases) {
+        g_err = "dsb_slot_submit: batch exceeds the slot's capacity";
+        return -1;
+    }
+    CU(cudaSetDevice(s->ix->dev));
+    s->n_reads = n_reads;
+    s->n_bases = n_bases;
+    // longest reads first: the persistent grid's tail is then made of short reads
+    uint32_t Lmax = 0;
+    {
+        std::vector<uint64_t> key(n_reads);
+        for (uint32_t i = 0; i < n_reads; i++) {
+            const uint32_t L = s->h_desc[i].len;
+            if (L > Lmax) Lmax = L;
+            key[i] = ((uint64_t)(0xffffffffu - L) << 32) | i;
+        }
+        std::sort(key.begin(), key.end());
+        for (uint32_t i = 0; i < n_reads; i++) s->h_order[i] = (uint32_t)key[i];
+    }
+    s->Lmax = Lmax;
+    if (ensure_scratch(s, Lmax)) return -1;
+    CU(cudaEventRecord(s->ev[0], s->stream));
+    CU(cudaMemcpyAsync(s->d_seq, s->h_seq, n_bases, cudaMemcpyHostToDevice, s->stream));
+    CU(cudaMemcpyAsync(s->d_desc, s->h_desc, (size_t)n_reads * sizeof(dsb_read_desc), cudaMemcpyHostToDevice, s->stream));
+    CU(cudaMemcpyAsync(s->d_edge, s->h_edge, (size_t)n_reads * (DSB_HEAD_BYTES + DSB_TAIL_BYTES), cudaMemcpyHostToDevice,
+                       s->stream));
+    CU(cudaMemcpyAsync(s->d_order, s->h_order, (size_t)n_reads * 4, cudaMemcpyHostToDevice, s->stream));
+    if (launch_kernels(s)) return -1;
+    s->in_flight = true;
+    return 0;
+}
+
+int dsb_slot_rerun_device(dsb_slot *s)
+{
+    if (s->n_reads == 0) { g_err = "dsb_slot_rerun_device: nothing was submitted"; return -1; }
+    CU(cudaSetDevice(s->ix->dev));
+    CU(cudaEventRecord(s->ev[0], s->stream));
+    if (launch_kernels(s)) return -1;
+    s->in_flight = true;
+    return 0;
+}
+
+int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **hits, uint32_t *n_hits,
+                  dsb_counters *counters)
+{
+    if (!s->in_flight) { g_err = "dsb_slot_wait: no batch in flight"; return -1; }
+    CU(cudaSetDevice(s->ix->dev));
+    for (int attempt = 0;; attempt++) {
+        CU(cudaStreamSynchronize(s->stream));
+        const uint32_t of = s->h_ctrl->overflow;
+        if (of == 0) break;
+        if (of & 2u) {
+            s->in_flight = false;
+            g_err = "a chain gap of >= 2000 reference bases reached sdp_middle: the reference aborts here (src/cly.c:2468)";
+            return -2;
+        }
+        if (attempt >= 8) { s->in_flight = false; g_err = "scratch arenas still too small after 8 regrows"; return -1; }
+        // grow whatever overflowed and run the batch again (inputs are still on the device)
+        if (of & 1u) {
+            s->cap_anchor *= 4;
+            s->cap_sms *= 4;
+            if (ensure_scratch(s, s->Lmax)) return -1;
+        }
+        if (of & 4u) {
+            if (ensure_hits(s, s->cap_hits * 4u)) return -1;
+        }
+        if (launch_kernels(s)) return -1;
+    }
+    const uint32_t nh = s->h_ctrl->n_hits;
+    if (nh > s->h_cap_hits) {
+        cudaFreeHost(s->h_hits);
+        s->h_hits = nullptr;
+        s->h_cap_hits = 0;
+        CU(cudaHostAlloc((void **)&s->h_hits, (size_t)s->cap_hits * sizeof(dsb_hit), cudaHostAllocDefault));
+        s->h_cap_hits = s->cap_hits;
+    }
+    if (nh) CU(cudaMemcpyAsync(s->h_hits, s->d_hits, (size_t)nh * sizeof(dsb_hit), cudaMemcpyDeviceToHost, s->stream));
+    CU(cudaEventRecord(s->ev[4], s->stream));
+    CU(cudaStreamSynchronize(s->stream));
+    cudaEventElapsedTime(&s->ms_total, s->ev[0], s->ev[4]);
+    cudaEventElapsedTime(&s->ms_exist, s->ev[1], s->ev[2]);
+    cudaEventElapsedTime(&s->ms_classify, s->ev[2], s->ev[3]);
+    s->in_flight = false;
+    *results = s->h_results;
+    *hits = s->h_hits;
+    *n_hits = nh;
+    if (counters) *counters = s->h_ctrl->counters;
+    return 0;
+}
+
+int dsb_slot_timing(dsb_slot *s, float *ms_total, float *ms_exist, float *ms_classify)
+{
+    *ms_total = s->ms_total;
+    *ms_exist = s->ms_exist;
+    *ms_classify = s->ms_classify;
+    return 0;
+}
+
+}  // extern "C"
