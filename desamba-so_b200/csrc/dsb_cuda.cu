@@ -277,11 +277,10 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
         std::vector<DsbFmBlock> fm(nblk);
         uint64_t bad = 0;
         dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, fm.data(), &bad);
-        if (bad) {
-            g_err = "FM blocks whose stored '#' count differs from the derived one: index not supported";
-            delete ix;
-            return -1;
-        }
+        // `bad` counts blocks whose stored '#' checkpoint differs from the one derived from A/C/G/T
+        // (padding after the last BWT symbol); the classifier never consumes a '#' rank, so it is
+        // informational only.
+        (void)bad;
         v.n_fm_blocks = nblk;
         rc |= upload(ix, fm.data(), nblk, 1, &v.fm);
     }

@@ -1,0 +1,178 @@
+#!/usr/bin/env python3
+"""Build a named synthetic data set for the classify hot path (test / bench infrastructure).
+
+A data set = reference FASTA + kmer.srt + index directory (built by the UNMODIFIED reference
+binary oracle/_ref/deSAMBA) + reads FASTQ + the reference's own `classify -t 1`
+SAM ("golden").  Everything is derived from seeds, so the GPU box rebuilds byte-identical inputs
+from this script alone; nothing here reads /root/reference.
+
+Reads on which the reference binary itself crashes are dropped (they are "reference-undefined":
+e.g. sdp_left_M2 reads ref_bin at a negative offset for a chain near the start of reference 0,
+reference src/cly.c:2719-2722).  The crashers are found by bisection and recorded in
+<dir>/dropped.txt so the same filtered FASTQ is used by both sides.
+"""
+import argparse
+import hashlib
+import json
+import os
+import subprocess
+import sys
+import time
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "deSAMBA")
+sys.path.insert(0, HERE)
+import synth  # noqa: E402
+
+# name -> parameters.  `cfg1` is the stand-in for BASELINE.json configs[0] (the demo data are
+# not in the reference tree), `cfg2` is configs[1] (the bench workload), `tiny` is for smoke.
+CONFIGS = {
+    "tiny": dict(families=4, strains=3, length=80000, snp=0.01, ref_seed=7, human_first=False,
+                 n_reads=300, read_len=5000, err=0.10, read_seed=9, junk=0.05, mix="1,1,1", jitter=0.0),
+    "mixed": dict(families=4, strains=3, length=80000, snp=0.01, ref_seed=7, human_first=False,
+                  n_reads=400, read_len=2000, err=0.12, read_seed=11, junk=0.10, mix="1,1,1", jitter=0.95),
+    "cfg1": dict(families=1, strains=5, length=1000000, snp=0.01, ref_seed=1, human_first=True,
+                 n_reads=2000, read_len=5000, err=0.10, read_seed=2, junk=0.05, mix="1,1,1", jitter=0.0),
+    "cfg2": dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
+                 n_reads=10000, read_len=5000, err=0.10, read_seed=43, junk=0.05, mix="1,1,1", jitter=0.0),
+    "ont10k": dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
+                   n_reads=4000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5),
+}
+
+
+def data_root():
+    return os.environ.get("DSB_DATA", "/tmp/dsb_data")
+
+
+def ref_key(p):
+    return "ref_f%d_s%d_l%d_snp%g_seed%d_h%d" % (p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"],
+                                                 int(p["human_first"]))
+
+
+def run(cmd, **kw):
+    return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, **kw)
+
+
+def build_index(p, log=sys.stderr):
+    """Reference FASTA + index directory shared by every read set on the same genomes."""
+    d = os.path.join(data_root(), ref_key(p))
+    idx = os.path.join(d, "idx")
+    if os.path.exists(os.path.join(d, "index.ok")):
+        return d, idx
+    if not os.path.exists(REF_BIN):
+        raise RuntimeError("oracle/_ref/deSAMBA is missing: run `make -C oracle ref` where /root/reference exists")
+    os.makedirs(idx, exist_ok=True)
+    t0 = time.time()
+    g = synth.make_genomes(p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"])
+    synth.write_fasta(os.path.join(d, "ref.fa"), g, p["human_first"])
+    synth.write_kmer_srt(os.path.join(d, "kmer.srt"), g)
+    synth.write_taxonomy(idx, g, p["strains"], p["human_first"])
+    r = run([REF_BIN, "index", "kmer.srt", "ref.fa", "idx"], cwd=d)
+    if r.returncode != 0 or not os.path.exists(os.path.join(idx, "deSAMBA.bwt")):
+        raise RuntimeError("reference index build failed:\n" + r.stderr.decode()[-2000:])
+    os.remove(os.path.join(d, "kmer.srt"))
+    open(os.path.join(d, "index.ok"), "w").write("ok\n")
+    print("[dataset] index %s built in %.1fs" % (ref_key(p), time.time() - t0), file=log)
+    return d, idx
+
+
+def read_fastq_records(path):
+    with open(path, "rb") as fh:
+        lines = fh.read().split(b"\n")
+    return [b"\n".join(lines[i:i + 4]) + b"\n" for i in range(0, len(lines) - 1, 4)]
+
+
+def ref_classify(idx, fq, out, threads=1, fmt="SAM"):
+    with open(out, "wb") as fo:
+        r = subprocess.run([REF_BIN, "classify", "-t", str(threads), "-f", fmt, idx + "/", fq], stdout=fo,
+                           stderr=subprocess.PIPE)
+    return r.returncode
+
+
+def find_crashers(idx, recs, tmp):
+    """Indices of records on which the reference crashes when classified alone-in-context."""
+    bad = []
+
+    def crashes(ids):
+        with open(tmp, "wb") as fh:
+            for i in ids:
+                fh.write(recs[i])
+        return ref_classify(idx, tmp, tmp + ".sam") != 0
+
+    def rec(ids):
+        if not crashes(ids):
+            return
+        if len(ids) == 1:
+            bad.append(ids[0])
+            return
+        h = len(ids) // 2
+        rec(ids[:h])
+        rec(ids[h:])
+
+    chunk = 256
+    for s in range(0, len(recs), chunk):
+        rec(list(range(s, min(s + chunk, len(recs)))))
+    return bad
+
+
+def build(name, log=sys.stderr, golden=True):
+    """Returns dict(dir, idx, reads, golden, n_reads, n_bases)."""
+    p = CONFIGS[name]
+    rd, idx = build_index(p, log)
+    d = os.path.join(data_root(), name)
+    meta_path = os.path.join(d, "meta.json")
+    if os.path.exists(meta_path):
+        meta = json.load(open(meta_path))
+        if not golden or meta.get("golden"):
+            return meta
+    os.makedirs(d, exist_ok=True)
+    t0 = time.time()
+    g = synth.make_genomes(p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"])
+    w = [float(x) for x in p["mix"].split(",")]
+    raw = os.path.join(d, "raw.fq")
+    synth.write_reads(raw, g, p["n_reads"], p["read_len"], p["err"], p["read_seed"], p["junk"],
+                      tuple(x / sum(w) for x in w), p["jitter"])
+    recs = read_fastq_records(raw)
+    fq = os.path.join(d, "reads.fq")
+    sam = os.path.join(d, "golden.sam")
+    dropped = []
+    committed = os.path.join(ROOT, "tests", "golden", name + ".dropped.txt")
+    if os.path.exists(committed):
+        names = set(open(committed).read().split())
+        dropped = [i for i, r in enumerate(recs) if r.split(b"\n", 1)[0][1:].decode() in names]
+    for _ in range(4):
+        keep = [r for i, r in enumerate(recs) if i not in set(dropped)]
+        with open(fq, "wb") as fh:
+            fh.write(b"".join(keep))
+        if not golden:
+            break
+        if ref_classify(idx, fq, sam) == 0:
+            break
+        print("[dataset] %s: reference crashed, bisecting" % name, file=log)
+        live = [i for i in range(len(recs)) if i not in set(dropped)]
+        sub = [recs[i] for i in live]
+        dropped += [live[j] for j in find_crashers(idx, sub, os.path.join(d, "bisect.fq"))]
+    else:
+        raise RuntimeError("reference keeps crashing on " + name)
+    os.remove(raw)
+    with open(os.path.join(d, "dropped.txt"), "w") as fh:
+        for i in dropped:
+            fh.write(recs[i].split(b"\n", 1)[0][1:].decode() + "\n")
+    n_bases = sum(len(r.split(b"\n")[1]) for i, r in enumerate(recs) if i not in set(dropped))
+    meta = dict(name=name, dir=d, idx=idx, reads=fq, golden=sam if golden else None,
+                n_reads=len(recs) - len(dropped), n_bases=n_bases, dropped=len(dropped))
+    if golden:
+        meta["golden_md5"] = hashlib.md5(open(sam, "rb").read()).hexdigest()
+    json.dump(meta, open(meta_path, "w"))
+    print("[dataset] %s: %d reads, %d bases, %d dropped, %.1fs" % (name, meta["n_reads"], n_bases, len(dropped),
+                                                                 time.time() - t0), file=log)
+    return meta
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("name", choices=sorted(CONFIGS))
+    ap.add_argument("--no-golden", action="store_true")
+    a = ap.parse_args()
+    print(json.dumps(build(a.name, golden=not a.no_golden), indent=1))
