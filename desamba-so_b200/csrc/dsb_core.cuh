@@ -188,6 +188,14 @@ struct DsbWork {
     DsbStats st;
 };
 
+// host-simulator tracing (tests/hostsim built with -DDSB_TRACE_ON): compiled out everywhere else
+#if defined(DSB_TRACE_ON) && !defined(__CUDACC__)
+#include <stdio.h>
+#define DSB_TRACE(...) fprintf(stderr, __VA_ARGS__)
+#else
+#define DSB_TRACE(...) ((void)0)
+#endif
+
 #define DSB_MAX(a, b) (((a) > (b)) ? (a) : (b))     // src/lib/utils.h:61-64 (same macro shapes:
 #define DSB_MIN(a, b) (((a) < (b)) ? (a) : (b))     //  mixed signed/unsigned operands convert
 #define DSB_ABS(a) (((a) > 0) ? (a) : (-(a)))       //  exactly as in the reference)
@@ -852,12 +860,15 @@ DSB_HDN void dsb_fast_classify(DsbWork *w, int strand)
             const int string_index = kmer_index + l_ek - 1;
             const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
             const int n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
+            DSB_TRACE("FAST strand=%d island=%u j=%d sidx=%d n_mem=%d\n", strand, ci, j, string_index, n_mem);
             if (n_mem == 0) { j -= 2; continue; }
             j -= 3;
             int max_score = 0;
             for (int mi = 0; mi < n_mem; mi++) {
                 m_r[mi].read_offset = string_index - m_r[mi].match_len;
                 const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, direction);
+                DSB_TRACE("  MEM len=%d roff=%d sp=%llu score=%d\n", m_r[mi].match_len, m_r[mi].read_offset,
+                          (unsigned long long)m_r[mi].sp, c_score);
                 max_score = DSB_MAX(c_score, max_score);
             }
             if (max_score > 35) j -= 7;
@@ -1424,6 +1435,8 @@ DSB_HDN int dsb_sdp_right(DsbWork *w, const uint8_t *q_str, int strand, int key_
     const uint64_t t_length = ix->ref_len[c_h->ref_ID];
     uint32_t c_t_offset = c_h->t_ed - 3;
     int last_search = 0;
+    DSB_TRACE("RBEG chain=%d ref=%u q_st=%u q_ed=%u t_st=%u t_ed=%u score=%d\n", chain_ID, c_h->ref_ID, c_h->q_st, c_h->q_ed,
+              c_h->t_st, c_h->t_ed, score_ori - 10000);
     while (1) {
         if (w->overflow) break;
         if (w->n_sms == current_sms) {
@@ -1494,6 +1507,8 @@ DSB_HDN int dsb_sdp_right(DsbWork *w, const uint8_t *q_str, int strand, int key_
     }
     c_h->q_ed = w->sms[max_sms_id].q_pos + w->sms[max_sms_id].len + DSB_KMER9;
     c_h->t_ed = w->sms[max_sms_id].t_pos + w->sms[max_sms_id].len + DSB_KMER9;
+    DSB_TRACE("REND chain=%d ref=%u q_ed=%u t_ed=%u score=%d maxid=%d n=%d\n", chain_ID, c_h->ref_ID, c_h->q_ed, c_h->t_ed,
+              total_max_score - 10000, max_sms_id, (int)w->n_sms);
     return total_max_score - 10000;
 }
 
@@ -1598,7 +1613,11 @@ DSB_HDN void dsb_get_score(DsbWork *w)
         if (w->chains[i].sum_score == 0) continue;
         const int strand = (w->chains[i].direction == DSB_FORWARD) ? 0 : 1;
         const uint8_t *q_str = w->bin + (strand ? w->L : 0);
+        DSB_TRACE("CH %u ref=%u dir=%d q=%u-%u t=%u-%u ss=%u an=%u indel=%u top=%d\n", i, w->chains[i].ref_ID,
+                  w->chains[i].direction, w->chains[i].q_st, w->chains[i].q_ed, w->chains[i].t_st, w->chains[i].t_ed,
+                  w->chains[i].sum_score, w->chains[i].anchor_number, w->chains[i].indel, w->chains[i].with_top);
         int score = dsb_sdp_middle(w, w->chains[i].cur, q_str, strand, key_len);
+        DSB_TRACE("MID %u score=%d\n", i, score);
         score = dsb_sdp_right(w, q_str, strand, key_len, (int)i, w->L, score);
         score = dsb_sdp_left(w, q_str, strand, key_len, (int)i, w->L, score);
         w->chains[i].sum_score = (uint32_t)score;

@@ -217,6 +217,30 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
     }
 }
 
+
+// bulk primitives (parity known-answer entry + roofline probes)
+__global__ void __launch_bounds__(256) k_fm_rank(const __grid_constant__ DsbIndexView ix, const uint64_t *__restrict__ row,
+                                                 const uint8_t *__restrict__ c_in, uint64_t n, uint64_t *__restrict__ out,
+                                                 uint8_t *__restrict__ c_out)
+{
+    DsbWork w;
+    w.ix = &ix;
+    w.st.occ = 0;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint8_t c = c_in[i];
+        out[i] = dsb_occ(&w, row[i], &c);
+        c_out[i] = c;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_exist_flat(const __grid_constant__ DsbIndexView ix, const uint8_t *__restrict__ codes,
+                                                    uint64_t n_kmer, uint8_t *__restrict__ exist)
+{
+    uint32_t p0 = 0, p1 = 0;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_kmer; i += (uint64_t)gridDim.x * blockDim.x)
+        exist[i] = dsb_exist_kmer(&ix, codes + i, &p0, &p1);
+}
+
 // ------------------------------------------------------------------------------------------
 // C-ABI: index
 // ------------------------------------------------------------------------------------------
@@ -541,6 +565,71 @@ int dsb_slot_timing(dsb_slot *s, float *ms_total, float *ms_exist, float *ms_cla
     *ms_total = s->ms_total;
     *ms_exist = s->ms_exist;
     *ms_classify = s->ms_classify;
+    return 0;
+}
+
+int dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint64_t n, uint64_t *out, uint8_t *c_out,
+                      int repeat, float *ms)
+{
+    CU(cudaSetDevice(ix->dev));
+    uint64_t *d_row = nullptr, *d_out = nullptr;
+    uint8_t *d_c = nullptr, *d_co = nullptr;
+    cudaEvent_t e0, e1;
+    CU(cudaMalloc((void **)&d_row, n * 8 + 8));
+    CU(cudaMalloc((void **)&d_out, n * 8 + 8));
+    CU(cudaMalloc((void **)&d_c, n + 8));
+    CU(cudaMalloc((void **)&d_co, n + 8));
+    CU(cudaMemcpy(d_row, row, n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_c, c, n, cudaMemcpyHostToDevice));
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int grid = ix->sm_count * 8;
+    if (repeat < 1) repeat = 1;
+    k_fm_rank<<<grid, 256>>>(ix->v, d_row, d_c, n, d_out, d_co);        // warm-up
+    CU(cudaEventRecord(e0));
+    for (int r = 0; r < repeat; r++) k_fm_rank<<<grid, 256>>>(ix->v, d_row, d_c, n, d_out, d_co);
+    CU(cudaEventRecord(e1));
+    CU(cudaDeviceSynchronize());
+    CU(cudaGetLastError());
+    g_launches += repeat + 1;
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (ms) *ms = t / repeat;
+    CU(cudaMemcpy(out, d_out, n * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(c_out, d_co, n, cudaMemcpyDeviceToHost));
+    cudaFree(d_row); cudaFree(d_out); cudaFree(d_c); cudaFree(d_co);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+
+int dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist, int repeat, float *ms)
+{
+    CU(cudaSetDevice(ix->dev));
+    const uint64_t k = (uint64_t)ix->v.ek_len;
+    if (n < k) { g_err = "dsb_exist_batch: string shorter than k"; return -1; }
+    const uint64_t nk = n - k + 1;
+    uint8_t *d_codes = nullptr, *d_ex = nullptr;
+    cudaEvent_t e0, e1;
+    CU(cudaMalloc((void **)&d_codes, n + 64));
+    CU(cudaMalloc((void **)&d_ex, nk + 64));
+    CU(cudaMemcpy(d_codes, codes, n, cudaMemcpyHostToDevice));
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int grid = ix->sm_count * 8;
+    if (repeat < 1) repeat = 1;
+    k_exist_flat<<<grid, 256>>>(ix->v, d_codes, nk, d_ex);
+    CU(cudaEventRecord(e0));
+    for (int r = 0; r < repeat; r++) k_exist_flat<<<grid, 256>>>(ix->v, d_codes, nk, d_ex);
+    CU(cudaEventRecord(e1));
+    CU(cudaDeviceSynchronize());
+    CU(cudaGetLastError());
+    g_launches += repeat + 1;
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (ms) *ms = t / repeat;
+    CU(cudaMemcpy(exist, d_ex, nk, cudaMemcpyDeviceToHost));
+    cudaFree(d_codes); cudaFree(d_ex);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;
 }
 

@@ -16,7 +16,8 @@ LIB_DIR = os.path.join(HERE, "lib")
 API_SYMBOLS = ["load_index", "read_classify", "meta_analysis"]
 CUDA_SYMBOLS = ["dsb_gpu_count", "dsb_index_upload", "dsb_index_free", "dsb_index_device_bytes", "dsb_slot_create",
                 "dsb_slot_free", "dsb_slot_staging", "dsb_slot_submit", "dsb_slot_wait", "dsb_slot_timing",
-                "dsb_slot_rerun_device", "dsb_last_error", "dsb_kernel_launch_count"]
+                "dsb_slot_rerun_device", "dsb_last_error", "dsb_kernel_launch_count", "dsb_fm_rank_batch",
+                "dsb_exist_batch"]
 HOST_SYMBOLS = ["dsb_index_load", "dsb_index_release_bulk", "dsb_index_destroy", "dsb_engine_create",
                 "dsb_engine_destroy", "dsb_session_create", "dsb_session_destroy", "dsb_session_run",
                 "dsb_fq_open_path", "dsb_fq_open_mem", "dsb_fq_close", "dsb_history_new", "dsb_history_next",
@@ -63,7 +64,7 @@ def load_cuda_layer(hostsim=False):
                                                                           "libdsb_hostsim.so")
     if not os.path.exists(p):
         raise RuntimeError("%s is not built (run __graft_entry__.build())" % p)
-    lib = C.CDLL(p, mode=C.RTLD_GLOBAL)
+    lib = C.CDLL(p)
     lib.dsb_last_error.restype = C.c_char_p
     lib.dsb_index_device_bytes.restype = C.c_uint64
     return lib
@@ -116,3 +117,83 @@ class Desamba:
         if hs.value:
             self.libc.free(hs)
         return text, snap
+
+
+class DeviceIndex:
+    """Index loaded by the C host loader and made resident through the CUDA C-ABI (or the host simulator)."""
+
+    def __init__(self, index_dir, dev=0, hostsim=False):
+        import numpy as np
+        self.np = np
+        self.cuda = load_cuda_layer(hostsim)
+        self.host = C.CDLL(lib_path("libdesamba.so", hostsim))
+        self.buf = C.create_string_buffer(1 << 16)          # dsb_loaded_index (its first member is dsb_host_index)
+        self.host.dsb_index_load(self.buf, index_dir.encode(), 170, 64)
+        self.handle = C.c_void_p()
+        rc = self.cuda.dsb_index_upload(self.buf, dev, C.byref(self.handle))
+        if rc != 0:
+            raise RuntimeError("dsb_index_upload: " + self.cuda.dsb_last_error().decode())
+
+    def close(self):
+        if self.handle:
+            self.cuda.dsb_index_free(self.handle)
+            self.handle = C.c_void_p()
+            self.host.dsb_index_destroy(self.buf)
+
+    def fm_rank(self, rows, c, repeat=1):
+        np = self.np
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        c = np.ascontiguousarray(c, dtype=np.uint8)
+        out = np.empty(len(rows), dtype=np.uint64)
+        c_out = np.empty(len(rows), dtype=np.uint8)
+        ms = C.c_float(0)
+        rc = self.cuda.dsb_fm_rank_batch(self.handle, rows.ctypes.data_as(C.c_void_p), c.ctypes.data_as(C.c_void_p),
+                                         C.c_uint64(len(rows)), out.ctypes.data_as(C.c_void_p),
+                                         c_out.ctypes.data_as(C.c_void_p), repeat, C.byref(ms))
+        if rc != 0:
+            raise RuntimeError("dsb_fm_rank_batch: " + self.cuda.dsb_last_error().decode())
+        return out, c_out, ms.value
+
+    def exist(self, codes, repeat=1):
+        np = self.np
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        k = self.ek_len()
+        out = np.empty(len(codes) - k + 1, dtype=np.uint8)
+        ms = C.c_float(0)
+        rc = self.cuda.dsb_exist_batch(self.handle, codes.ctypes.data_as(C.c_void_p), C.c_uint64(len(codes)),
+                                       out.ctypes.data_as(C.c_void_p), repeat, C.byref(ms))
+        if rc != 0:
+            raise RuntimeError("dsb_exist_batch: " + self.cuda.dsb_last_error().decode())
+        return out, ms.value
+
+    def ek_len(self):
+        self.host.dsb_ekmer_len.argtypes = [C.c_uint64]
+        return self.host.dsb_ekmer_len(C.c_uint64(self.ek_bytes()))
+
+    def ek_bytes(self):
+        # dsb_host_index.e_kmer_size: see include/dsb_cuda.h (field order is part of the C-ABI)
+        off = 8 + 8 + 6 * 8 + 8 + 8 + 8 + 8 + 8 + 8
+        return C.c_uint64.from_buffer(self.buf, off).value
+
+
+def read_index_files(index_dir):
+    """Raw views of the reference's on-disk index (formats: reference src/idx.c:1103-1160, src/bwt.c:68-104)."""
+    import numpy as np
+    d = {}
+    raw = np.fromfile(os.path.join(index_dir, "deSAMBA.bwt"), dtype=np.uint8)
+    n = int(raw[:8].view(np.uint64)[0])
+    d["bwt_occ"] = raw[8:8 + n]
+    d["rank"] = raw[8 + n:8 + n + 40].view(np.uint64).copy()
+    d["lut"] = raw[8 + n + 40:].view(np.uint64)
+    d["ek0"] = np.fromfile(os.path.join(index_dir, "deSAMBA.exk0"), dtype=np.uint8)
+    d["ek1"] = np.fromfile(os.path.join(index_dir, "deSAMBA.exk1"), dtype=np.uint8)
+    d["ref_bin"] = np.fromfile(os.path.join(index_dir, "deSAMBA.ref_b"), dtype=np.uint8)[8:]
+    unv = np.fromfile(os.path.join(index_dir, "deSAMBA.unv"), dtype=np.uint64)
+    d["n_unitig_file"] = int(unv[0])
+    d["dollar_pos"] = int(unv[0]) - 2              # DOLLOR_POS = unitig_v.n - 1 - 1 (src/idx.c:1128)
+    bits = {0x8000000: (30, 16), 0x10000000: (31, 17), 0x20000000: (32, 17), 0x40000000: (33, 18),
+            0x80000000: (34, 18), 0x100000000: (35, 19), 0x200000000: (36, 19), 0x400000000: (37, 20)}
+    b, k = bits[len(d["ek0"])]
+    d["ek_mask"] = (1 << b) - 1
+    d["k"] = k
+    return d

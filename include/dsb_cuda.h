@@ -126,6 +126,17 @@ int  dsb_slot_timing(dsb_slot *s, float *ms_total, float *ms_exist, float *ms_cl
  * re-run the kernels of the last submitted batch without any host<->device copy. */
 int  dsb_slot_rerun_device(dsb_slot *s);
 
+/* FM rank queries in bulk (one thread per query): out[i] = occ(row[i], c[i]) exactly as the reference's
+ * occ() (src/bwt.c:43-65) returns it, c_out[i] = the symbol used (c[i] == 0xff asks for the symbol at
+ * the row).  Host pointers.  `repeat` >= 1 re-runs the kernel that many times on the device-resident
+ * queries and *ms returns the mean kernel time: this is the FM-search roofline probe of bench.py and the
+ * known-answer entry of the parity tests. */
+int  dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint64_t n, uint64_t *out,
+                       uint8_t *c_out, int repeat, float *ms);
+/* Exist-k-mer probes in bulk for 2-bit coded strings (test / roofline entry): exist[i] for every
+ * k-mer start of codes[0..n), same rule as k_exist.  Host pointers. */
+int  dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist, int repeat, float *ms);
+
 const char *dsb_last_error(void);
 int  dsb_kernel_launch_count(void);   /* kernels launched by this library so far */
 

@@ -248,4 +248,33 @@ int dsb_slot_timing(dsb_slot *s, float *a, float *b, float *c)
 
 int dsb_slot_rerun_device(dsb_slot *s) { return dsb_slot_submit(s, s->n_reads, s->n_bases); }
 
+int dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint64_t n, uint64_t *out, uint8_t *c_out,
+                      int repeat, float *ms)
+{
+    (void)repeat;
+    DsbWork w;
+    memset(&w, 0, sizeof w);
+    w.ix = &ix->v;
+    for (uint64_t i = 0; i < n; i++) {
+        uint8_t cc = c[i];
+        out[i] = dsb_occ(&w, row[i], &cc);
+        c_out[i] = cc;
+    }
+    if (ms) *ms = 0;
+    g_launches++;
+    return 0;
+}
+
+int dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist, int repeat, float *ms)
+{
+    (void)repeat;
+    const uint64_t k = (uint64_t)ix->v.ek_len;
+    if (n < k) return -1;
+    uint32_t p0 = 0, p1 = 0;
+    for (uint64_t i = 0; i + k <= n; i++) exist[i] = dsb_exist_kmer(&ix->v, codes + i, &p0, &p1);
+    if (ms) *ms = 0;
+    g_launches++;
+    return 0;
+}
+
 }  // extern "C"

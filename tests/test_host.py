@@ -1,0 +1,122 @@
+"""Host-side logic without a GPU: the C-ABI libraries load and export what include/*.h declares, and
+the C host code (FASTQ parser, history model, batcher, SAM formatter) reproduces the reference's SAM
+when the kernel source runs on the host simulator (tests/hostsim, test infrastructure)."""
+import ctypes as C
+import gzip
+import os
+import re
+import subprocess
+
+import pytest
+
+from conftest import GOLD, PKG, ROOT, sam_records
+
+SIM = os.path.join(ROOT, "tests", "hostsim", "deSAMBA_hostsim")
+
+
+def declared_functions(header):
+    text = open(os.path.join(ROOT, "include", header)).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(\w+)\s*\([^;{]*\)\s*;", text)))
+
+
+def test_cuda_abi_exports_every_declared_symbol(built):
+    names = declared_functions("dsb_cuda.h")
+    assert "dsb_slot_submit" in names and "dsb_fm_rank_batch" in names and len(names) >= 15
+    lib = C.CDLL(os.path.join(PKG, "lib", "libdsb_cuda.so"))
+    for n in names:
+        assert hasattr(lib, n), n
+
+
+def test_api_exports_exactly_the_reference_symbols(built):
+    names = declared_functions("desamba.h")
+    assert names == ["load_index", "meta_analysis", "read_classify"]
+    lib = C.CDLL(os.path.join(PKG, "lib", "libdesamba.so"))
+    for n in names:
+        assert hasattr(lib, n), n
+
+
+def test_product_library_has_no_oracle_or_simulator_dependency(built):
+    for so in ("libdesamba.so", "libdsb_cuda.so"):
+        out = subprocess.run(["ldd", os.path.join(PKG, "lib", so)], stdout=subprocess.PIPE).stdout.decode()
+        assert "hostsim" not in out and "oracle" not in out
+    # the product CLI aborts loudly without a CUDA device instead of falling back
+    if not os.path.exists("/dev/nvidia0"):
+        r = subprocess.run([os.path.join(PKG, "bin", "deSAMBA"), "classify", os.path.join(GOLD, "nonexistent"), "x.fq"],
+                           stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert r.returncode != 0
+
+
+def run_sim(idx, reads, fmt="SAM", env=None, extra=()):
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run([SIM, "classify", "-f", fmt] + list(extra) + [idx] + list(reads), stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, env=e)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    return r.stdout
+
+
+@pytest.mark.parametrize("name", ["tiny", "mixed"])
+def test_hostsim_cli_equals_reference_golden(name, request):
+    meta = request.getfixturevalue(name)
+    out = run_sim(meta["idx"], [meta["reads"]])
+    assert out == open(os.path.join(GOLD, name + ".sam"), "rb").read()
+
+
+def test_batch_boundaries_and_device_count_do_not_change_results(mixed):
+    want = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
+    assert run_sim(mixed["idx"], [mixed["reads"]], env={"DSB_BATCH_READS": "37"}) == want
+    assert run_sim(mixed["idx"], [mixed["reads"]], env={"DSB_BATCH_BASES": "20000"}) == want
+    assert run_sim(mixed["idx"], [mixed["reads"]], env={"DSB_BATCH_READS": "11", "DSB_HOSTSIM_GPUS": "2"}) == want
+
+
+def test_gzip_and_fasta_inputs(tiny, tmp_path):
+    recs = open(tiny["reads"], "rb").read().split(b"\n")
+    n = 40
+    fq = b"\n".join(recs[:4 * n]) + b"\n"
+    gz = tmp_path / "r.fq.gz"
+    gz.write_bytes(gzip.compress(fq))
+    fa = tmp_path / "r.fa"
+    with open(fa, "wb") as fh:
+        for i in range(n):
+            seq = recs[4 * i + 1]
+            fh.write(b">" + recs[4 * i][1:] + b" some comment\n")
+            for j in range(0, len(seq), 61):          # multi-line FASTA
+                fh.write(seq[j:j + 61] + b"\n")
+    plain = tmp_path / "r.fq"
+    plain.write_bytes(fq)
+    a = run_sim(tiny["idx"], [str(plain)])
+    assert run_sim(tiny["idx"], [str(gz)]) == a
+    assert run_sim(tiny["idx"], [str(fa)]) == a
+    want = sam_records(open(os.path.join(GOLD, "tiny.sam"), "rb").read())
+    got = sam_records(a)
+    assert len(got) == n
+    for k, v in got.items():
+        assert want[k] == v
+
+
+def test_api_read_classify_through_hostsim_library(tiny):
+    """read_classify(): text input, path input, empty input, history carried across calls per thread_id."""
+    import pydsb
+    d = pydsb.Desamba(hostsim=True)
+    d.load_index(tiny["idx"])
+    text = open(tiny["reads"], "rb").read()
+    recs = text.split(b"\n")
+    half = len(recs) // 8 * 4
+    a, b = b"\n".join(recs[:half]) + b"\n", b"\n".join(recs[half:])
+    want = sam_records(open(os.path.join(GOLD, "tiny.sam"), "rb").read())
+    # two consecutive calls on one thread_id == one reference run over the concatenation
+    got = sam_records(d.read_classify(a + b"\0", thread_id=3) + d.read_classify(b, thread_id=3))
+    assert got == want
+    # path input on a fresh thread_id
+    assert sam_records(d.read_classify(tiny["reads"], thread_id=4)) == want
+    # input_n == 0 leaves the outputs alone
+    out, out_n = C.c_void_p(0x1234), C.c_uint64(77)
+    d.lib.read_classify(d.idx, b"", 0, C.byref(out), C.byref(out_n), 0, 1)
+    assert out.value == 0x1234 and out_n.value == 0
+
+
+def test_sam_full_format_carries_seq_and_qual(tiny):
+    out = run_sim(tiny["idx"], [tiny["reads"]], fmt="SAM_FULL").decode().split("\n")
+    prim = [ln.split("\t") for ln in out if ln and not (int(ln.split("\t")[1]) & 0x900)]
+    assert prim and all(len(f[9]) == len(f[10]) and (f[9] == "*" or set(f[10]) == {"I"}) for f in prim)
