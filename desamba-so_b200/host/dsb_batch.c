@@ -64,8 +64,12 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     if (want > have) want = have;
     e->n_gpu = want;
     e->dev = (dsb_index **)dsb_xcalloc((size_t)want, sizeof(dsb_index *));
+    /* DSB_GPU_FIRST: first device ordinal (one-process-per-GPU launchers give each rank its own) */
+    int first = (int)env_u64("DSB_GPU_FIRST", 0);
+    if (first + want > have) first = 0;
     for (int g = 0; g < want; g++)
-        if (dsb_index_upload(&ix->h, g, &e->dev[g]) != 0) dsb_fatal("index upload to GPU %d failed: %s", g, dsb_last_error());
+        if (dsb_index_upload(&ix->h, first + g, &e->dev[g]) != 0)
+            dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
     e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)32 << 20);
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
     return e;

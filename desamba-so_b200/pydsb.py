@@ -197,3 +197,63 @@ def read_index_files(index_dir):
     d["ek_mask"] = (1 << b) - 1
     d["k"] = k
     return d
+
+
+class HostIndex(C.Structure):
+    """dsb_host_index of include/dsb_cuda.h, field for field."""
+    _fields_ = [("bwt_occ", C.c_void_p), ("bwt_bytes", C.c_uint64), ("rank", C.c_uint64 * 6), ("dollar_pos", C.c_uint64),
+                ("hash_index", C.c_void_p), ("sa_taxon", C.c_void_p), ("sa_n", C.c_uint64), ("e_kmer0", C.c_void_p),
+                ("e_kmer1", C.c_void_p), ("e_kmer_size", C.c_uint64), ("unitig", C.c_void_p), ("n_unitig", C.c_uint64),
+                ("ref_pos", C.c_void_p), ("n_ref_pos", C.c_uint64), ("ref_bin", C.c_void_p), ("ref_bin_n", C.c_uint64),
+                ("ref_seq_offset", C.c_void_p), ("ref_seq_len", C.c_void_p), ("n_ref", C.c_uint64), ("q_mem", C.c_void_p),
+                ("q_lv", C.c_void_p), ("filter_min_length", C.c_int32), ("filter_min_score", C.c_int32),
+                ("filter_min_score_lv3", C.c_int32)]
+
+
+class _SyntheticIndex(DeviceIndex):
+    def __init__(self, handle, cuda, keep):
+        import numpy as np
+        self.np = np
+        self.cuda = cuda
+        self.handle = handle
+        self.keep = keep
+
+    def close(self):
+        if self.handle:
+            self.cuda.dsb_index_free(self.handle)
+            self.handle = C.c_void_p()
+
+
+def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3):
+    """A device index whose FM part is a random BWT of n_sym symbols in the reference's 168-byte block layout
+    (counts are consistent inside a block, which is all a rank query reads).  Only dsb_fm_rank_batch is
+    meaningful on it: it exists to measure rank-query throughput on a table far larger than L2."""
+    import numpy as np
+    cuda = load_cuda_layer(hostsim)
+    rng = np.random.default_rng(seed)
+    nb = n_sym // 256
+    blocks = np.zeros((nb, 168), dtype=np.uint8)
+    blocks[:, 40:] = rng.integers(0, 256, size=(nb, 128), dtype=np.uint8) & 0x33   # nibbles in 0..3
+    keep = dict(blocks=blocks, lut=np.zeros((1 << 26) + 1, dtype=np.uint64), sa=np.zeros(8, dtype=np.uint64),
+                ek=np.zeros(0x8000000, dtype=np.uint8), small=np.zeros(64, dtype=np.uint64),
+                q=np.zeros(2400, dtype=np.int32))
+    h = HostIndex()
+    h.bwt_occ = blocks.ctypes.data
+    h.bwt_bytes = nb * 168
+    h.dollar_pos = n_sym + 5
+    h.hash_index = keep["lut"].ctypes.data
+    h.sa_taxon = keep["sa"].ctypes.data
+    h.sa_n = 8
+    h.e_kmer0 = h.e_kmer1 = keep["ek"].ctypes.data
+    h.e_kmer_size = 0x8000000
+    h.unitig = h.ref_pos = h.ref_seq_offset = h.ref_seq_len = keep["small"].ctypes.data
+    h.n_unitig = h.n_ref_pos = h.n_ref = 8
+    h.ref_bin = keep["small"].ctypes.data
+    h.ref_bin_n = 64
+    h.q_mem = keep["q"].ctypes.data
+    h.q_lv = keep["q"].ctypes.data + 8000
+    handle = C.c_void_p()
+    rc = cuda.dsb_index_upload(C.byref(h), dev, C.byref(handle))
+    if rc != 0:
+        raise RuntimeError("dsb_index_upload: " + cuda.dsb_last_error().decode())
+    return _SyntheticIndex(handle, cuda, keep)

@@ -118,7 +118,9 @@ def find_crashers(idx, recs, tmp):
 
 def build(name, log=sys.stderr, golden=True):
     """Returns dict(dir, idx, reads, golden, n_reads, n_bases)."""
-    p = CONFIGS[name]
+    p = dict(CONFIGS[name.split("@")[0]])
+    if "@" in name:                      # "<cfg>@<k>": same genomes, k-th independent read set (bench shards)
+        p["read_seed"] += 1000 * int(name.split("@")[1])
     rd, idx = build_index(p, log)
     d = os.path.join(data_root(), name)
     meta_path = os.path.join(d, "meta.json")
@@ -172,7 +174,7 @@ def build(name, log=sys.stderr, golden=True):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("name", choices=sorted(CONFIGS))
+    ap.add_argument("name")
     ap.add_argument("--no-golden", action="store_true")
     a = ap.parse_args()
     print(json.dumps(build(a.name, golden=not a.no_golden), indent=1))
