@@ -20,9 +20,17 @@
 #if defined(__CUDACC__)
 #define DSB_HD __host__ __device__ __forceinline__
 #define DSB_HDN __host__ __device__ __noinline__
+// helpers that are called from many places: kept out of line on the device so that the classifier's
+// instruction footprint stays small (ncu r01: 52 % of stall samples were instruction-cache misses)
+#if defined(DSB_INLINE_ALL)
+#define DSB_HDO __host__ __device__ __forceinline__
+#else
+#define DSB_HDO __host__ __device__ __noinline__
+#endif
 #else
 #define DSB_HD static inline
 #define DSB_HDN static
+#define DSB_HDO static inline
 #endif
 #if defined(__CUDA_ARCH__)
 #define DSB_DEVICE_CODE 1
@@ -150,7 +158,18 @@ struct DsbScHash {                // seed_con_hash src/cly.h:120-125
 
 struct DsbStats {
     unsigned long long occ, lut, sa, unitig, refpos, ref_bytes, mem_search, map_seed, sdp_win, slow;
+    unsigned long long cyc[8];    // SM cycles per phase (device only; see dsb_counters.phase_cycles)
 };
+
+#if defined(__CUDA_ARCH__)
+#define DSB_PHASE_BEGIN() long long dsb_t0_ = clock64()
+#define DSB_PHASE_BEGIN2() dsb_t0_ = clock64()
+#define DSB_PHASE_END(w, ph) do { const long long t_ = clock64(); (w)->st.cyc[ph] += (unsigned long long)(t_ - dsb_t0_); dsb_t0_ = t_; } while (0)
+#else
+#define DSB_PHASE_BEGIN() ((void)0)
+#define DSB_PHASE_BEGIN2() ((void)0)
+#define DSB_PHASE_END(w, ph) ((void)0)
+#endif
 
 // Everything one warp needs while it owns a read.  Pointers reference the warp's private slice
 // of the global scratch arena (L1/L2 resident while in use).
@@ -222,7 +241,7 @@ DSB_HD uint32_t dsb_nib_eq_count(uint64_t w, uint32_t c, uint32_t n)
 // occ(bt, r, &c): *c == 0xff means "use the symbol at row r" (written back to *c).
 // Returns the count of *c in BWT[0, r)  (r exclusive), or dollar_pos when
 // the symbol at r is '$'.  The caller adds rank[*c].
-DSB_HD uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
+DSB_HDO uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
 {
     const DsbIndexView *ix = w->ix;
     const uint64_t blk = r >> 6;
@@ -274,7 +293,7 @@ DSB_HD uint8_t dsb_ref_base(const DsbIndexView *ix, uint64_t pos)
     return (uint8_t)((v >> ((3 - (uint32_t)(pos & 3)) << 1)) & 3);
 }
 
-DSB_HD void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t length, bool is_forward)
+DSB_HDO void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t length, bool is_forward)
 {
     const DsbIndexView *ix = w->ix;
     w->st.ref_bytes += (length + 3) >> 2;
@@ -302,7 +321,7 @@ DSB_HD void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t 
 // Both strings always have the same length here (every call site passes len, len).
 // Returns the edit distance, or `len` when no alignment with <= 4 edits exists.
 // ------------------------------------------------------------------------------------------
-DSB_HD int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len)
+DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len)
 {
     if (len <= 0) return 0;                   // returns 0 whatever the bytes are
     uint8_t rbuf[8 + DSB_LV_L + 2], qbuf[8 + DSB_LV_L + 2];
@@ -429,7 +448,7 @@ DSB_HD uint8_t dsb_exist_kmer(const DsbIndexView *ix, const uint8_t *s, uint32_t
 // islands (restates search_exist_kmer_M2 src/cly.c:1066-1155 and the `top` marking of
 // get_seed_vector_M2 src/cly.c:1157-1229).  ex[i] = exist bit of k-mer i, n = L-k+1.
 // ------------------------------------------------------------------------------------------
-DSB_HD void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
+DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
 {
     const uint8_t *ex = w->exist[strand];
     const uint32_t n = w->L - (uint32_t)w->ix->ek_len + 1;
@@ -496,7 +515,7 @@ struct DsbSpSet { uint64_t *set; int l, m; };
 
 // insert fails (returns 0) when the row is already present; the list silently empties when
 // full
-DSB_HD int dsb_sp_set_insert(uint64_t node, DsbSpSet *s)
+DSB_HDO int dsb_sp_set_insert(uint64_t node, DsbSpSet *s)
 {
     if (s->l == s->m) s->l = 0;
     uint64_t *set = s->set;
@@ -518,7 +537,7 @@ DSB_HD int dsb_sp_set_insert(uint64_t node, DsbSpSet *s)
 
 // single-row LF walk to the left while the BWT symbol equals the next read base.
 // `str` points at the next base to compare (moving towards index 0).
-DSB_HD void dsb_single_search(DsbWork *w, uint64_t sp, const uint8_t *str, int max_match_len,
+DSB_HDO void dsb_single_search(DsbWork *w, uint64_t sp, const uint8_t *str, int max_match_len,
                               DsbSpSet *sp_set, DsbMem *m)
 {
     const uint64_t *rank = w->ix->rank;
@@ -544,7 +563,7 @@ DSB_HD void dsb_single_search(DsbWork *w, uint64_t sp, const uint8_t *str, int m
 }
 
 // `str` points at the LAST base of the exist-k-mer; pre_v is the value of its last 13 bases.
-DSB_HD int dsb_mem_search(DsbWork *w, const uint8_t *str, uint64_t pre_v, int max_rst, int l_min_mth,
+DSB_HDO int dsb_mem_search(DsbWork *w, const uint8_t *str, uint64_t pre_v, int max_rst, int l_min_mth,
                           int l_max_mth, DsbSpSet *sp_set, DsbMem *mem)
 {
     const uint64_t *rank = w->ix->rank;
@@ -591,7 +610,7 @@ DSB_HD int dsb_mem_search(DsbWork *w, const uint8_t *str, uint64_t pre_v, int ma
 // map_seed :701-934)
 // ------------------------------------------------------------------------------------------
 // returns the unitig index; *global_offset / *uni_offset as in the reference
-DSB_HD uint64_t dsb_get_uni(DsbWork *w, uint64_t bwt_pos, int search_l, uint64_t *global_offset, uint32_t *uni_offset_)
+DSB_HDO uint64_t dsb_get_uni(DsbWork *w, uint64_t bwt_pos, int search_l, uint64_t *global_offset, uint32_t *uni_offset_)
 {
     const DsbIndexView *ix = w->ix;
     const uint64_t sa = ix->sa[bwt_pos >> DSB_SA_OFF];
@@ -617,7 +636,7 @@ DSB_HD uint64_t dsb_get_uni(DsbWork *w, uint64_t bwt_pos, int search_l, uint64_t
 }
 
 // q_b = strand base pointer (index 0 = first base of the strand)
-DSB_HD void dsb_get_new_ed(DsbWork *w, uint32_t *e_d, uint32_t *len_, uint32_t *l_mem_ext, int32_t q_off,
+DSB_HDO void dsb_get_new_ed(DsbWork *w, uint32_t *e_d, uint32_t *len_, uint32_t *l_mem_ext, int32_t q_off,
                            uint64_t t_off, uint32_t l_read, const uint8_t *q_b, bool is_fwd)
 {
     uint8_t q_buff[13], t_buff[13];
@@ -1191,14 +1210,25 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
         for (uint32_t p = lane; p < n_pos; p += 32) kmer[p] = dsb_kmer9(q + p);
         __syncwarp();
-        if (lane == 0) {
-            for (uint32_t p = n_pos; p-- > 0;) {
-                const uint32_t key = kmer[p] & key_mask;
-                next[p] = head[key];
-                head[key] = p + 1;
+        // Buckets must list positions in ascending order (the reference appends to the tail).  32
+        // positions per step, from the highest chunk down: inside a chunk, lanes with the same key
+        // (match_any) link to the next higher lane of their group; the group's highest lane links to
+        // the bucket head left by the chunks above, its lowest lane becomes the new head.
+        for (int32_t cs = (int32_t)((n_pos - 1) & ~31u); cs >= 0; cs -= 32) {
+            const uint32_t p = (uint32_t)cs + lane;
+            const bool valid = p < n_pos;
+            const uint32_t key = valid ? (kmer[p] & key_mask) : (0x80000000u | lane);
+            const uint32_t peers = __match_any_sync(0xffffffffu, key);
+            const uint32_t higher = peers & ~((2u << lane) - 1u);
+            uint32_t nx = 0;
+            if (valid) nx = higher ? ((uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u) : head[key];
+            __syncwarp();
+            if (valid) {
+                next[p] = nx;
+                if ((peers & ((1u << lane) - 1u)) == 0) head[key] = p + 1;
             }
+            __syncwarp();
         }
-        __syncwarp();
 #else
         for (uint32_t i = 0; i <= key_mask; i++) head[i] = 0;
         for (uint32_t p = n_pos; p-- > 0;) {
@@ -1219,6 +1249,20 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
 DSB_HD int dsb_run_len(const uint8_t *q, const uint8_t *t, bool forward, int max)
 {
     int len = 0;
+#if defined(DSB_DEVICE_CODE)
+    if (max > 8) {
+        // 32 positions per step: the first lane whose bases differ (or that lies beyond `max`) ends the run
+        const int lane = (int)(threadIdx.x & 31);
+        for (;;) {
+            const int idx = len + lane;
+            bool ok = false;
+            if (idx < max) ok = forward ? (q[idx] == t[idx]) : (q[-idx] == t[-idx]);
+            const uint32_t m = __ballot_sync(0xffffffffu, ok);
+            if (m != 0xffffffffu) return len + __ffs((int)~m) - 1;
+            len += 32;
+        }
+    }
+#endif
     if (forward) for (; len < max && *q++ == *t++; len++) {}
     else for (; len < max && *q-- == *t--; len++) {}
     return len;
@@ -1238,6 +1282,75 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
     const uint32_t t_kmer_num = t_len - DSB_KMER9 + 1;
     const uint32_t *head = w->h_head[strand], *nxt = w->h_next[strand], *hk = w->h_kmer[strand];
     w->st.sdp_win++;
+#if defined(DSB_DEVICE_CODE)
+    {
+        // Lane-parallel form: lane l owns window k-mer number i = 4 + 4*(base + l).  Every lane walks its
+        // own bucket chain to its first hit (32 dependent-load chains in flight instead of one); hits are
+        // then consumed in (lane, chain) order = the serial order, with all lanes cooperating on the
+        // exact-run extension, so the match-block list is identical to the reference's.
+        const uint32_t lane = threadIdx.x & 31;
+        const uint32_t n_i = (t_kmer_num > 4) ? ((t_kmer_num - 4 + 3) >> 2) : 0;     // i = 4, 8, ... < t_kmer_num
+        for (uint32_t base = 0; base < n_i; base += 32) {
+            const uint32_t mine = base + lane;
+            const int i_l = 4 + 4 * (int)mine;
+            const long off_l = is_forward ? (long)i_l : ((long)t_len - DSB_KMER9 - (long)i_l);
+            uint32_t kmer = 0, node = 0;
+            if (mine < n_i) {
+                kmer = dsb_kmer9(t_str + off_l);
+                node = head[kmer & key_mask];
+                while (node != 0) {
+                    const uint32_t qp = node - 1;
+                    if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
+                    node = nxt[qp];
+                }
+            }
+            uint32_t act = __ballot_sync(0xffffffffu, node != 0);
+            while (act) {
+                const int l = __ffs((int)act) - 1;
+                const int i = 4 + 4 * (int)(base + (uint32_t)l);
+                const long c_off = is_forward ? (long)i : ((long)t_len - DSB_KMER9 - (long)i);
+                const uint8_t *c_t_str = t_str + c_off;
+                for (;;) {
+                    const uint32_t n_l = __shfl_sync(0xffffffffu, node, l);
+                    if (n_l == 0) break;
+                    const uint32_t q_pos = n_l - 1;
+                    if (is_forward) {
+                        const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, 4);
+                        if (back_len < 4 || i == 4) {
+                            uint32_t max_search = q_ed - q_pos - 1;
+                            max_search = DSB_MIN(max_search, t_len - (uint32_t)i - 1) + DSB_OVER_SEARCH;
+                            const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, (int)max_search);
+                            const int total_len = back_len + forward_len + 1;
+                            if (total_len >= 4)
+                                dsb_push_sms(w, (uint32_t)(i - back_len) + t_st, q_pos - (uint32_t)back_len, (uint32_t)total_len);
+                        }
+                    } else {
+                        const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, 4);
+                        if (forward_len < 4 || i == 4) {
+                            uint32_t max_search = q_pos;
+                            max_search = (uint32_t)(DSB_MIN((long)max_search, c_off)) + DSB_OVER_SEARCH;
+                            const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, (int)max_search);
+                            const int total_len = back_len + forward_len + 1;
+                            if (total_len >= 4)
+                                dsb_push_sms(w, (uint32_t)(c_off - back_len + (long)t_st), q_pos - (uint32_t)back_len, (uint32_t)total_len);
+                        }
+                    }
+                    if ((int)lane == l) {                     // the owner moves to its next hit
+                        node = nxt[q_pos];
+                        while (node != 0) {
+                            const uint32_t qp = node - 1;
+                            if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
+                            node = nxt[qp];
+                        }
+                    }
+                    __syncwarp();
+                }
+                act &= ~(1u << l);
+            }
+        }
+        return;
+    }
+#endif
     if (is_forward) {
         for (int i = 4; (uint32_t)i < t_kmer_num; i += 4) {
             const uint8_t *c_t_str = t_str + i;
@@ -1288,7 +1401,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
 // diagonal hash of chain ends (restates sc_hash_idx src/cly.c:1686-1705) and chain merging
 // (combine_chain :1758-1803)
 // ------------------------------------------------------------------------------------------
-DSB_HD void dsb_sc_hash_idx(DsbWork *w)
+DSB_HDO void dsb_sc_hash_idx(DsbWork *w)
 {
     DsbScHash *h = w->sc_hash;
     for (int i = 0; i < 256; i++) { h[i].next = 0; h[i].seed_ID = 0; h[i].s_or_e = 0; }
@@ -1307,7 +1420,7 @@ DSB_HD void dsb_sc_hash_idx(DsbWork *w)
 }
 
 // returns the index of the absorbed chain or -1
-DSB_HD int dsb_combine_chain(DsbWork *w, int chain_ID, int dis, bool isleft, int c_q_pos)
+DSB_HDO int dsb_combine_chain(DsbWork *w, int chain_ID, int dis, bool isleft, int c_q_pos)
 {
     const DsbScHash *h = w->sc_hash;
     uint16_t key = (uint16_t)(dis & 0xff);
@@ -1389,6 +1502,32 @@ DSB_HDN int dsb_sdp_middle(DsbWork *w, int32_t c_a, const uint8_t *q_str, int st
                     int max_score = (int)c_spd->len;
                     const uint32_t max_q = c_spd->q_pos + DSB_SMS_OVERLAP;
                     const uint32_t max_t = c_spd->t_pos + DSB_SMS_OVERLAP;
+#if defined(DSB_DEVICE_CODE)
+                    {   // predecessors spread over the lanes; max is order-independent
+                        const int32_t lane = (int32_t)(threadIdx.x & 31);
+                        const uint32_t c_len = c_spd->len, c_q = c_spd->q_pos, c_t = c_spd->t_pos;
+                        for (int32_t top = (int32_t)ci - 1; top >= 0; top -= 32) {
+                            const int32_t pi = top - lane;
+                            if (pi < 0) continue;
+                            const DsbSms pv = S[pi];
+                            const int pre_q_ed = (int)(pv.q_pos + pv.len + DSB_KMER9 - 1);
+                            const int pre_t_ed = (int)(pv.t_pos + pv.len + DSB_KMER9 - 1);
+                            if ((uint32_t)pre_q_ed > max_q) continue;
+                            if ((uint32_t)pre_t_ed > max_t) continue;
+                            const int indel = (int)(pv.q_pos - pv.t_pos - (max_q - max_t));
+                            const int ABS_indel = DSB_ABS(indel);
+                            if (ABS_indel > 200) continue;
+                            int new_score = (int)(pv.score + c_len - (uint32_t)(ABS_indel >> 3));
+                            if ((uint32_t)pre_q_ed > c_q || (uint32_t)pre_t_ed > c_t) {
+                                const int overlap_q = (int)((uint32_t)pre_q_ed - c_q);
+                                const int overlap_t = (int)((uint32_t)pre_t_ed - c_t);
+                                new_score -= DSB_MAX(overlap_q, overlap_t);
+                            }
+                            max_score = DSB_MAX(max_score, new_score);
+                        }
+                        max_score = __reduce_max_sync(0xffffffffu, max_score);
+                    }
+#else
                     for (int32_t pi = (int32_t)ci - 1; pi >= 0; pi--) {
                         const DsbSms *p = S + pi;
                         const int pre_q_ed = (int)(p->q_pos + p->len + DSB_KMER9 - 1);
@@ -1406,6 +1545,7 @@ DSB_HDN int dsb_sdp_middle(DsbWork *w, int32_t c_a, const uint8_t *q_str, int st
                         }
                         max_score = DSB_MAX(max_score, new_score);
                     }
+#endif
                     score = DSB_MAX(max_score, score);
                     c_spd->score = (uint32_t)max_score;
                 }
@@ -1464,6 +1604,47 @@ DSB_HDN int dsb_sdp_right(DsbWork *w, const uint8_t *q_str, int strand, int key_
         int max_score = (int)c_sms->len;
         const uint32_t max_pre_q = c_sms->q_pos + DSB_SMS_OVERLAP;
         const uint32_t max_pre_t = c_sms->t_pos + DSB_SMS_OVERLAP;
+#if defined(DSB_DEVICE_CODE)
+        {   // lanes take 32 predecessors at a time; the reference's `break` cuts the scan at the first
+            // (highest-index) predecessor that passes both overlap tests and lies > 600 bp back
+            const int32_t lane = (int32_t)(threadIdx.x & 31);
+            const uint32_t c_len = c_sms->len, c_q = c_sms->q_pos, c_t = c_sms->t_pos;
+            for (int32_t top = (int32_t)current_sms - 2; top >= 0; top -= 32) {
+                const int32_t pi = top - lane;
+                bool brk = false;
+                int cand = -2147483647 - 1;
+                if (pi >= 0) {
+                    const DsbSms pv = w->sms[pi];
+                    const int pre_q_ed = (int)(pv.q_pos + pv.len + DSB_KMER9 - 1);
+                    const int pre_t_ed = (int)(pv.t_pos + pv.len + DSB_KMER9 - 1);
+                    if (!((uint32_t)pre_q_ed > max_pre_q) && !((uint32_t)pre_t_ed > max_pre_t)) {
+                        if (pv.t_pos + 600 < max_pre_t) brk = true;
+                        else {
+                            const int indel = (int)(pv.q_pos - pv.t_pos - (max_pre_q - max_pre_t));
+                            const int ABS_indel = DSB_ABS(indel);
+                            if (!(ABS_indel > 200)) {
+                                int new_score = (int)(pv.score + c_len - (uint32_t)(ABS_indel >> 3));
+                                if ((uint32_t)pre_q_ed > c_q || (uint32_t)pre_t_ed > c_t) {
+                                    const int overlap_q = (int)((uint32_t)pre_q_ed - c_q);
+                                    const int overlap_t = (int)((uint32_t)pre_t_ed - c_t);
+                                    new_score -= DSB_MAX(overlap_q, overlap_t);
+                                }
+                                cand = new_score;
+                            }
+                        }
+                    }
+                }
+                const uint32_t bm = __ballot_sync(0xffffffffu, brk);
+                if (bm) {
+                    const int32_t cut = __ffs((int)bm) - 1;          // lanes below `cut` were scanned before the break
+                    if (lane < cut) max_score = DSB_MAX(max_score, cand);
+                    break;
+                }
+                max_score = DSB_MAX(max_score, cand);
+            }
+            max_score = __reduce_max_sync(0xffffffffu, max_score);
+        }
+#else
         for (int32_t pi = (int32_t)current_sms - 2; pi >= 0; pi--) {
             const DsbSms *p = w->sms + pi;
             const int pre_q_ed = (int)(p->q_pos + p->len + DSB_KMER9 - 1);
@@ -1482,6 +1663,7 @@ DSB_HDN int dsb_sdp_right(DsbWork *w, const uint8_t *q_str, int strand, int key_
             }
             max_score = DSB_MAX(max_score, new_score);
         }
+#endif
         c_sms->score = (uint32_t)max_score;
         if (c_sms->len >= 8) {
             const uint32_t cs_len = c_sms->len;     // c_sms is invalidated by the nested sdp_middle
@@ -1561,6 +1743,44 @@ DSB_HDN int dsb_sdp_left(DsbWork *w, const uint8_t *q_str, int strand, int key_l
         int max_score = (int)c_sms->len;
         const uint32_t min_pre_q = c_sms->q_pos + c_sms->len - DSB_SMS_OVERLAP + DSB_KMER9 - 1;
         const uint32_t min_pre_t = c_sms->t_pos + c_sms->len - DSB_SMS_OVERLAP + DSB_KMER9 - 1;
+#if defined(DSB_DEVICE_CODE)
+        {
+            const int32_t lane = (int32_t)(threadIdx.x & 31);
+            const uint32_t c_len = c_sms->len;
+            for (int32_t top = (int32_t)current_sms - 2; top >= 0; top -= 32) {
+                const int32_t pi = top - lane;
+                bool brk = false;
+                int cand = -2147483647 - 1;
+                if (pi >= 0) {
+                    const DsbSms pv = w->sms[pi];
+                    if (!(pv.q_pos < min_pre_q) && !(pv.t_pos < min_pre_t)) {
+                        if (min_pre_t + 600 < pv.t_pos) brk = true;
+                        else {
+                            const int indel = (int)(pv.q_pos - pv.t_pos - (min_pre_q - min_pre_t));
+                            const int ABS_indel = DSB_ABS(indel);
+                            if (!(ABS_indel > 200)) {
+                                int new_score = (int)(pv.score + c_len - (uint32_t)(ABS_indel >> 3));
+                                if (min_pre_q + DSB_SMS_OVERLAP > pv.q_pos || min_pre_t + DSB_SMS_OVERLAP > pv.t_pos) {
+                                    const int overlap_q = (int)(min_pre_q + DSB_SMS_OVERLAP - pv.q_pos);
+                                    const int overlap_t = (int)(min_pre_t + DSB_SMS_OVERLAP - pv.t_pos);
+                                    new_score -= DSB_MAX(overlap_q, overlap_t);
+                                }
+                                cand = new_score;
+                            }
+                        }
+                    }
+                }
+                const uint32_t bm = __ballot_sync(0xffffffffu, brk);
+                if (bm) {
+                    const int32_t cut = __ffs((int)bm) - 1;
+                    if (lane < cut) max_score = DSB_MAX(max_score, cand);
+                    break;
+                }
+                max_score = DSB_MAX(max_score, cand);
+            }
+            max_score = __reduce_max_sync(0xffffffffu, max_score);
+        }
+#else
         for (int32_t pi = (int32_t)current_sms - 2; pi >= 0; pi--) {
             const DsbSms *p = w->sms + pi;
             if (p->q_pos < min_pre_q) continue;
@@ -1577,6 +1797,7 @@ DSB_HDN int dsb_sdp_left(DsbWork *w, const uint8_t *q_str, int strand, int key_l
             }
             max_score = DSB_MAX(max_score, new_score);
         }
+#endif
         c_sms->score = (uint32_t)max_score;
         if (c_sms->len >= 8) {
             const uint32_t cs_len = c_sms->len;
@@ -1608,7 +1829,9 @@ DSB_HDN int dsb_sdp_left(DsbWork *w, const uint8_t *q_str, int strand, int key_l
 
 DSB_HDN void dsb_get_score(DsbWork *w)
 {
+    DSB_PHASE_BEGIN();
     const int key_len = dsb_build_read_hash(w);
+    DSB_PHASE_END(w, 4);
     for (uint32_t i = 0; i < w->n_chain; i++) {
         if (w->chains[i].sum_score == 0) continue;
         const int strand = (w->chains[i].direction == DSB_FORWARD) ? 0 : 1;
@@ -1623,6 +1846,7 @@ DSB_HDN void dsb_get_score(DsbWork *w)
         w->chains[i].sum_score = (uint32_t)score;
         if (w->overflow) return;
     }
+    DSB_PHASE_END(w, 5);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1642,6 +1866,7 @@ DSB_HDN void dsb_delete_small_score_rst(DsbWork *w)
     dsb_sc_hash_idx(w);
     dsb_get_score(w);
     if (w->overflow) return;
+    DSB_PHASE_BEGIN();
     const uint32_t n = w->n_chain;
     DsbChain *C = w->chains;
     if (n > 1) {
@@ -1725,6 +1950,7 @@ DSB_HDN void dsb_delete_small_score_rst(DsbWork *w)
     for (; k < n; k++)
         if (C[k].sum_score == 0) break;
     w->n_chain = k;
+    DSB_PHASE_END(w, 6);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1791,8 +2017,10 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     w->n_chain = 0;
     w->fast_classify = 1;
     if (w->L < 40) return;                                                  // MIN_READ_LEN
+    DSB_PHASE_BEGIN();
     dsb_islands(w, 0);
     dsb_islands(w, 1);
+    DSB_PHASE_END(w, 0);
     // search_dir[0] = forward unless the reverse strand scores strictly higher
     int dir0 = 0, dir1 = 1;
     if (w->total_score[0] < w->total_score[1]) { dir0 = 1; dir1 = 0; }
@@ -1800,7 +2028,9 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     const bool both_direction = ((s0 - s1) <= (s0 >> 3));
     dsb_fast_classify(w, dir0);
     if (both_direction) dsb_fast_classify(w, dir1);
+    DSB_PHASE_END(w, 1);
     dsb_resolve_tree(w);
+    DSB_PHASE_END(w, 2);
     bool run_slow_mode = false;
     if (w->n_chain <= 0)
         run_slow_mode = true;
@@ -1817,9 +2047,12 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
             dsb_slow_classify(w, dir1);                                     // appends
             dsb_resolve_tree(w);
         }
+        DSB_PHASE_END(w, 3);
     }
     if (w->overflow) return;
     dsb_delete_small_score_rst(w);
     if (w->overflow) return;
+    DSB_PHASE_BEGIN2();
     dsb_detect_primary(w);
+    DSB_PHASE_END(w, 6);
 }

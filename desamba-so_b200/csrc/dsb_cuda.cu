@@ -211,6 +211,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
             DSB_ADD(ref_window_bytes, w.st.ref_bytes); DSB_ADD(mem_searches, w.st.mem_search);
             DSB_ADD(map_seeds, w.st.map_seed); DSB_ADD(sdp_windows, w.st.sdp_win);
             DSB_ADD(anchors, w.n_anchor); DSB_ADD(slow_reads, w.st.slow);
+            for (int ph = 0; ph < 8; ph++) DSB_ADD(phase_cycles[ph], w.st.cyc[ph]);
 #undef DSB_ADD
         }
         __syncwarp();

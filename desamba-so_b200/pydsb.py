@@ -11,7 +11,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_DIR = os.path.join(HERE, "lib")
+LIB_DIR = os.environ.get("DSB_LIB_DIR") or os.path.join(HERE, "lib")     # DSB_LIB_DIR: A/B builds of the CUDA layer
 
 API_SYMBOLS = ["load_index", "read_classify", "meta_analysis"]
 CUDA_SYMBOLS = ["dsb_gpu_count", "dsb_index_upload", "dsb_index_free", "dsb_index_device_bytes", "dsb_slot_create",
@@ -27,10 +27,13 @@ HOST_SYMBOLS = ["dsb_index_load", "dsb_index_release_bulk", "dsb_index_destroy",
 class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "exist_probes0", "exist_probes1", "occ_queries", "lut_lookups", "sa_lookups", "unitig_reads", "refpos_reads",
-        "ref_window_bytes", "mem_searches", "map_seeds", "sdp_windows", "anchors", "slow_reads")]
+        "ref_window_bytes", "mem_searches", "map_seeds", "sdp_windows", "anchors", "slow_reads")] + [
+        ("phase_cycles", C.c_uint64 * 8)]
 
     def as_dict(self):
-        return {n: int(getattr(self, n)) for n, _ in self._fields_}
+        d = {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "phase_cycles"}
+        d["phase_cycles"] = [int(x) for x in self.phase_cycles]
+        return d
 
 
 class ReadDesc(C.Structure):

@@ -101,6 +101,10 @@ typedef struct dsb_counters {
     uint64_t unitig_reads, refpos_reads;
     uint64_t ref_window_bytes;             /* bytes of 2-bit reference fetched */
     uint64_t mem_searches, map_seeds, sdp_windows, anchors, slow_reads;
+    /* SM clock cycles the classify kernel's warps spent per phase (profiling aid; lane 0 of each warp):
+     * 0 islands, 1 fast seeding, 2 chaining, 3 slow seeding, 4 read 9-mer table, 5 chain scoring,
+     * 6 filters + primary, 7 result write-back */
+    uint64_t phase_cycles[8];
 } dsb_counters;
 
 typedef struct dsb_slot dsb_slot;  /* one CUDA stream + pinned staging + device scratch */
