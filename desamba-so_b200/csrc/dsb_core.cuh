@@ -156,6 +156,18 @@ struct DsbScHash {                // seed_con_hash src/cly.h:120-125
     uint8_t  pad;
 };
 
+// One top island handed to one lane by the fast seeding stage (see dsb_fast_seeding)
+struct DsbJob {
+    uint32_t strand_ci;           // bit 31 strand (0 forward, 1 reverse), bits 0-30 island index
+    uint32_t start;               // first anchor of this island in the owning lane's staging area
+    uint32_t count;               // anchors it produced
+    uint16_t lane;                // which lane's staging area
+    uint16_t skip;                // the island ended with max_score > 512: the serial loop skips island ci+1
+};
+
+#define DSB_LANE_MEMS 8           // MEM slots of a lane working alone (fast mode keeps <= 2 rows per search)
+#define DSB_LANE_PRIV_BYTES (512 * 8 + DSB_LANE_MEMS * 32)
+
 struct DsbStats {
     unsigned long long occ, lut, sa, unitig, refpos, ref_bytes, mem_search, map_seed, sdp_win, slow;
     unsigned long long cyc[8];    // SM cycles per phase (device only; see dsb_counters.phase_cycles)
@@ -204,6 +216,14 @@ struct DsbWork {
     uint8_t *ref_ext;             // 1000+64+64 : right / left window
     uint32_t fast_classify;
     uint32_t overflow;            // set when an arena was too small -> batch is re-run bigger
+    // fast seeding: islands are independent work items, one lane each (dsb_fast_seeding)
+    uint32_t solo;                // 1 while this lane runs an island on its own (no warp-collective code)
+    uint32_t *warp_ctr;           // the warp's job counter (shared memory on the device)
+    DsbJob *jobs;
+    uint32_t cap_jobs;
+    DsbAnchor *stage;             // 32 lanes x cap_stage anchors
+    uint32_t cap_stage;
+    uint8_t *lane_priv;           // 32 x DSB_LANE_PRIV_BYTES: a lane's own SP_SET + MEM slots
     DsbStats st;
 };
 
@@ -300,7 +320,7 @@ DSB_HDO void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t
 #if defined(DSB_DEVICE_CODE)
     // Short fetches (the 12-base LV windows) land in thread-private arrays, so every lane fills its
     // own copy; long windows always land in the warp's scratch slice and are spread over the lanes.
-    if (length <= 16) {
+    if (length <= 16 || w->solo) {
         for (uint32_t k = 0; k < length; k++)
             dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
         return;
@@ -511,7 +531,7 @@ DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
 // FM seeding (restates sp_set_insert src/cly.c:1281-1293, bwt_single_search :1339-1378,
 // bwt_MEM_search :1383-1442)
 // ------------------------------------------------------------------------------------------
-struct DsbSpSet { uint64_t *set; int l, m; };
+struct DsbSpSet { uint64_t *set; int l, m; int solo; };
 
 // insert fails (returns 0) when the row is already present; the list silently empties when
 // full
@@ -520,12 +540,18 @@ DSB_HDO int dsb_sp_set_insert(uint64_t node, DsbSpSet *s)
     if (s->l == s->m) s->l = 0;
     uint64_t *set = s->set;
 #if defined(DSB_DEVICE_CODE)
-    const uint32_t lane = threadIdx.x & 31;
-    bool found = false;
-    for (int i = lane; i < s->l; i += 32) found |= (set[i] == node);
-    if (__any_sync(0xffffffffu, found)) return 0;
-    if (lane == 0) set[s->l] = node;
-    __syncwarp();
+    if (s->solo) {
+        for (int i = 0; i < s->l; i++)
+            if (set[i] == node) return 0;
+        set[s->l] = node;
+    } else {
+        const uint32_t lane = threadIdx.x & 31;
+        bool found = false;
+        for (int i = lane; i < s->l; i += 32) found |= (set[i] == node);
+        if (__any_sync(0xffffffffu, found)) return 0;
+        if (lane == 0) set[s->l] = node;
+        __syncwarp();
+    }
 #else
     for (int i = 0; i < s->l; i++)
         if (set[i] == node) return 0;
@@ -859,45 +885,152 @@ DSB_HD void dsb_mark_useless(DsbWork *w, uint32_t a_b, uint32_t a_e)
     for (uint32_t i = a_b; i < a_e; i++) w->anchors[i].useless = (w->anchors[i].score < top_score) ? 1 : 0;
 }
 
-// strand: 0 forward, 1 reverse (index into w->seeds / bin halves)
-DSB_HDN void dsb_fast_classify(DsbWork *w, int strand)
+// One top island of fast_classify (the body of the reference's loop over `c_i`, src/cly.c:1489-1538).
+// Islands are independent of each other: SP_SET restarts empty for each one and the anchors are
+// only appended.  The single coupling is `max_score > 512` making the serial loop skip island
+// ci+1; it is returned as a flag and applied when the islands' anchors are merged in order.
+// Pushes into w->anchors / w->n_anchor (whatever they currently point at).
+DSB_HDN uint32_t dsb_fast_island(DsbWork *w, int strand, uint32_t ci, DsbSpSet *sp_set, DsbMem *m_r)
 {
     const int l_ek = w->ix->ek_len;
     const int min_index = 21 - l_ek;                      // MIN_MEM_LEN_FAST - l_ek
     const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
     const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
-    DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX};
-    DsbMem *m_r = w->mems;
-    const DsbSeed *sv = w->seeds[strand];
-    const uint32_t nsv = w->n_seeds[strand];
-    for (uint32_t ci = 0; ci < nsv; ci++) {
-        if (sv[ci].top == 0) continue;
-        sp_set.l = 0;
-        const uint32_t a_b_idx = w->n_anchor;
-        for (int j = (int)sv[ci].len - 1; j >= min_index;) {
-            const int kmer_index = (int)sv[ci].offset + j;
-            const int string_index = kmer_index + l_ek - 1;
-            const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
-            const int n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
-            DSB_TRACE("FAST strand=%d island=%u j=%d sidx=%d n_mem=%d\n", strand, ci, j, string_index, n_mem);
-            if (n_mem == 0) { j -= 2; continue; }
-            j -= 3;
-            int max_score = 0;
-            for (int mi = 0; mi < n_mem; mi++) {
-                m_r[mi].read_offset = string_index - m_r[mi].match_len;
-                const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, direction);
-                DSB_TRACE("  MEM len=%d roff=%d sp=%llu score=%d\n", m_r[mi].match_len, m_r[mi].read_offset,
-                          (unsigned long long)m_r[mi].sp, c_score);
-                max_score = DSB_MAX(c_score, max_score);
-            }
-            if (max_score > 35) j -= 7;
-            if (max_score > 256) {
-                if (max_score > 512) ci++;
-                break;
-            }
+    const DsbSeed sd = w->seeds[strand][ci];
+    uint32_t skip_next = 0;
+    sp_set->l = 0;
+    const uint32_t a_b_idx = w->n_anchor;
+    for (int j = (int)sd.len - 1; j >= min_index;) {
+        const int kmer_index = (int)sd.offset + j;
+        const int string_index = kmer_index + l_ek - 1;
+        const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
+        const int n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, sp_set, m_r);
+        DSB_TRACE("FAST strand=%d island=%u j=%d sidx=%d n_mem=%d\n", strand, ci, j, string_index, n_mem);
+        if (n_mem == 0) { j -= 2; continue; }
+        j -= 3;
+        int max_score = 0;
+        for (int mi = 0; mi < n_mem; mi++) {
+            m_r[mi].read_offset = string_index - m_r[mi].match_len;
+            const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, direction);
+            DSB_TRACE("  MEM len=%d roff=%d sp=%llu score=%d\n", m_r[mi].match_len, m_r[mi].read_offset,
+                      (unsigned long long)m_r[mi].sp, c_score);
+            max_score = DSB_MAX(c_score, max_score);
         }
-        dsb_mark_useless(w, a_b_idx, w->n_anchor);
+        if (max_score > 35) j -= 7;
+        if (max_score > 256) {
+            if (max_score > 512) skip_next = 1;
+            break;
+        }
     }
+    dsb_mark_useless(w, a_b_idx, w->n_anchor);
+    return skip_next;
+}
+
+// fast_classify over one or two strands (src/cly.c:1473-1541, called at :3093-3095).
+// Stage 1 lists the top islands in the serial order (dir0's, then dir1's).  Stage 2 runs them as
+// independent jobs, ONE LANE PER ISLAND on the device (each lane pulls the next job from the warp's
+// counter and works on private SP_SET / MEM slots / anchor staging; 32 dependent FM walks are in
+// flight per warp instead of one); the host build runs the same jobs one after the other, cycling
+// through the 32 staging areas so that the merge below is exercised identically.  Stage 3 appends
+// the staged anchors in job order and drops the islands the serial loop would have skipped.
+DSB_HDN void dsb_fast_seeding(DsbWork *w, int dir0, int dir1 /* -1: one strand only */)
+{
+    DsbJob *jobs = w->jobs;
+    uint32_t n_jobs = 0;
+    for (int pass = 0; pass < 2; pass++) {
+        const int strand = pass ? dir1 : dir0;
+        if (strand < 0) continue;
+        const DsbSeed *sv = w->seeds[strand];
+        const uint32_t nsv = w->n_seeds[strand];
+        for (uint32_t ci = 0; ci < nsv; ci++) {
+            if (sv[ci].top == 0) continue;
+            if (n_jobs >= w->cap_jobs) { w->overflow = 1; return; }
+            jobs[n_jobs].strand_ci = ((uint32_t)strand << 31) | ci;
+            n_jobs++;
+        }
+    }
+    if (n_jobs == 0) return;
+    DsbAnchor *const main_anchors = w->anchors;
+    const uint32_t main_n = w->n_anchor, main_cap = w->cap_anchor;
+#if defined(DSB_DEVICE_CODE)
+    {
+        const uint32_t lane = threadIdx.x & 31;
+        __syncwarp();                                     // the job list (written by every lane alike) is complete
+        if (lane == 0) *w->warp_ctr = 0;
+        __syncwarp();
+        const DsbStats snap = w->st;
+        uint8_t *priv = w->lane_priv + (size_t)lane * DSB_LANE_PRIV_BYTES;
+        DsbSpSet sp_set = {(uint64_t *)priv, 0, DSB_SP_SET_MAX, 1};
+        DsbMem *m_r = (DsbMem *)(priv + 512 * 8);
+        w->anchors = w->stage + (size_t)lane * w->cap_stage;
+        w->cap_anchor = w->cap_stage;
+        w->n_anchor = 0;
+        w->solo = 1;
+        for (;;) {
+            const uint32_t j = atomicAdd(w->warp_ctr, 1u);
+            if (j >= n_jobs) break;
+            const uint32_t key = jobs[j].strand_ci;
+            const uint32_t start = w->n_anchor;
+            const uint32_t skip = dsb_fast_island(w, (int)(key >> 31), key & 0x7fffffffu, &sp_set, m_r);
+            jobs[j].start = start;
+            jobs[j].count = w->n_anchor - start;
+            jobs[j].lane = (uint16_t)lane;
+            jobs[j].skip = (uint16_t)skip;
+        }
+        w->solo = 0;
+        __syncwarp();
+        // every lane counted its own work: fold the counters back into the warp-uniform totals
+#define DSB_FOLD(f) w->st.f = snap.f + __reduce_add_sync(0xffffffffu, (unsigned)(w->st.f - snap.f))
+        DSB_FOLD(occ); DSB_FOLD(lut); DSB_FOLD(sa); DSB_FOLD(unitig); DSB_FOLD(refpos); DSB_FOLD(ref_bytes);
+        DSB_FOLD(mem_search); DSB_FOLD(map_seed);
+#undef DSB_FOLD
+        w->overflow = __any_sync(0xffffffffu, w->overflow != 0) ? 1u : 0u;
+    }
+#else
+    {
+        uint32_t n_priv[32];
+        for (int l = 0; l < 32; l++) n_priv[l] = 0;
+        DsbSpSet sp_set = {(uint64_t *)w->lane_priv, 0, DSB_SP_SET_MAX, 1};
+        DsbMem *m_r = (DsbMem *)(w->lane_priv + 512 * 8);
+        for (uint32_t j = 0; j < n_jobs; j++) {
+            const uint32_t lane = (j * 7u) & 31u;         // any assignment must give the same result
+            const uint32_t key = jobs[j].strand_ci;
+            w->anchors = w->stage + (size_t)lane * w->cap_stage;
+            w->cap_anchor = w->cap_stage;
+            w->n_anchor = n_priv[lane];
+            const uint32_t start = w->n_anchor;
+            const uint32_t skip = dsb_fast_island(w, (int)(key >> 31), key & 0x7fffffffu, &sp_set, m_r);
+            jobs[j].start = start;
+            jobs[j].count = w->n_anchor - start;
+            jobs[j].lane = (uint16_t)lane;
+            jobs[j].skip = (uint16_t)skip;
+            n_priv[lane] = w->n_anchor;
+        }
+    }
+#endif
+    w->anchors = main_anchors;
+    w->n_anchor = main_n;
+    w->cap_anchor = main_cap;
+    if (w->overflow) return;
+    uint32_t skip_key = 0xffffffffu;
+    for (uint32_t j = 0; j < n_jobs; j++) {
+        const DsbJob jb = jobs[j];
+        if (jb.strand_ci == skip_key) { skip_key = 0xffffffffu; continue; }   // `ci++` of src/cly.c:1533
+        skip_key = jb.skip ? jb.strand_ci + 1 : 0xffffffffu;
+        if (jb.count == 0) continue;
+        if (w->n_anchor + jb.count > w->cap_anchor) { w->overflow = 1; return; }
+        const DsbAnchor *src = w->stage + (size_t)jb.lane * w->cap_stage + jb.start;
+        DsbAnchor *dst = w->anchors + w->n_anchor;
+#if defined(DSB_DEVICE_CODE)
+        for (uint32_t k = threadIdx.x & 31; k < jb.count; k += 32) dst[k] = src[k];
+#else
+        for (uint32_t k = 0; k < jb.count; k++) dst[k] = src[k];
+#endif
+        w->n_anchor += jb.count;
+    }
+#if defined(DSB_DEVICE_CODE)
+    __syncwarp();
+#endif
 }
 
 // stable insertion sort of the MEM list by match_len descending: equivalent to the reference's
@@ -917,7 +1050,7 @@ DSB_HDN void dsb_slow_classify(DsbWork *w, int strand)
     const int l_ek = w->ix->ek_len;
     const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
     const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
-    DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX};
+    DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX, 0};
     DsbMem *mem_rst = w->mems;
     const DsbSeed *sv = w->seeds[strand];
     const uint32_t nsv = w->n_seeds[strand];
@@ -2026,8 +2159,7 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     if (w->total_score[0] < w->total_score[1]) { dir0 = 1; dir1 = 0; }
     const uint32_t s0 = w->total_score[dir0], s1 = w->total_score[dir1];
     const bool both_direction = ((s0 - s1) <= (s0 >> 3));
-    dsb_fast_classify(w, dir0);
-    if (both_direction) dsb_fast_classify(w, dir1);
+    dsb_fast_seeding(w, dir0, both_direction ? dir1 : -1);
     DSB_PHASE_END(w, 1);
     dsb_resolve_tree(w);
     DSB_PHASE_END(w, 2);

@@ -158,12 +158,14 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
     const __grid_constant__ DsbScratchDims dims, dsb_read_result *__restrict__ results, dsb_hit *__restrict__ hits,
     uint32_t cap_hits, uint32_t n_reads, DsbCtrl *ctrl)
 {
+    __shared__ uint32_t s_job_ctr[DSB_CLASSIFY_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     DsbWork w;
     memset(&w, 0, sizeof w);
     w.ix = &ix;
     dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
+    w.warp_ctr = &s_job_ctr[threadIdx.x >> 5];
     for (;;) {
         uint32_t slot = 0;
         if (lane == 0) slot = atomicAdd(&ctrl->next_read, 1u);

@@ -41,9 +41,11 @@ struct DsbScratchDims {
     uint32_t cap_anchor;    // anchors == chains == sort buffers capacity
     uint32_t cap_sms;
     uint32_t head_entries;  // 2^key_len for Lmax
+    uint32_t cap_jobs;      // top islands of both strands (<= L/100 + 1 each)
+    uint32_t cap_stage;     // anchors one lane may stage during fast seeding
     // byte offsets inside a slice
     size_t o_seeds0, o_seeds1, o_anchors, o_anchors_tmp, o_chains, o_chains_tmp, o_sort_a, o_sort_b, o_score_v,
-        o_sp_set, o_mems, o_sms, o_head0, o_head1, o_next0, o_next1, o_kmer0, o_kmer1, o_sc_hash, o_ref_mid, o_ref_ext;
+        o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms, o_head0, o_head1, o_next0, o_next1, o_kmer0, o_kmer1, o_sc_hash, o_ref_mid, o_ref_ext;
     size_t bytes;           // slice size (multiple of 256)
 };
 
@@ -74,6 +76,11 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     DSB_TAKE(o_score_v, 1024 * 4);
     DSB_TAKE(o_sp_set, 512 * 8);
     DSB_TAKE(o_mems, 256 * sizeof(DsbMem));
+    d->cap_jobs = 2 * (Lmax / DSB_SEED_RANGE + 2) + 8;
+    d->cap_stage = cap_anchor / 8;
+    DSB_TAKE(o_jobs, (size_t)d->cap_jobs * sizeof(DsbJob));
+    DSB_TAKE(o_stage, (size_t)32 * d->cap_stage * sizeof(DsbAnchor));
+    DSB_TAKE(o_lane_priv, (size_t)32 * DSB_LANE_PRIV_BYTES);
     DSB_TAKE(o_sms, (size_t)cap_sms * sizeof(DsbSms));
     DSB_TAKE(o_head0, (size_t)d->head_entries * 4);
     DSB_TAKE(o_head1, (size_t)d->head_entries * 4);
@@ -103,6 +110,12 @@ DSB_HD void dsb_bind_scratch(DsbWork *w, uint8_t *base, const DsbScratchDims *d)
     w->score_v = (int32_t *)(base + d->o_score_v);
     w->sp_set = (uint64_t *)(base + d->o_sp_set);
     w->mems = (DsbMem *)(base + d->o_mems);
+    w->jobs = (DsbJob *)(base + d->o_jobs);
+    w->cap_jobs = d->cap_jobs;
+    w->stage = (DsbAnchor *)(base + d->o_stage);
+    w->cap_stage = d->cap_stage;
+    w->lane_priv = base + d->o_lane_priv;
+    w->solo = 0;
     w->sms = (DsbSms *)(base + d->o_sms);
     w->cap_sms = d->cap_sms;
     w->h_head[0] = (uint32_t *)(base + d->o_head0);
