@@ -461,7 +461,11 @@ static int launch_kernels(dsb_slot *s)
     CU(cudaEventRecord(s->ev[1], s->stream));
     k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
     CU(cudaEventRecord(s->ev[2], s->stream));
-    k_classify<<<s->blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
+    // small batches: no more warps than reads (the other slots' kernels fill the rest of the device)
+    const int warps_per_block = s->threads / 32;
+    int blocks = (int)((n + warps_per_block - 1) / warps_per_block);
+    if (blocks > s->blocks) blocks = s->blocks;
+    k_classify<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
                                                        s->dims, s->d_results, s->d_hits, s->cap_hits, n, s->d_ctrl);
     CU(cudaEventRecord(s->ev[3], s->stream));
     CU(cudaGetLastError());

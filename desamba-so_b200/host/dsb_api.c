@@ -9,6 +9,7 @@
 #include "desamba.h"
 #include "dsb_host.h"
 #include <pthread.h>
+#include <sys/mman.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -63,14 +64,6 @@ static dsb_session *session_for(api_index *a, int thread_id)
     return s;
 }
 
-static void sink_strbuf(void *ctx, const char *text, size_t n)
-{
-    dsb_strbuf *b = (dsb_strbuf *)ctx;
-    dsb_strbuf_reserve(b, n);
-    memcpy(b->s + b->l, text, n);
-    b->l += n;
-}
-
 void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint64_t *output_n, int thread_id,
                    int thread_num)
 {
@@ -85,8 +78,18 @@ void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint
     dsb_fq *f = (input_n == (uint64_t)-1) ? dsb_fq_open_path(input) : dsb_fq_open_mem(input, input_n);
     dsb_out_opt o = {DSB_OUT_SAM_FULL, 5};          /* reference src/cly_mt.c:970-976 */
     dsb_strbuf out = {NULL, 0, 0};
-    dsb_strbuf_reserve(&out, 1);
-    dsb_session_run(s, f, &o, sink_strbuf, &out, NULL);
+    /* SAM_FULL repeats SEQ and QUAL of every read: about the size of the input plus the record fields */
+    dsb_strbuf_reserve(&out, input_n == (uint64_t)-1 ? 1 : (size_t)(input_n + input_n / 16 + 4096));
+#ifdef MADV_HUGEPAGE
+    if (out.m >= ((size_t)4 << 20)) {
+        /* a fresh block this large comes straight from mmap: ask for huge pages so that filling it
+         * costs tens of page faults instead of tens of thousands */
+        uintptr_t a = ((uintptr_t)out.s + ((size_t)2 << 20) - 1) & ~(uintptr_t)(((size_t)2 << 20) - 1);
+        uintptr_t e = ((uintptr_t)out.s + out.m) & ~(uintptr_t)(((size_t)2 << 20) - 1);
+        if (e > a) madvise((void *)a, (size_t)(e - a), MADV_HUGEPAGE);
+    }
+#endif
+    dsb_session_run(s, f, &o, NULL, &out, NULL);        /* NULL sink: append straight to `out` */
     dsb_fq_close(f);
     out.s[out.l] = 0;
     /* caller free()s: hand over a plain malloc block */

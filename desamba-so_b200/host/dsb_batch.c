@@ -13,10 +13,13 @@
  * in read order, before a read is handed to any device (dsb_history.c).
  */
 #include "dsb_host.h"
+#include <pthread.h>
 #include <stdlib.h>
 #include <string.h>
+#include <unistd.h>
 
-#define SLOTS_PER_GPU 2
+#define SLOTS_PER_GPU 4
+#define MAX_FMT_THREADS 32
 
 uint32_t dsb_history_max(const dsb_history *h);
 void dsb_history_note_max(dsb_history *h, uint32_t len);
@@ -27,17 +30,35 @@ struct dsb_engine {
     dsb_index **dev;
     uint64_t batch_bases;
     uint32_t batch_reads;
+    int fmt_threads;
 };
 
 typedef struct batch_meta {
     uint32_t n_reads;
     uint64_t n_bases;
     dsb_strbuf names;       /* NUL-separated */
-    dsb_strbuf quals;       /* concatenated, same offsets as seq */
     uint64_t *name_off;
-    uint8_t *has_qual;
-    int busy;
+    /* quality strings: a pointer into the caller's input block when the record view is stable
+     * (zero copy), else an offset into `quals`; both "none" for FASTA records */
+    const char **qual_ptr;
+    uint64_t *qual_off;
+    dsb_strbuf quals;
 } batch_meta;
+
+/* fork-join helpers for the text formatter (the serial step 2 of the reference's pipeline,
+ * src/cly_mt.c:333-348, is the slowest host stage once the classifier runs on the GPU) */
+typedef struct fmt_pool {
+    pthread_t th[MAX_FMT_THREADS];
+    int n;
+    pthread_mutex_t mu;
+    pthread_cond_t cv_go, cv_done;
+    uint64_t gen;
+    int pending, quit;
+    void (*fn)(void *arg, int part, int n_parts);
+    void *arg;
+} fmt_pool;
+
+typedef struct fmt_worker_arg { fmt_pool *p; int id; } fmt_worker_arg;
 
 struct dsb_session {
     dsb_engine *e;
@@ -45,6 +66,12 @@ struct dsb_session {
     dsb_slot **slots;
     batch_meta *meta;
     dsb_history *hist;
+    fmt_pool pool;
+    fmt_worker_arg pool_arg[MAX_FMT_THREADS];
+    dsb_strbuf fmt_buf[MAX_FMT_THREADS + 1];
+    /* a record that did not fit the previous batch */
+    int have_carry;
+    dsb_rec_view carry;
 };
 
 static uint64_t env_u64(const char *name, uint64_t dflt)
@@ -70,8 +97,13 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     for (int g = 0; g < want; g++)
         if (dsb_index_upload(&ix->h, first + g, &e->dev[g]) != 0)
             dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
-    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)32 << 20);
+    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)8 << 20);
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
+    long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
+    if (ncpu < 1) ncpu = 1;
+    e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 8 ? 8 : ncpu));
+    if (e->fmt_threads < 1) e->fmt_threads = 1;
+    if (e->fmt_threads > MAX_FMT_THREADS) e->fmt_threads = MAX_FMT_THREADS;
     return e;
 }
 
@@ -85,6 +117,45 @@ void dsb_engine_destroy(dsb_engine *e)
 
 int dsb_engine_n_gpu(const dsb_engine *e) { return e->n_gpu; }
 
+/* ---- formatter pool ------------------------------------------------------------------- */
+static void *fmt_worker(void *argp)
+{
+    fmt_worker_arg *wa = (fmt_worker_arg *)argp;
+    fmt_pool *p = wa->p;
+    uint64_t seen = 0;
+    for (;;) {
+        pthread_mutex_lock(&p->mu);
+        while (!p->quit && p->gen == seen) pthread_cond_wait(&p->cv_go, &p->mu);
+        if (p->quit) { pthread_mutex_unlock(&p->mu); return NULL; }
+        seen = p->gen;
+        pthread_mutex_unlock(&p->mu);
+        p->fn(p->arg, wa->id, p->n + 1);
+        pthread_mutex_lock(&p->mu);
+        if (--p->pending == 0) pthread_cond_signal(&p->cv_done);
+        pthread_mutex_unlock(&p->mu);
+    }
+}
+
+/* run fn(arg, part, n_parts) for part = 0..n_parts-1; the caller does the last part itself */
+static void pool_run(fmt_pool *p, void (*fn)(void *, int, int), void *arg)
+{
+    if (p->n > 0) {
+        pthread_mutex_lock(&p->mu);
+        p->fn = fn;
+        p->arg = arg;
+        p->pending = p->n;
+        p->gen++;
+        pthread_cond_broadcast(&p->cv_go);
+        pthread_mutex_unlock(&p->mu);
+    }
+    fn(arg, p->n, p->n + 1);
+    if (p->n > 0) {
+        pthread_mutex_lock(&p->mu);
+        while (p->pending) pthread_cond_wait(&p->cv_done, &p->mu);
+        pthread_mutex_unlock(&p->mu);
+    }
+}
+
 dsb_session *dsb_session_create(dsb_engine *e)
 {
     dsb_session *s = (dsb_session *)dsb_xcalloc(1, sizeof *s);
@@ -97,22 +168,41 @@ dsb_session *dsb_session_create(dsb_engine *e)
         if (dsb_slot_create(e->dev[k % e->n_gpu], e->batch_bases, e->batch_reads, &s->slots[k]) != 0)
             dsb_fatal("slot creation failed: %s", dsb_last_error());
         s->meta[k].name_off = (uint64_t *)dsb_xmalloc((size_t)e->batch_reads * 8);
-        s->meta[k].has_qual = (uint8_t *)dsb_xmalloc((size_t)e->batch_reads);
+        s->meta[k].qual_ptr = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
+        s->meta[k].qual_off = (uint64_t *)dsb_xmalloc((size_t)e->batch_reads * 8);
     }
     s->hist = dsb_history_new();
+    fmt_pool *p = &s->pool;
+    pthread_mutex_init(&p->mu, NULL);
+    pthread_cond_init(&p->cv_go, NULL);
+    pthread_cond_init(&p->cv_done, NULL);
+    p->n = e->fmt_threads - 1;
+    for (int i = 0; i < p->n; i++) {
+        s->pool_arg[i].p = p;
+        s->pool_arg[i].id = i;
+        if (pthread_create(&p->th[i], NULL, fmt_worker, &s->pool_arg[i]) != 0) { p->n = i; break; }
+    }
     return s;
 }
 
 void dsb_session_destroy(dsb_session *s)
 {
     if (!s) return;
+    fmt_pool *p = &s->pool;
+    pthread_mutex_lock(&p->mu);
+    p->quit = 1;
+    pthread_cond_broadcast(&p->cv_go);
+    pthread_mutex_unlock(&p->mu);
+    for (int i = 0; i < p->n; i++) pthread_join(p->th[i], NULL);
     for (int k = 0; k < s->n_slots; k++) {
         dsb_slot_free(s->slots[k]);
         free(s->meta[k].names.s);
         free(s->meta[k].quals.s);
         free(s->meta[k].name_off);
-        free(s->meta[k].has_qual);
+        free(s->meta[k].qual_ptr);
+        free(s->meta[k].qual_off);
     }
+    for (int i = 0; i <= MAX_FMT_THREADS; i++) free(s->fmt_buf[i].s);
     free(s->slots);
     free(s->meta);
     dsb_history_free(s->hist);
@@ -132,36 +222,49 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
     m->quals.l = 0;
     uint32_t n = 0;
     uint64_t bases = 0;
-    dsb_strbuf name = {NULL, 0, 0}, qual = {NULL, 0, 0};
     while (n < e->batch_reads) {
-        int is_fq = 0;
-        int64_t L = dsb_fq_next(f, &name, seq + bases, e->batch_bases - bases, want_qual ? &qual : NULL, &is_fq);
-        if (L == -3) {
+        dsb_rec_view v;
+        if (s->have_carry) {
+            v = s->carry;
+            s->have_carry = 0;
+        } else {
+            int64_t r = dsb_fq_next_view(f, &v);
+            if (r < 0) { *eof = 1; break; }
+        }
+        const uint64_t L = v.seq_l;
+        if (L > 0x7fffffff) dsb_fatal("read too long");
+        if (L > e->batch_bases - bases) {
             if (n == 0) dsb_fatal("a single read is longer than the batch capacity (%llu bases); raise DSB_BATCH_BASES",
                                   (unsigned long long)e->batch_bases);
+            s->carry = v;                      /* stays valid: no further reader call before the next batch */
+            s->have_carry = 1;
             break;
         }
-        if (L < 0) { *eof = 1; break; }
-        if (L > 0x7fffffff) dsb_fatal("read too long");
+        memcpy(seq + bases, v.seq, L);
         desc[n].seq_off = bases;
         desc[n].len = (uint32_t)L;
         desc[n].flags = dsb_history_next(s->hist, seq + bases, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES));
         if (L >= 40) dsb_history_note_max(s->hist, (uint32_t)L);
         m->name_off[n] = m->names.l;
-        dsb_strbuf_reserve(&m->names, name.l + 1);
-        memcpy(m->names.s + m->names.l, name.s, name.l + 1);
-        m->names.l += name.l + 1;
-        if (want_qual) {
-            dsb_strbuf_reserve(&m->quals, bases + (uint64_t)L + 1 - m->quals.l);
-            m->has_qual[n] = (uint8_t)is_fq;
-            if (is_fq) memcpy(m->quals.s + bases, qual.s, (size_t)L);
-            m->quals.l = bases + (uint64_t)L;
+        dsb_strbuf_reserve(&m->names, v.name_l + 1);
+        memcpy(m->names.s + m->names.l, v.name, v.name_l);
+        m->names.s[m->names.l + v.name_l] = 0;
+        m->names.l += v.name_l + 1;
+        m->qual_ptr[n] = NULL;
+        m->qual_off[n] = UINT64_MAX;
+        if (want_qual && v.is_fastq) {
+            if (v.stable)
+                m->qual_ptr[n] = v.qual;
+            else {
+                dsb_strbuf_reserve(&m->quals, L + 1);
+                memcpy(m->quals.s + m->quals.l, v.qual, L);
+                m->qual_off[n] = m->quals.l;
+                m->quals.l += L;
+            }
         }
-        bases += (uint64_t)L;
+        bases += L;
         n++;
     }
-    free(name.s);
-    free(qual.s);
     m->n_reads = n;
     m->n_bases = bases;
     return n;
@@ -174,30 +277,84 @@ static void add_counters(dsb_counters *a, const dsb_counters *b)
     for (size_t i = 0; i < sizeof(dsb_counters) / 8; i++) x[i] += y[i];
 }
 
-static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_strbuf *text,
-                       dsb_run_stats *st)
-{
-    batch_meta *m = &s->meta[k];
+typedef struct fmt_job {
+    dsb_session *s;
+    const batch_meta *m;
+    const dsb_out_opt *o;
+    const char *seq;
+    const dsb_read_desc *desc;
     const dsb_read_result *res;
     const dsb_hit *hits;
+    uint32_t cut[MAX_FMT_THREADS + 2];     /* part p formats reads [cut[p], cut[p+1]) */
+    char *dst;                             /* direct mode: where part p's text goes = dst + off[p] */
+    size_t off[MAX_FMT_THREADS + 2];
+} fmt_job;
+
+static void fmt_part(void *arg, int part, int n_parts)
+{
+    (void)n_parts;
+    fmt_job *j = (fmt_job *)arg;
+    const batch_meta *m = j->m;
+    dsb_strbuf *text = &j->s->fmt_buf[part];
+    text->l = 0;
+    for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
+        const char *q = m->qual_ptr[i];
+        if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
+        dsb_format_read(text, j->s->e->ix, j->o, m->names.s + m->name_off[i], j->seq + j->desc[i].seq_off, q, j->desc[i].len,
+                        &j->res[i], j->hits + j->res[i].hit_off);
+    }
+}
+
+static void copy_part(void *arg, int part, int n_parts)
+{
+    (void)n_parts;
+    fmt_job *j = (fmt_job *)arg;
+    const dsb_strbuf *text = &j->s->fmt_buf[part];
+    if (text->l) memcpy(j->dst + j->off[part], text->s, text->l);
+}
+
+static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *st)
+{
+    batch_meta *m = &s->meta[k];
+    fmt_job j;
     uint32_t n_hits;
     dsb_counters c;
     double t0 = dsb_now();
-    if (dsb_slot_wait(s->slots[k], &res, &hits, &n_hits, &c) != 0) dsb_fatal("GPU batch failed: %s", dsb_last_error());
+    if (dsb_slot_wait(s->slots[k], &j.res, &j.hits, &n_hits, &c) != 0) dsb_fatal("GPU batch failed: %s", dsb_last_error());
     double t1 = dsb_now();
     char *seq;
     dsb_read_desc *desc;
     uint8_t *edge;
     dsb_slot_staging(s->slots[k], &seq, &desc, &edge);
-    text->l = 0;
-    for (uint32_t i = 0; i < m->n_reads; i++) {
-        const char *q = NULL;
-        if (o->format == DSB_OUT_SAM_FULL && m->has_qual[i]) q = m->quals.s + desc[i].seq_off;
-        dsb_format_read(text, s->e->ix, o, m->names.s + m->name_off[i], seq + desc[i].seq_off, q, desc[i].len, &res[i],
-                        hits + res[i].hit_off);
-        if (text->l > ((size_t)8 << 20)) { sink(ctx, text->s, text->l); text->l = 0; }
+    j.s = s; j.m = m; j.o = o; j.seq = seq; j.desc = desc;
+    /* contiguous read ranges of about equal size in bases, one per formatter thread, sunk in order */
+    const int parts = s->pool.n + 1;
+    j.cut[0] = 0;
+    {
+        uint32_t i = 0;
+        for (int p = 1; p < parts; p++) {
+            const uint64_t target = m->n_bases * (uint64_t)p / (uint64_t)parts;
+            while (i < m->n_reads && desc[i].seq_off < target) i++;
+            j.cut[p] = i;
+        }
+        j.cut[parts] = m->n_reads;
     }
-    if (text->l) sink(ctx, text->s, text->l);
+    pool_run(&s->pool, fmt_part, &j);
+    const double t_f = dsb_now();
+    if (sink) {
+        for (int p = 0; p < parts; p++)
+            if (s->fmt_buf[p].l) sink(ctx, s->fmt_buf[p].s, s->fmt_buf[p].l);
+    } else {
+        /* direct mode: ctx is the caller's dsb_strbuf; every thread copies its own part, so the page
+         * faults of the fresh output block are taken in parallel too */
+        dsb_strbuf *out = (dsb_strbuf *)ctx;
+        size_t total = 0;
+        for (int p = 0; p < parts; p++) { j.off[p] = total; total += s->fmt_buf[p].l; }
+        dsb_strbuf_reserve(out, total);
+        j.dst = out->s + out->l;
+        pool_run(&s->pool, copy_part, &j);
+        out->l += total;
+    }
     double t2 = dsb_now();
     if (st) {
         float a = 0, b = 0, d = 0;
@@ -205,9 +362,39 @@ static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn 
         st->gpu_ms_total += a; st->gpu_ms_exist += b; st->gpu_ms_classify += d;
         st->t_gpu_wait += t1 - t0;
         st->t_format += t2 - t1;
+        if (getenv("DSB_VERBOSE")) fprintf(stderr, "[dsb]   slot %d: wait %.1f ms, format %.1f ms, sink %.1f ms\n", k, 1e3 * (t1 - t0), 1e3 * (t_f - t1), 1e3 * (t2 - t_f));
         add_counters(&st->counters, &c);
     }
-    m->busy = 0;
+}
+
+/* ---- the pipeline: producer (caller's thread) parses + submits, a drain thread waits + formats ---- */
+typedef struct run_ctx {
+    dsb_session *s;
+    const dsb_out_opt *o;
+    dsb_sink_fn sink;
+    void *ctx;
+    dsb_run_stats *stats;
+    pthread_mutex_t mu;
+    pthread_cond_t cv;
+    uint64_t submitted, drained;
+    int done;
+} run_ctx;
+
+static void *drain_thread(void *argp)
+{
+    run_ctx *r = (run_ctx *)argp;
+    for (uint64_t b = 0;; b++) {
+        pthread_mutex_lock(&r->mu);
+        while (r->submitted <= b && !r->done) pthread_cond_wait(&r->cv, &r->mu);
+        const int have = r->submitted > b;
+        pthread_mutex_unlock(&r->mu);
+        if (!have) return NULL;
+        drain_slot(r->s, (int)(b % (uint64_t)r->s->n_slots), r->o, r->sink, r->ctx, r->stats);
+        pthread_mutex_lock(&r->mu);
+        r->drained = b + 1;
+        pthread_cond_broadcast(&r->cv);
+        pthread_mutex_unlock(&r->mu);
+    }
 }
 
 void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *stats)
@@ -216,12 +403,24 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     if (!stats) stats = &local;
     memset(stats, 0, sizeof *stats);
     const double t_start = dsb_now();
-    dsb_strbuf text = {NULL, 0, 0};
     const int want_qual = (o->format == DSB_OUT_SAM_FULL);
-    int eof = 0, k = 0;
-    while (!eof) {
-        if (s->meta[k].busy) drain_slot(s, k, o, sink, ctx, &text, stats);
-        /* the slot's sequence staging is about to be overwritten: the history must own what it still needs */
+    run_ctx r;
+    memset(&r, 0, sizeof r);
+    r.s = s; r.o = o; r.sink = sink; r.ctx = ctx; r.stats = stats;
+    pthread_mutex_init(&r.mu, NULL);
+    pthread_cond_init(&r.cv, NULL);
+    pthread_t th;
+    if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
+    int eof = 0;
+    s->have_carry = 0;
+    for (uint64_t b = 0; !eof; b++) {
+        const int k = (int)(b % (uint64_t)s->n_slots);
+        /* batch b reuses the slot of batch b - n_slots: wait until that one has been formatted */
+        pthread_mutex_lock(&r.mu);
+        while (b >= r.drained + (uint64_t)s->n_slots) pthread_cond_wait(&r.cv, &r.mu);
+        pthread_mutex_unlock(&r.mu);
+        /* the history borrows sequence pointers from the staging of earlier batches: before any
+         * staging is overwritten it must own what it still needs */
         dsb_history_end_batch(s->hist);
         double t0 = dsb_now();
         uint32_t n = fill_slot(s, k, f, want_qual, &eof);
@@ -231,15 +430,22 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         stats->n_bases += s->meta[k].n_bases;
         stats->n_batches++;
         if (dsb_slot_submit(s->slots[k], n, s->meta[k].n_bases) != 0) dsb_fatal("submit failed: %s", dsb_last_error());
-        s->meta[k].busy = 1;
-        k = (k + 1) % s->n_slots;
+        pthread_mutex_lock(&r.mu);
+        r.submitted = b + 1;
+        pthread_cond_broadcast(&r.cv);
+        pthread_mutex_unlock(&r.mu);
     }
-    /* drain in submission order: oldest first */
-    for (int i = 0; i < s->n_slots; i++) {
-        int j = (k + i) % s->n_slots;
-        if (s->meta[j].busy) drain_slot(s, j, o, sink, ctx, &text, stats);
-    }
+    pthread_mutex_lock(&r.mu);
+    r.done = 1;
+    pthread_cond_broadcast(&r.cv);
+    pthread_mutex_unlock(&r.mu);
+    pthread_join(th, NULL);
     dsb_history_end_batch(s->hist);
-    free(text.s);
+    pthread_mutex_destroy(&r.mu);
+    pthread_cond_destroy(&r.cv);
     stats->t_total = dsb_now() - t_start;
+    if (getenv("DSB_VERBOSE"))
+        fprintf(stderr, "[dsb] %llu reads %llu bases %llu batches: parse %.1f ms, gpu-wait %.1f ms, format %.1f ms, total %.1f ms\n",
+                (unsigned long long)stats->n_reads, (unsigned long long)stats->n_bases, (unsigned long long)stats->n_batches,
+                1e3 * stats->t_parse, 1e3 * stats->t_gpu_wait, 1e3 * stats->t_format, 1e3 * stats->t_total);
 }

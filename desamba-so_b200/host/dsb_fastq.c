@@ -17,10 +17,11 @@
 struct dsb_fq {
     gzFile gz;                 /* stream mode */
     FILE *tmp;                 /* gzip-in-memory goes through a temp file like the reference */
-    const unsigned char *mem;  /* memory mode */
-    uint64_t mem_n, mem_pos;
+    const unsigned char *mem;  /* memory mode: `buf` IS the caller's block (no copy), begin/end span it */
+    uint64_t mem_n;
     unsigned char *buf;
-    int begin, end, is_eof;
+    size_t begin, end;
+    int is_eof;
     int last_char;
     /* pending record when the caller's buffer was too small */
     int have_pending;
@@ -29,19 +30,15 @@ struct dsb_fq {
     int64_t p_ret;
 };
 
-static int fq_fill(dsb_fq *f)
+static size_t fq_fill(dsb_fq *f)
 {
-    f->begin = 0;
-    if (f->gz) {
-        f->end = gzread(f->gz, f->buf, FQ_BUFSIZE);
-        if (f->end < 0) f->end = 0;
-    } else {
-        uint64_t left = f->mem_n - f->mem_pos;
-        int n = (left > FQ_BUFSIZE) ? FQ_BUFSIZE : (int)left;
-        memcpy(f->buf, f->mem + f->mem_pos, (size_t)n);
-        f->mem_pos += (uint64_t)n;
-        f->end = n;
+    if (!f->gz) {               /* memory mode has everything in view from the start */
+        f->is_eof = 1;
+        return 0;
     }
+    f->begin = 0;
+    int n = gzread(f->gz, f->buf, FQ_BUFSIZE);
+    f->end = n < 0 ? 0 : (size_t)n;
     if (f->end < FQ_BUFSIZE) f->is_eof = 1;
     return f->end;
 }
@@ -72,7 +69,7 @@ static int64_t fq_getuntil(dsb_fq *f, int delimiter, dsb_strbuf *str, int *dret,
     if (!append) str->l = 0;
     if (f->begin >= f->end && f->is_eof) return -1;
     for (;;) {
-        int i;
+        size_t i;
         if (f->begin >= f->end) {
             if (!f->is_eof) {
                 if (fq_fill(f) == 0) break;
@@ -81,7 +78,7 @@ static int64_t fq_getuntil(dsb_fq *f, int delimiter, dsb_strbuf *str, int *dret,
         }
         if (delimiter) {
             unsigned char *p = (unsigned char *)memchr(f->buf + f->begin, delimiter, (size_t)(f->end - f->begin));
-            i = p ? (int)(p - f->buf) : f->end;
+            i = p ? (size_t)(p - f->buf) : f->end;
         } else {
             for (i = f->begin; i < f->end; ++i)
                 if (isspace(f->buf[i])) break;
@@ -100,16 +97,16 @@ static int64_t fq_getuntil(dsb_fq *f, int delimiter, dsb_strbuf *str, int *dret,
     return (int64_t)str->l;
 }
 
-static dsb_fq *fq_new(void)
+static dsb_fq *fq_new(int stream)
 {
     dsb_fq *f = (dsb_fq *)dsb_xcalloc(1, sizeof *f);
-    f->buf = (unsigned char *)dsb_xmalloc(FQ_BUFSIZE);
+    if (stream) f->buf = (unsigned char *)dsb_xmalloc(FQ_BUFSIZE);
     return f;
 }
 
 dsb_fq *dsb_fq_open_path(const char *path)
 {
-    dsb_fq *f = fq_new();
+    dsb_fq *f = fq_new(1);
     f->gz = gzopen(path, "r");
     if (!f->gz) dsb_fatal("cannot open reads file %s", path);
     gzbuffer(f->gz, 1 << 20);
@@ -118,8 +115,9 @@ dsb_fq *dsb_fq_open_path(const char *path)
 
 dsb_fq *dsb_fq_open_mem(const char *buf, uint64_t n)
 {
-    dsb_fq *f = fq_new();
-    if (n >= 2 && (unsigned char)buf[0] == 0x1f && (unsigned char)buf[1] == 0x8b) {
+    const int gz = (n >= 2 && (unsigned char)buf[0] == 0x1f && (unsigned char)buf[1] == 0x8b);
+    dsb_fq *f = fq_new(gz);
+    if (gz) {
         f->tmp = tmpfile();
         if (!f->tmp) dsb_fatal("tmpfile() failed");
         if (fwrite(buf, 1, n, f->tmp) != n) dsb_fatal("short write to temp file");
@@ -129,6 +127,10 @@ dsb_fq *dsb_fq_open_mem(const char *buf, uint64_t n)
     } else {
         f->mem = (const unsigned char *)buf;
         f->mem_n = n;
+        f->buf = (unsigned char *)buf;     /* never written: every access below only reads buf */
+        f->begin = 0;
+        f->end = (size_t)n;
+        f->is_eof = 1;
     }
     return f;
 }
@@ -138,7 +140,7 @@ void dsb_fq_close(dsb_fq *f)
     if (!f) return;
     if (f->gz) gzclose(f->gz);
     if (f->tmp) fclose(f->tmp);
-    free(f->buf);
+    if (!f->mem) free(f->buf);
     free(f->p_name.s);
     free(f->p_seq.s);
     free(f->p_qual.s);
@@ -203,5 +205,75 @@ int64_t dsb_fq_next(dsb_fq *f, dsb_strbuf *name, char *seq_out, uint64_t cap, ds
         qual->s[qual->l] = 0;
     }
     if (is_fastq) *is_fastq = f->p_is_fastq;
+    return f->p_ret;
+}
+
+/* ---- zero-copy record views ---------------------------------------------------------------
+ * In memory mode the common record shape -- header line, ONE sequence line, '+' line, ONE quality
+ * line of the same length -- is recognised directly in the caller's block and returned as pointers
+ * into it; anything else (FASTA, wrapped lines, short qualities, end-of-input oddities) goes through
+ * fq_read_record() above, i.e. the kseq restatement, from the unchanged reader state.  The fast
+ * path accepts a record only where kseq_read would produce exactly the same name / seq / qual. */
+static int fq_try_fast(dsb_fq *f, dsb_rec_view *v)
+{
+    const unsigned char *b = f->buf;
+    size_t p = f->begin;
+    const size_t e = f->end;
+    if (f->last_char == 0) {
+        while (p < e && b[p] != '>' && b[p] != '@') p++;
+        if (p >= e) return 0;
+        p++;
+    }
+    const size_t ns = p;
+    while (p < e && !isspace(b[p])) p++;
+    if (p >= e) return 0;
+    const size_t nl = p - ns;
+    const unsigned char *q;
+    if (b[p] != '\n') {
+        q = (const unsigned char *)memchr(b + p, '\n', e - p);
+        if (!q) return 0;
+        p = (size_t)(q - b);
+    }
+    p++;
+    if (p >= e) return 0;
+    if (b[p] == '>' || b[p] == '+' || b[p] == '@' || b[p] == '\n') return 0;
+    const size_t ss = p;
+    q = (const unsigned char *)memchr(b + p, '\n', e - p);
+    if (!q) return 0;
+    const size_t sl = (size_t)(q - b) - ss;
+    p = (size_t)(q - b) + 1;
+    if (p >= e || b[p] != '+') return 0;
+    q = (const unsigned char *)memchr(b + p, '\n', e - p);
+    if (!q) return 0;
+    p = (size_t)(q - b) + 1;
+    const size_t qs = p;
+    size_t ql;
+    q = (p < e) ? (const unsigned char *)memchr(b + p, '\n', e - p) : NULL;
+    if (q) { ql = (size_t)(q - b) - qs; p = (size_t)(q - b) + 1; }
+    else { ql = e - qs; p = e; }
+    if (ql != sl) return 0;
+    v->name = (const char *)b + ns; v->name_l = nl;
+    v->seq = (const char *)b + ss; v->seq_l = sl;
+    v->qual = (const char *)b + qs; v->is_fastq = 1;
+    v->stable = 1;
+    f->begin = p;
+    f->last_char = 0;
+    return 1;
+}
+
+int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v)
+{
+    if (f->have_pending) {              /* a record fetched by dsb_fq_next() that did not fit its buffer */
+        f->have_pending = 0;
+    } else {
+        if (f->mem && fq_try_fast(f, v)) return (int64_t)v->seq_l;
+        f->p_ret = fq_read_record(f);
+        if (f->p_ret < 0) return f->p_ret;
+    }
+    v->name = f->p_name.s; v->name_l = f->p_name.l;
+    v->seq = f->p_seq.s; v->seq_l = f->p_seq.l;
+    v->qual = f->p_is_fastq ? f->p_qual.s : NULL;
+    v->is_fastq = f->p_is_fastq;
+    v->stable = 0;
     return f->p_ret;
 }

@@ -66,6 +66,17 @@ typedef struct dsb_strbuf { char *s; size_t l, m; } dsb_strbuf;
  * is kept pending and -3 returned when they do not (call again with a bigger/empty buffer). */
 int64_t dsb_fq_next(dsb_fq *f, dsb_strbuf *name, char *seq_out, uint64_t cap, dsb_strbuf *qual, int *is_fastq);
 
+/* A record as pointers (not NUL-terminated).  stable = 1: they point into the caller's memory block
+ * and stay valid for the life of the reader; stable = 0: into the reader's buffers, valid until
+ * the next call.  qual is NULL for FASTA records. */
+typedef struct dsb_rec_view {
+    const char *name, *seq, *qual;
+    size_t name_l, seq_l;
+    int is_fastq, stable;
+} dsb_rec_view;
+/* next record as a view: >= 0 sequence length, -1 end of input, -2 malformed quality */
+int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v);
+
 /* ---- worker-buffer history ------------------------------------------- */
 typedef struct dsb_history dsb_history;
 dsb_history *dsb_history_new(void);
@@ -107,7 +118,8 @@ typedef struct dsb_run_stats {
     dsb_counters counters;
     double gpu_ms_total, gpu_ms_exist, gpu_ms_classify;
 } dsb_run_stats;
-/* classify every record of `f`, in order, writing text to sink */
+/* classify every record of `f`, in order, writing text to sink; sink == NULL: ctx is a dsb_strbuf* the
+ * text is appended to (parallel copy) */
 void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx,
                      dsb_run_stats *stats);
 

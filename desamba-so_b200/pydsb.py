@@ -109,6 +109,17 @@ class Desamba:
         self.libc.free(out)
         return text
 
+    def read_classify_timed(self, data, thread_id=0, thread_num=1):
+        """What a C caller does and nothing else: read_classify() on host text, then free() of the result.
+        Returns (seconds, output bytes); the text is not copied into Python."""
+        import time
+        out, out_n = C.c_void_p(), C.c_uint64(0)
+        t0 = time.perf_counter()
+        self.lib.read_classify(self.idx, data, len(data), C.byref(out), C.byref(out_n), thread_id, thread_num)
+        if out.value:
+            self.libc.free(out)
+        return time.perf_counter() - t0, out_n.value
+
     def meta_analysis(self, sam, thread_id=0, flag=1, max_snapshot_len=65536):
         out, out_n, hs, hs_n = C.c_void_p(), C.c_uint64(0), C.c_void_p(), C.c_uint64(0)
         self.lib.meta_analysis(self.idx, sam, len(sam), C.byref(out), C.byref(out_n), thread_id, flag, max_snapshot_len,
