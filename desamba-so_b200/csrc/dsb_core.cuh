@@ -208,6 +208,7 @@ struct DsbWork {
     // scoring
     DsbSms *sms;
     uint32_t n_sms, cap_sms;
+    DsbSms *sms_stage;            // 32 lanes x DSB_SMS_LANE_CAP (dsb_sdp_match)
     uint32_t *h_head[2];          // [0] forward strand table, [1] reverse; 2^key_len entries
     uint32_t *h_next[2];          // L entries
     uint32_t *h_kmer[2];          // L entries
@@ -1193,6 +1194,46 @@ DSB_HDN void dsb_chain_insert_M3(DsbWork *w)
 {
     const uint32_t n = w->n_anchor;
     // stable sort by (ref_ID, direction, ref_offset): Anchor_cmp_by_chr_ID_and_pos returns a>b
+#if defined(DSB_DEVICE_CODE)
+    {
+        // The comparator is a consistent order on (ref_ID, direction, ref_offset), so the reference's merge
+        // sort is simply a STABLE sort: equal to sorting the unique pairs (key, input index) with any
+        // algorithm.  Bitonic network over the warp, keys in the (idle) chains_tmp area.
+        const uint32_t lane = threadIdx.x & 31;
+        uint32_t P = 64;
+        while (P < n) P <<= 1;
+        uint64_t *key = (uint64_t *)w->chains_tmp;          // cap_anchor * sizeof(DsbChain) >= 2 * cap_anchor * 8
+        uint32_t *idx = w->sort_a;                          // 2 * cap_anchor entries
+        for (uint32_t i = lane; i < P; i += 32) {
+            uint64_t k = ~0ull;
+            if (i < n) {
+                const DsbAnchor *a = w->anchors + i;
+                k = ((uint64_t)a->ref_ID << 33) | ((uint64_t)(a->direction ? 1u : 0u) << 32) | (uint64_t)a->ref_offset;
+            }
+            key[i] = k;
+            idx[i] = i;
+        }
+        __syncwarp();
+        for (uint32_t kk = 2; kk <= P; kk <<= 1) {
+            for (uint32_t j = kk >> 1; j > 0; j >>= 1) {
+                for (uint32_t t = lane; t < (P >> 1); t += 32) {
+                    const uint32_t lo = ((t & ~(j - 1)) << 1) | (t & (j - 1));     // pair (lo, lo | j)
+                    const uint32_t hi = lo | j;
+                    const bool up = ((lo & kk) == 0);
+                    const uint64_t ka = key[lo], kb = key[hi];
+                    const uint32_t ia = idx[lo], ib = idx[hi];
+                    const bool a_gt_b = (ka > kb) || (ka == kb && ia > ib);
+                    if (a_gt_b == up) { key[lo] = kb; key[hi] = ka; idx[lo] = ib; idx[hi] = ia; }
+                }
+                __syncwarp();
+            }
+        }
+        for (uint32_t i = lane; i < n; i += 32) w->anchors_tmp[i] = w->anchors[idx[i]];
+        __syncwarp();
+        for (uint32_t i = lane; i < n; i += 32) w->anchors[i] = w->anchors_tmp[i];
+        __syncwarp();
+    }
+#else
     {
         const DsbAnchor *A = w->anchors;
         dsb_msort_idx(w->sort_a, w->sort_b, n, [A](uint32_t i, uint32_t j) -> int {
@@ -1204,6 +1245,7 @@ DSB_HDN void dsb_chain_insert_M3(DsbWork *w)
         for (uint32_t i = 0; i < n; i++) w->anchors_tmp[i] = w->anchors[w->sort_a[i]];
         for (uint32_t i = 0; i < n; i++) w->anchors[i] = w->anchors_tmp[i];
     }
+#endif
     DsbAnchor *A = w->anchors;
     int32_t *score_v = w->score_v;
     for (uint32_t chr_st = 0; chr_st < n;) {
@@ -1220,6 +1262,48 @@ DSB_HDN void dsb_chain_insert_M3(DsbWork *w)
             anchor_max_score = A[c_a].score;
             const uint32_t max_t = A[c_a].ref_offset + 3;
             const uint32_t max_q = A[c_a].index_in_read + 3;
+#if defined(DSB_DEVICE_CODE)
+            {
+                // 32 predecessors per step, scanned from c_a-1 downwards.  The reference takes the FIRST
+                // predecessor reaching the maximum (strict >) and stops at the first one that passes both
+                // overlap tests and lies more than 1000 bases back.
+                const int32_t lane = (int32_t)(threadIdx.x & 31);
+                const uint32_t c_len = A[c_a].mtch_len;
+                int32_t best_pre = -1;
+                for (int32_t top = (int32_t)c_a - 1; top >= (int32_t)chr_st; top -= 32) {
+                    const int32_t pre = top - lane;
+                    bool brk = false;
+                    int cand = -2147483647 - 1;
+                    if (pre >= (int32_t)chr_st) {
+                        const DsbAnchor pv = A[pre];
+                        if (!(pv.index_in_read + pv.mtch_len > max_q) && !(pv.ref_offset + pv.mtch_len > max_t)) {
+                            if (pv.index_in_read + 1000 < max_q || pv.ref_offset + 1000 < max_t) brk = true;
+                            else {
+                                const int indel = (int)(pv.index_in_read - pv.ref_offset - (max_q - max_t));
+                                const int ABS_indel = DSB_ABS(indel);
+                                if (!(ABS_indel > 200))
+                                    cand = (int)(score_v[pre - (int32_t)chr_st] + c_len - (ABS_indel >> 4) -
+                                                 ((max_q - pv.index_in_read) >> 8));
+                            }
+                        }
+                    }
+                    const uint32_t bm = __ballot_sync(0xffffffffu, brk);
+                    if (bm) {
+                        const int32_t cut = __ffs((int)bm) - 1;      // lanes below `cut` were scanned before the break
+                        if (lane >= cut) cand = -2147483647 - 1;
+                    }
+                    const int gmax = __reduce_max_sync(0xffffffffu, cand);
+                    if (gmax > anchor_max_score) {
+                        const uint32_t who = __ballot_sync(0xffffffffu, cand == gmax);
+                        anchor_max_score = gmax;
+                        best_pre = top - (__ffs((int)who) - 1);      // lowest lane = highest index = met first
+                    }
+                    if (bm) break;
+                }
+                if (best_pre >= 0) A[c_a].pre = best_pre;
+                __syncwarp();
+            }
+#else
             for (int32_t pre = (int32_t)c_a - 1; pre >= (int32_t)chr_st; pre--) {
                 const DsbAnchor *p = A + pre;
                 if (p->index_in_read + p->mtch_len > max_q) continue;
@@ -1236,7 +1320,11 @@ DSB_HDN void dsb_chain_insert_M3(DsbWork *w)
                     A[c_a].pre = pre;
                 }
             }
+#endif
             score_v[c_a - chr_st] = anchor_max_score;
+#if defined(DSB_DEVICE_CODE)
+            __syncwarp();                                  // the next anchor's lanes read this entry
+#endif
             if (max_score < anchor_max_score) {
                 max_score = anchor_max_score;
                 max_anchor = (int32_t)c_a;
@@ -1401,6 +1489,17 @@ DSB_HD int dsb_run_len(const uint8_t *q, const uint8_t *t, bool forward, int max
     return len;
 }
 
+// the same, one lane on its own
+DSB_HD int dsb_run_len_solo(const uint8_t *q, const uint8_t *t, bool forward, int max)
+{
+    int len = 0;
+    if (forward) for (; len < max && *q++ == *t++; len++) {}
+    else for (; len < max && *q-- == *t--; len++) {}
+    return len;
+}
+
+#define DSB_SMS_LANE_CAP 8       // match blocks one lane may stage per window k-mer before the serial path takes over
+
 DSB_HD void dsb_push_sms(DsbWork *w, uint32_t t_pos, uint32_t q_pos, uint32_t len)
 {
     if (w->n_sms >= w->cap_sms) { w->overflow = 1; return; }
@@ -1435,6 +1534,71 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                     const uint32_t qp = node - 1;
                     if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
                     node = nxt[qp];
+                }
+            }
+            if (!__any_sync(0xffffffffu, node != 0)) continue;
+            // Every hit is an independent computation (two exact-run extensions); only the ORDER of the
+            // match-block list couples them (window position, then bucket order).  So each lane extends
+            // all hits of its own k-mer alone into a small staging area, and the warp then appends the
+            // staged blocks in lane order.  A lane with more hits than the staging holds (a repeat)
+            // sends the whole group of 32 through the serial consumption below instead.
+            {
+                DsbSms *my = w->sms_stage + lane * DSB_SMS_LANE_CAP;
+                const uint8_t *c_t = t_str + off_l;
+                uint32_t cnt = 0, nd = node;
+                while (nd != 0 && cnt <= DSB_SMS_LANE_CAP) {
+                    const uint32_t q_pos = nd - 1;
+                    uint32_t o_t = 0, o_q = 0, o_len = 0;
+                    bool emit = false;
+                    if (is_forward) {
+                        const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, 4);
+                        if (back_len < 4 || i_l == 4) {
+                            uint32_t max_search = q_ed - q_pos - 1;
+                            max_search = DSB_MIN(max_search, t_len - (uint32_t)i_l - 1) + DSB_OVER_SEARCH;
+                            const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, (int)max_search);
+                            const int total_len = back_len + forward_len + 1;
+                            if (total_len >= 4) {
+                                emit = true;
+                                o_t = (uint32_t)(i_l - back_len) + t_st; o_q = q_pos - (uint32_t)back_len; o_len = (uint32_t)total_len;
+                            }
+                        }
+                    } else {
+                        const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, 4);
+                        if (forward_len < 4 || i_l == 4) {
+                            uint32_t max_search = q_pos;
+                            max_search = (uint32_t)(DSB_MIN((long)max_search, off_l)) + DSB_OVER_SEARCH;
+                            const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, (int)max_search);
+                            const int total_len = back_len + forward_len + 1;
+                            if (total_len >= 4) {
+                                emit = true;
+                                o_t = (uint32_t)(off_l - back_len + (long)t_st); o_q = q_pos - (uint32_t)back_len; o_len = (uint32_t)total_len;
+                            }
+                        }
+                    }
+                    if (emit) {
+                        if (cnt < DSB_SMS_LANE_CAP) { my[cnt].t_pos = o_t; my[cnt].q_pos = o_q; my[cnt].len = o_len; }
+                        cnt++;
+                    }
+                    nd = nxt[q_pos];
+                    while (nd != 0) {
+                        const uint32_t qp = nd - 1;
+                        if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
+                        nd = nxt[qp];
+                    }
+                }
+                if (!__any_sync(0xffffffffu, cnt > DSB_SMS_LANE_CAP)) {
+                    uint32_t pre = cnt;                       // inclusive prefix sum of the lanes' counts
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
+                        if ((int)lane >= o) pre += v;
+                    }
+                    const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+                    if (w->n_sms + total > w->cap_sms) { w->overflow = 1; return; }
+                    DsbSms *dst = w->sms + w->n_sms + (pre - cnt);
+                    for (uint32_t k = 0; k < cnt; k++) { dst[k].t_pos = my[k].t_pos; dst[k].q_pos = my[k].q_pos; dst[k].len = my[k].len; }
+                    w->n_sms += total;
+                    __syncwarp();
+                    continue;
                 }
             }
             uint32_t act = __ballot_sync(0xffffffffu, node != 0);
