@@ -67,12 +67,13 @@
 // ------------------------------------------------------------------------------------------
 // device-resident index view
 // ------------------------------------------------------------------------------------------
-// FM block: 64 BWT symbols.  cnt[c] = number of symbol c (A,C,G,T) in BWT[0, 64*blk);
-// sym[w] holds symbols 16w..16w+15, 4 bits each, symbol i at bits 4*(i&15) -- the same nibble
-// order as the reference's little-endian u16 words (src/bwt.c:52), so bytes copy over verbatim.
+// FM block: 64 BWT symbols in 64 bytes.  cnt[c] = number of symbol c (A,C,G,T) in BWT[0, 64*blk);
+// plane[b] bit i = bit b of symbol i's 4-bit code (the reference's nibbles, src/bwt.c:52, transposed
+// into bit planes at upload): "symbols equal to c among the first r" is then four XOR/ORs and one
+// popcount on 64-bit words instead of nibble arithmetic on four words.
 struct __attribute__((aligned(64))) DsbFmBlock {
     uint64_t cnt[4];
-    uint64_t sym[4];
+    uint64_t plane[4];
 };
 
 struct DsbIndexView {
@@ -244,14 +245,8 @@ struct DsbWork {
 // ------------------------------------------------------------------------------------------
 // FM index: rank query on the 64-symbol block (restates occ, src/bwt.c:43-65)
 // ------------------------------------------------------------------------------------------
-// number of nibbles equal to c among the low `n` nibbles (n in [0,16]) of w
-DSB_HD uint32_t dsb_nib_eq_count(uint64_t w, uint32_t c, uint32_t n)
+DSB_HD uint32_t dsb_popc64(uint64_t x)
 {
-    uint64_t x = w ^ (0x1111111111111111ull * (uint64_t)c);   // matching nibbles become 0
-    x |= x >> 2;
-    x |= x >> 1;                                              // bit0 of each nibble = (nibble != 0)
-    x = ~x & 0x1111111111111111ull;
-    if (n < 16) x &= (1ull << (4 * n)) - 1ull;
 #if defined(DSB_DEVICE_CODE)
     return (uint32_t)__popcll(x);
 #else
@@ -269,37 +264,47 @@ DSB_HDO uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
     const uint32_t in = (uint32_t)(r & 63);
     const DsbFmBlock *b = ix->fm + blk;
     w->st.occ++;
+    uint64_t p0, p1, p2, p3, cnt_c = 0, cnt_sum = 0;
+    uint32_t cc = *c;
 #if defined(DSB_DEVICE_CODE)
     const uint4 *p = reinterpret_cast<const uint4 *>(b);
-    uint4 v0 = __ldg(p), v1 = __ldg(p + 1), v2 = __ldg(p + 2), v3 = __ldg(p + 3);
-    uint64_t cnt[4] = {((uint64_t)v0.y << 32) | v0.x, ((uint64_t)v0.w << 32) | v0.z,
-                       ((uint64_t)v1.y << 32) | v1.x, ((uint64_t)v1.w << 32) | v1.z};
-    uint64_t sym[4] = {((uint64_t)v2.y << 32) | v2.x, ((uint64_t)v2.w << 32) | v2.z,
-                       ((uint64_t)v3.y << 32) | v3.x, ((uint64_t)v3.w << 32) | v3.z};
+    const uint4 v2 = __ldg(p + 2), v3 = __ldg(p + 3);
+    p0 = ((uint64_t)v2.y << 32) | v2.x; p1 = ((uint64_t)v2.w << 32) | v2.z;
+    p2 = ((uint64_t)v3.y << 32) | v3.x; p3 = ((uint64_t)v3.w << 32) | v3.z;
+    if (cc == 0xff || cc >= 4) {
+        // the count to use depends on the symbol found: fetch all four with the planes (one 64-byte line)
+        const uint4 v0 = __ldg(p), v1 = __ldg(p + 1);
+        cc = (cc == 0xff) ? (uint32_t)(((p0 >> in) & 1) | (((p1 >> in) & 1) << 1) | (((p2 >> in) & 1) << 2) | (((p3 >> in) & 1) << 3)) : cc;
+        const uint64_t c0 = ((uint64_t)v0.y << 32) | v0.x, c1 = ((uint64_t)v0.w << 32) | v0.z;
+        const uint64_t c2 = ((uint64_t)v1.y << 32) | v1.x, c3 = ((uint64_t)v1.w << 32) | v1.z;
+        cnt_c = (cc == 0) ? c0 : (cc == 1) ? c1 : (cc == 2) ? c2 : c3;
+        cnt_sum = c0 + c1 + c2 + c3;
+    } else {
+        cnt_c = __ldg(&b->cnt[cc]);
+    }
 #else
-    const uint64_t *cnt = b->cnt;
-    const uint64_t *sym = b->sym;
+    p0 = b->plane[0]; p1 = b->plane[1]; p2 = b->plane[2]; p3 = b->plane[3];
+    if (cc == 0xff)
+        cc = (uint32_t)(((p0 >> in) & 1) | (((p1 >> in) & 1) << 1) | (((p2 >> in) & 1) << 2) | (((p3 >> in) & 1) << 3));
+    cnt_c = b->cnt[cc & 3];
+    cnt_sum = b->cnt[0] + b->cnt[1] + b->cnt[2] + b->cnt[3];
 #endif
     if (*c == 0xff) {
-        *c = (uint8_t)((sym[in >> 4] >> ((in & 15) << 2)) & 0xf);
-        if (*c == 5) return ix->dollar_pos;
+        *c = (uint8_t)cc;
+        if (cc == 5) return ix->dollar_pos;
     }
-    const uint32_t cc = *c;
     uint64_t base;
     if (cc < 4) {
-        base = cnt[cc];
+        base = cnt_c;
     } else {
         // '#': everything before the block that is not A/C/G/T/$
         const uint64_t start = blk << 6;
-        base = start - (cnt[0] + cnt[1] + cnt[2] + cnt[3]) - ((ix->dollar_pos < start) ? 1 : 0);
+        base = start - cnt_sum - ((ix->dollar_pos < start) ? 1 : 0);
     }
-    uint32_t k = 0;
-    const uint32_t full = in >> 4;
-    for (uint32_t i = 0; i < 4; i++) {
-        if (i < full) k += dsb_nib_eq_count(sym[i], cc, 16);
-        else if (i == full) k += dsb_nib_eq_count(sym[i], cc, in & 15);
-    }
-    return base + k;
+    const uint64_t x = (p0 ^ (0ull - (uint64_t)(cc & 1))) | (p1 ^ (0ull - (uint64_t)((cc >> 1) & 1))) |
+                       (p2 ^ (0ull - (uint64_t)((cc >> 2) & 1))) | (p3 ^ (0ull - (uint64_t)((cc >> 3) & 1)));
+    const uint64_t low = in ? (~0ull >> (64 - in)) : 0ull;
+    return base + dsb_popc64(~x & low);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -318,21 +323,30 @@ DSB_HDO void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t
 {
     const DsbIndexView *ix = w->ix;
     w->st.ref_bytes += (length + 3) >> 2;
+    if (length == 0) return;
+    // One packed byte = four bases: walk the SOURCE bytes (b0, b0+1, ... or b0, b0-1, ...) and scatter
+    // each byte's bases to their places in dst.  Bytes outside the array read as 0 ('A'), which is also
+    // what a wrapped (negative) position of the reference's unsigned arithmetic gives here.
+    const uint32_t first = (uint32_t)(uni_offset & 3);
+    const int64_t b0 = (int64_t)(uni_offset >> 2);
+    const uint32_t nb = (((is_forward ? first : 3u - first) + length - 1u) >> 2) + 1u;
+    uint32_t j0 = 0, jstep = 1;
 #if defined(DSB_DEVICE_CODE)
     // Short fetches (the 12-base LV windows) land in thread-private arrays, so every lane fills its
     // own copy; long windows always land in the warp's scratch slice and are spread over the lanes.
-    if (length <= 16 || w->solo) {
-        for (uint32_t k = 0; k < length; k++)
-            dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
-        return;
+    const bool spread = !(length <= 16 || w->solo);
+    if (spread) { j0 = threadIdx.x & 31; jstep = 32; }
+#endif
+    for (uint32_t j = j0; j < nb; j += jstep) {
+        const int64_t sb = is_forward ? b0 + (int64_t)j : b0 - (int64_t)j;
+        const uint32_t v = (sb >= 0 && (uint64_t)sb < ix->ref_bin_n) ? (uint32_t)ix->ref_bin[sb] : 0u;
+        for (uint32_t r = 0; r < 4; r++) {
+            const uint32_t k = is_forward ? (4u * j + r - first) : (4u * j + first - r);     // wraps when out of range
+            if (k < length) dst[k] = (uint8_t)((v >> ((3u - r) << 1)) & 3u);
+        }
     }
-    const uint32_t lane = threadIdx.x & 31;
-    for (uint32_t k = lane; k < length; k += 32)
-        dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
-    __syncwarp();
-#else
-    for (uint32_t k = 0; k < length; k++)
-        dst[k] = dsb_ref_base(ix, is_forward ? uni_offset + k : uni_offset - k);
+#if defined(DSB_DEVICE_CODE)
+    if (spread) __syncwarp();
 #endif
 }
 
@@ -361,6 +375,9 @@ DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int3
         ed[i] = (i > 0) ? i : -i;
     }
     mn[DSB_LV_ERROR + 2] = -1; ed[DSB_LV_ERROR + 2] = DSB_LV_ERROR + 2;   // read but never used
+#if defined(DSB_DEVICE_CODE)
+#pragma unroll 1                              // 25 unrolled cells were 26 KB of code: the instruction cache matters more
+#endif
     for (int i = 0; i <= DSB_LV_ERROR; i++) {
         prev_mn = -1;
         cur_mn = i - 1;
@@ -368,6 +385,9 @@ DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int3
         prev_ed = i + 1;
         cur_ed = i;
         next_ed = ed[-i + 1];
+#if defined(DSB_DEVICE_CODE)
+#pragma unroll 1
+#endif
         for (int j = -i; j <= DSB_LV_ERROR; j++) {
             if (cur_mn + j < ref_length - 1) {
                 int m = cur_mn + 1 - cur_ed;
@@ -475,6 +495,65 @@ DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
     const uint32_t n = w->L - (uint32_t)w->ix->ek_len + 1;
     DsbSeed *sv = w->seeds[strand];
     uint32_t ns = 0;
+#if defined(DSB_DEVICE_CODE)
+    {
+        // The scan visits every 3rd k-mer and restarts behind each island, so the visited positions are
+        // data dependent -- but between islands it is a plain strided search for the next set byte: 32
+        // candidates per step (ballot), and the run extension of a hit is a ballot over its neighbours.
+        const int lane = (int)(threadIdx.x & 31);
+        const int nn = (int)n;
+        if (strand == 0) {
+            for (int i = DSB_STEP_EK - 1; i < nn;) {
+                const int c = i + DSB_STEP_EK * lane;
+                const uint32_t m = __ballot_sync(0xffffffffu, c < nn && ex[c] == 1);
+                if (!m) { i += DSB_STEP_EK * 32; continue; }
+                i += DSB_STEP_EK * (__ffs((int)m) - 1);
+                const int b1 = (ex[i - 1] == 1) ? 1 : 0;
+                const int b2 = (b1 && ex[i - 2] == 1) ? 1 : 0;
+                const int len0 = 1 + b1 + b2;
+                int run = 0;
+                for (int jb = 1;; jb += 32) {
+                    const int p = i + jb + lane;
+                    const uint32_t mm = __ballot_sync(0xffffffffu, p < nn && ex[p] == 1);
+                    if (mm != 0xffffffffu) { run += __ffs((int)~mm) - 1; break; }
+                    run += 32;
+                    if (run >= 61 - len0) break;
+                }
+                const int len = len0 + DSB_MIN(run, 61 - len0);      // the reference stops right after len reaches 61
+                const int offset = i - b1 - b2;
+                sv[ns].offset = (uint32_t)offset;
+                sv[ns].len = (uint32_t)len;
+                ns++;
+                i = offset + len + DSB_STEP_EK;
+            }
+        } else {
+            for (int i = nn - DSB_STEP_EK; i >= 0;) {
+                const int c = i - DSB_STEP_EK * lane;
+                const uint32_t m = __ballot_sync(0xffffffffu, c >= 0 && ex[c] == 1);
+                if (!m) { i -= DSB_STEP_EK * 32; continue; }
+                i -= DSB_STEP_EK * (__ffs((int)m) - 1);
+                const int b1 = (ex[i + 1] == 1) ? 1 : 0;
+                const int b2 = (b1 && ex[i + 2] == 1) ? 1 : 0;
+                const int len0 = 1 + b1 + b2;
+                int run = 0;
+                for (int jb = 1;; jb += 32) {
+                    const int p = i - jb - lane;
+                    const uint32_t mm = __ballot_sync(0xffffffffu, p >= 0 && ex[p] == 1);
+                    if (mm != 0xffffffffu) { run += __ffs((int)~mm) - 1; break; }
+                    run += 32;
+                    if (run >= 61 - len0) break;
+                }
+                const int len = len0 + DSB_MIN(run, 61 - len0);
+                const int offset = i + b1 + b2;
+                sv[ns].offset = (uint32_t)(offset - len + 1);
+                sv[ns].len = (uint32_t)len;
+                ns++;
+                i = offset - len - DSB_STEP_EK;
+            }
+        }
+        __syncwarp();
+    }
+#else
     if (strand == 0) {
         for (uint32_t i = DSB_STEP_EK - 1; i < n; i += DSB_STEP_EK) {
             if (ex[i] != 1) continue;
@@ -506,6 +585,7 @@ DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
             i = (int)(offset - len);
         }
     }
+#endif
     // top 1 island per 100 bp window (replayed literally)
     uint32_t total = 0, max_index = 0, max_length = 0, index_end = DSB_SEED_RANGE;
     for (uint32_t m = 0; m < ns; m++) {
@@ -967,16 +1047,74 @@ DSB_HDN void dsb_fast_seeding(DsbWork *w, int dir0, int dir1 /* -1: one strand o
         w->cap_anchor = w->cap_stage;
         w->n_anchor = 0;
         w->solo = 1;
+        // The lanes run their islands in lock-step ROUNDS (one round = one bwt_MEM_search of the island's
+        // k-mer loop plus the map_seed calls it triggers, i.e. one iteration of the loop of
+        // dsb_fast_island): all lanes with work enter dsb_mem_search / dsb_map_seed together, so the
+        // instruction stream is shared instead of 32 private copies fighting for the instruction cache,
+        // while the 32 FM walks still overlap their memory latency.  A lane whose island is finished
+        // pulls the next job at the round boundary.
+        const int l_ek = w->ix->ek_len;
+        const int min_index = 21 - l_ek;
+        bool have = false;
+        uint32_t jb = 0, j_strand = 0, j_ci = 0, start = 0, skip_next = 0;
+        int j = 0;
+        DsbSeed sd = {0, 0, 0};
         for (;;) {
-            const uint32_t j = atomicAdd(w->warp_ctr, 1u);
-            if (j >= n_jobs) break;
-            const uint32_t key = jobs[j].strand_ci;
-            const uint32_t start = w->n_anchor;
-            const uint32_t skip = dsb_fast_island(w, (int)(key >> 31), key & 0x7fffffffu, &sp_set, m_r);
-            jobs[j].start = start;
-            jobs[j].count = w->n_anchor - start;
-            jobs[j].lane = (uint16_t)lane;
-            jobs[j].skip = (uint16_t)skip;
+            if (!have) {
+                jb = atomicAdd(w->warp_ctr, 1u);
+                if (jb < n_jobs) {
+                    const uint32_t key = jobs[jb].strand_ci;
+                    j_strand = key >> 31;
+                    j_ci = key & 0x7fffffffu;
+                    sd = w->seeds[j_strand][j_ci];
+                    j = (int)sd.len - 1;
+                    start = w->n_anchor;
+                    skip_next = 0;
+                    sp_set.l = 0;
+                    have = true;
+                }
+            }
+            if (!__any_sync(0xffffffffu, have)) break;
+            bool finish = false;
+            int n_mem = 0, string_index = 0;
+            const uint8_t *bin_read = w->bin + (j_strand ? w->L : 0);
+            if (have) {
+                if (j < min_index) finish = true;
+                else {
+                    string_index = (int)sd.offset + j + l_ek - 1;
+                    const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
+                    n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
+                }
+            }
+            __syncwarp();
+            int max_score = 0;
+            for (int mi = 0; mi < 2; mi++) {
+                if (have && mi < n_mem) {
+                    m_r[mi].read_offset = string_index - m_r[mi].match_len;
+                    const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD);
+                    max_score = DSB_MAX(c_score, max_score);
+                }
+                __syncwarp();
+            }
+            if (have && !finish) {
+                if (n_mem == 0) j -= 2;
+                else {
+                    j -= 3;
+                    if (max_score > 35) j -= 7;
+                    if (max_score > 256) {
+                        if (max_score > 512) skip_next = 1;
+                        finish = true;
+                    }
+                }
+            }
+            if (have && finish) {
+                dsb_mark_useless(w, start, w->n_anchor);
+                jobs[jb].start = start;
+                jobs[jb].count = w->n_anchor - start;
+                jobs[jb].lane = (uint16_t)lane;
+                jobs[jb].skip = (uint16_t)skip_next;
+                have = false;
+            }
         }
         w->solo = 0;
         __syncwarp();

@@ -160,7 +160,11 @@ static inline uint64_t dsb_fm_reblock(const uint8_t *bwt_occ, uint64_t bwt_bytes
         for (int s = 0; s < 4; s++) {
             DsbFmBlock *o = out + b * 4 + s;
             for (int c = 0; c < 4; c++) o->cnt[c] = cnt[c];
-            memcpy(o->sym, data + 32 * s, 32);
+            for (int pl = 0; pl < 4; pl++) o->plane[pl] = 0;
+            for (int i = 0; i < 64; i++) {              // symbol i: low nibble of byte i/2 for even i (src/bwt.c:52)
+                const uint8_t nib = (uint8_t)((data[32 * s + (i >> 1)] >> ((i & 1) << 2)) & 0xf);
+                for (int pl = 0; pl < 4; pl++) o->plane[pl] |= (uint64_t)((nib >> pl) & 1) << i;
+            }
             for (int i = 0; i < 32; i++) {
                 const uint8_t v = data[32 * s + i];
                 const uint8_t lo = v & 0xf, hi = v >> 4;
@@ -172,7 +176,7 @@ static inline uint64_t dsb_fm_reblock(const uint8_t *bwt_occ, uint64_t bwt_bytes
     }
     DsbFmBlock *t = out + nb * 4;
     for (int c = 0; c < 4; c++) t->cnt[c] = run[c];
-    memset(t->sym, 0, 32);
+    memset(t->plane, 0, 32);
     if (mismatch_hash_count) *mismatch_hash_count = bad;
     return nb * 4 + 1;
 }
