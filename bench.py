@@ -286,9 +286,20 @@ def fm_probe(ix_dir_unused, dev, hbm_peak):
     _o, _c, ms = ix.fm_rank(rows, c, repeat=5)
     ix.close()
     gbs = n * 64 / (ms * 1e-3) / 1e9
+    # the ceiling: plain random gathers of 32 / 64 / 128-byte pieces from an 8 GiB table (no arithmetic)
+    cuda = pydsb.load_cuda_layer()
+    ra = {}
+    for chunk in (32, 64, 128):
+        t = C.c_float(0)
+        rc = cuda.dsb_random_access_probe(dev, C.c_uint64(8 << 30), C.c_uint32(chunk), C.c_uint64(1 << 26), 3, C.byref(t))
+        if rc != 0:
+            raise RuntimeError("dsb_random_access_probe: " + cuda.dsb_last_error().decode())
+        ra["%dB" % chunk] = (1 << 26) * chunk / (t.value * 1e-3) / 1e9
     return {"kernel": "k_fm_rank", "queries": n, "ms": ms, "bytes_per_query": 64, "achieved": gbs, "peak": hbm_peak,
             "unit": "GB/s", "frac": gbs / hbm_peak, "table_bytes": (n_sym // 64) * 64,
-            "note": "one 64 B block (2 sectors) per rank query, random rows, table 16x larger than L2"}
+            "random_access_peak": ra, "frac_of_random_64B": gbs / ra["64B"],
+            "note": "one 64 B block (2 sectors) per rank query, random rows, table 16x larger than L2; "
+                    "random_access_peak = k_random_gather (pure gathers, 8 GiB table) measured in the same run"}
 
 
 def e2e_leg(meta, dev, steps, warmup):

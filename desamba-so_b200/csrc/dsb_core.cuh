@@ -211,8 +211,7 @@ struct DsbWork {
     uint32_t n_sms, cap_sms;
     DsbSms *sms_stage;            // 32 lanes x DSB_SMS_LANE_CAP (dsb_sdp_match)
     uint32_t *h_head[2];          // [0] forward strand table, [1] reverse; 2^key_len entries
-    uint32_t *h_next[2];          // L entries
-    uint32_t *h_kmer[2];          // L entries
+    uint32_t *h_ent[2];           // L entries: (next position + 1) << 8 | (9-mer >> key_len); one load per chain step
     DsbScHash *sc_hash;           // 256 + 2*400
     uint8_t *ref_mid;             // 2000+64  : sdp_middle window  (persistent per warp)
     uint8_t *ref_ext;             // 1000+64+64 : right / left window
@@ -257,13 +256,11 @@ DSB_HD uint32_t dsb_popc64(uint64_t x)
 // occ(bt, r, &c): *c == 0xff means "use the symbol at row r" (written back to *c).
 // Returns the count of *c in BWT[0, r)  (r exclusive), or dollar_pos when
 // the symbol at r is '$'.  The caller adds rank[*c].
-DSB_HDO uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
+DSB_HD uint64_t dsb_occ_ix(const DsbIndexView *ix, uint64_t r, uint8_t *c)
 {
-    const DsbIndexView *ix = w->ix;
     const uint64_t blk = r >> 6;
     const uint32_t in = (uint32_t)(r & 63);
     const DsbFmBlock *b = ix->fm + blk;
-    w->st.occ++;
     uint64_t p0, p1, p2, p3, cnt_c = 0, cnt_sum = 0;
     uint32_t cc = *c;
 #if defined(DSB_DEVICE_CODE)
@@ -305,6 +302,13 @@ DSB_HDO uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
                        (p2 ^ (0ull - (uint64_t)((cc >> 2) & 1))) | (p3 ^ (0ull - (uint64_t)((cc >> 3) & 1)));
     const uint64_t low = in ? (~0ull >> (64 - in)) : 0ull;
     return base + dsb_popc64(~x & low);
+}
+
+// the classifier's out-of-line copy (counts the query)
+DSB_HDO uint64_t dsb_occ(DsbWork *w, uint64_t r, uint8_t *c)
+{
+    w->st.occ++;
+    return dsb_occ_ix(w->ix, r, c);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1559,15 +1563,15 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         if ((int)(1u << key_len) >= q_len) break;
     const uint32_t key_mask = (1u << key_len) - 1u;
     const uint32_t n_pos = (uint32_t)(q_len - DSB_KMER9 + 1);
+    if (w->L >= (1u << 24)) { w->overflow = 2; return key_len; }     // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes)
     for (int c_dir = 2; c_dir >= 1; c_dir--) {
         if ((c_dir & both_dir) == 0) continue;
         const int strand = (c_dir == 2) ? 0 : 1;
         const uint8_t *q = w->bin + (strand ? w->L : 0);
-        uint32_t *head = w->h_head[strand], *next = w->h_next[strand], *kmer = w->h_kmer[strand];
+        uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
 #if defined(DSB_DEVICE_CODE)
         const uint32_t lane = threadIdx.x & 31;
         for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
-        for (uint32_t p = lane; p < n_pos; p += 32) kmer[p] = dsb_kmer9(q + p);
         __syncwarp();
         // Buckets must list positions in ascending order (the reference appends to the tail).  32
         // positions per step, from the highest chunk down: inside a chunk, lanes with the same key
@@ -1576,14 +1580,15 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         for (int32_t cs = (int32_t)((n_pos - 1) & ~31u); cs >= 0; cs -= 32) {
             const uint32_t p = (uint32_t)cs + lane;
             const bool valid = p < n_pos;
-            const uint32_t key = valid ? (kmer[p] & key_mask) : (0x80000000u | lane);
+            const uint32_t km = valid ? dsb_kmer9(q + p) : 0u;
+            const uint32_t key = valid ? (km & key_mask) : (0x80000000u | lane);
             const uint32_t peers = __match_any_sync(0xffffffffu, key);
             const uint32_t higher = peers & ~((2u << lane) - 1u);
             uint32_t nx = 0;
             if (valid) nx = higher ? ((uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u) : head[key];
             __syncwarp();
             if (valid) {
-                next[p] = nx;
+                ent[p] = (nx << 8) | (km >> key_len);
                 if ((peers & ((1u << lane) - 1u)) == 0) head[key] = p + 1;
             }
             __syncwarp();
@@ -1591,9 +1596,9 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
 #else
         for (uint32_t i = 0; i <= key_mask; i++) head[i] = 0;
         for (uint32_t p = n_pos; p-- > 0;) {
-            kmer[p] = dsb_kmer9(q + p);
-            const uint32_t key = kmer[p] & key_mask;
-            next[p] = head[key];
+            const uint32_t km = dsb_kmer9(q + p);
+            const uint32_t key = km & key_mask;
+            ent[p] = (head[key] << 8) | (km >> key_len);
             head[key] = p + 1;
         }
 #endif
@@ -1645,12 +1650,49 @@ DSB_HD void dsb_push_sms(DsbWork *w, uint32_t t_pos, uint32_t q_pos, uint32_t le
     p->t_pos = t_pos; p->q_pos = q_pos; p->len = len;
 }
 
+// One 9-mer hit (window 9-mer number i at offset c_off of the window, read position q_pos): the two exact-run
+// extensions and the acceptance rules of sdp_match (src/cly.c:2341-2378 forward, :2390-2430 backward), by
+// one lane on its own.  Returns whether a match block is emitted.
+DSB_HD bool dsb_extend_hit(const uint8_t *q_str, const uint8_t *t_str, uint32_t t_len, uint32_t q_ed, uint32_t t_st,
+                           bool is_forward, int i_l, long off_l, uint32_t q_pos, uint32_t *o_t, uint32_t *o_q, uint32_t *o_len)
+{
+    const uint8_t *c_t = t_str + off_l;
+    if (is_forward) {
+        const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, 4);
+        if (back_len < 4 || i_l == 4) {
+            uint32_t max_search = q_ed - q_pos - 1;
+            max_search = DSB_MIN(max_search, t_len - (uint32_t)i_l - 1) + DSB_OVER_SEARCH;
+            const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, (int)max_search);
+            const int total_len = back_len + forward_len + 1;
+            if (total_len >= 4) {
+                *o_t = (uint32_t)(i_l - back_len) + t_st; *o_q = q_pos - (uint32_t)back_len; *o_len = (uint32_t)total_len;
+                return true;
+            }
+        }
+    } else {
+        const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, 4);
+        if (forward_len < 4 || i_l == 4) {
+            uint32_t max_search = q_pos;
+            max_search = (uint32_t)(DSB_MIN((long)max_search, off_l)) + DSB_OVER_SEARCH;
+            const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, (int)max_search);
+            const int total_len = back_len + forward_len + 1;
+            if (total_len >= 4) {
+                *o_t = (uint32_t)(off_l - back_len + (long)t_st); *o_q = q_pos - (uint32_t)back_len; *o_len = (uint32_t)total_len;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
+#define DSB_SDP_STAGE 16         // staging slots per lane (dsb_sdp_match)
+
 DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8_t *q_str, const uint8_t *t_str,
                            uint32_t t_len, int key_len, int strand, uint32_t t_st, bool is_forward)
 {
     const uint32_t key_mask = (1u << key_len) - 1u;
     const uint32_t t_kmer_num = t_len - DSB_KMER9 + 1;
-    const uint32_t *head = w->h_head[strand], *nxt = w->h_next[strand], *hk = w->h_kmer[strand];
+    const uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
     w->st.sdp_win++;
 #if defined(DSB_DEVICE_CODE)
     {
@@ -1670,8 +1712,9 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                 node = head[kmer & key_mask];
                 while (node != 0) {
                     const uint32_t qp = node - 1;
-                    if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
-                    node = nxt[qp];
+                    const uint32_t e = ent[qp];
+                    if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
+                    node = e >> 8;
                 }
             }
             if (!__any_sync(0xffffffffu, node != 0)) continue;
@@ -1682,46 +1725,21 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             // sends the whole group of 32 through the serial consumption below instead.
             {
                 DsbSms *my = w->sms_stage + lane * DSB_SMS_LANE_CAP;
-                const uint8_t *c_t = t_str + off_l;
                 uint32_t cnt = 0, nd = node;
                 while (nd != 0 && cnt <= DSB_SMS_LANE_CAP) {
                     const uint32_t q_pos = nd - 1;
                     uint32_t o_t = 0, o_q = 0, o_len = 0;
-                    bool emit = false;
-                    if (is_forward) {
-                        const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, 4);
-                        if (back_len < 4 || i_l == 4) {
-                            uint32_t max_search = q_ed - q_pos - 1;
-                            max_search = DSB_MIN(max_search, t_len - (uint32_t)i_l - 1) + DSB_OVER_SEARCH;
-                            const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, (int)max_search);
-                            const int total_len = back_len + forward_len + 1;
-                            if (total_len >= 4) {
-                                emit = true;
-                                o_t = (uint32_t)(i_l - back_len) + t_st; o_q = q_pos - (uint32_t)back_len; o_len = (uint32_t)total_len;
-                            }
-                        }
-                    } else {
-                        const int forward_len = dsb_run_len_solo(q_str + q_pos + DSB_KMER9, c_t + DSB_KMER9, true, 4);
-                        if (forward_len < 4 || i_l == 4) {
-                            uint32_t max_search = q_pos;
-                            max_search = (uint32_t)(DSB_MIN((long)max_search, off_l)) + DSB_OVER_SEARCH;
-                            const int back_len = dsb_run_len_solo(q_str + q_pos - 1, c_t - 1, false, (int)max_search);
-                            const int total_len = back_len + forward_len + 1;
-                            if (total_len >= 4) {
-                                emit = true;
-                                o_t = (uint32_t)(off_l - back_len + (long)t_st); o_q = q_pos - (uint32_t)back_len; o_len = (uint32_t)total_len;
-                            }
-                        }
-                    }
+                    const bool emit = dsb_extend_hit(q_str, t_str, t_len, q_ed, t_st, is_forward, i_l, off_l, q_pos, &o_t, &o_q, &o_len);
                     if (emit) {
                         if (cnt < DSB_SMS_LANE_CAP) { my[cnt].t_pos = o_t; my[cnt].q_pos = o_q; my[cnt].len = o_len; }
                         cnt++;
                     }
-                    nd = nxt[q_pos];
+                    nd = ent[q_pos] >> 8;
                     while (nd != 0) {
                         const uint32_t qp = nd - 1;
-                        if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
-                        nd = nxt[qp];
+                        const uint32_t e = ent[qp];
+                        if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
+                        nd = e >> 8;
                     }
                 }
                 if (!__any_sync(0xffffffffu, cnt > DSB_SMS_LANE_CAP)) {
@@ -1771,11 +1789,12 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                         }
                     }
                     if ((int)lane == l) {                     // the owner moves to its next hit
-                        node = nxt[q_pos];
+                        node = ent[q_pos] >> 8;
                         while (node != 0) {
                             const uint32_t qp = node - 1;
-                            if (hk[qp] == kmer && qp >= q_bg && qp <= q_ed) break;
-                            node = nxt[qp];
+                            const uint32_t e = ent[qp];
+                            if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
+                            node = e >> 8;
                         }
                     }
                     __syncwarp();
@@ -1793,7 +1812,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             uint32_t node = head[kmer & key_mask];
             while (node != 0) {
                 const uint32_t q_pos = node - 1;
-                if (hk[q_pos] == kmer && q_pos >= q_bg && q_pos <= q_ed) {
+                if ((ent[q_pos] & 0xffu) == (kmer >> key_len) && q_pos >= q_bg && q_pos <= q_ed) {
                     const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, 4);
                     if (back_len < 4 || i == 4) {
                         uint32_t max_search = q_ed - q_pos - 1;
@@ -1804,7 +1823,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                             dsb_push_sms(w, (uint32_t)(i - back_len) + t_st, q_pos - (uint32_t)back_len, (uint32_t)total_len);
                     }
                 }
-                node = nxt[q_pos];
+                node = ent[q_pos] >> 8;
             }
         }
     } else {
@@ -1815,7 +1834,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             uint32_t node = head[kmer & key_mask];
             while (node != 0) {
                 const uint32_t q_pos = node - 1;
-                if (hk[q_pos] == kmer && q_pos >= q_bg && q_pos <= q_ed) {
+                if ((ent[q_pos] & 0xffu) == (kmer >> key_len) && q_pos >= q_bg && q_pos <= q_ed) {
                     const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, 4);
                     if (forward_len < 4 || i == 4) {
                         uint32_t max_search = q_pos;
@@ -1826,7 +1845,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                             dsb_push_sms(w, (uint32_t)(c_off - back_len + (long)t_st), q_pos - (uint32_t)back_len, (uint32_t)total_len);
                     }
                 }
-                node = nxt[q_pos];
+                node = ent[q_pos] >> 8;
             }
         }
     }

@@ -222,18 +222,58 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
 
 
 // bulk primitives (parity known-answer entry + roofline probes)
+// Four independent queries per thread per step: all their block loads are issued before the first
+// popcount, so a thread keeps 4 x 64 bytes of random HBM traffic in flight.
+#define DSB_FM_ILP 4
 __global__ void __launch_bounds__(256) k_fm_rank(const __grid_constant__ DsbIndexView ix, const uint64_t *__restrict__ row,
                                                  const uint8_t *__restrict__ c_in, uint64_t n, uint64_t *__restrict__ out,
                                                  uint8_t *__restrict__ c_out)
 {
-    DsbWork w;
-    w.ix = &ix;
-    w.st.occ = 0;
-    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        uint8_t c = c_in[i];
-        out[i] = dsb_occ(&w, row[i], &c);
-        c_out[i] = c;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i0 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i0 < n; i0 += stride * DSB_FM_ILP) {
+        uint64_t r[DSB_FM_ILP], o[DSB_FM_ILP];
+        uint8_t c[DSB_FM_ILP];
+#pragma unroll
+        for (int u = 0; u < DSB_FM_ILP; u++) {
+            const uint64_t i = i0 + (uint64_t)u * stride;
+            r[u] = (i < n) ? row[i] : 0;
+            c[u] = (i < n) ? c_in[i] : (uint8_t)0;
+        }
+#pragma unroll
+        for (int u = 0; u < DSB_FM_ILP; u++) o[u] = dsb_occ_ix(&ix, r[u], &c[u]);
+#pragma unroll
+        for (int u = 0; u < DSB_FM_ILP; u++) {
+            const uint64_t i = i0 + (uint64_t)u * stride;
+            if (i < n) { out[i] = o[u]; c_out[i] = c[u]; }
+        }
     }
+}
+
+// Random-access roofline probe: every thread gathers `chunk`-byte aligned pieces (32, 64 or 128 bytes) from
+// pseudo-random places of a table far larger than L2, DSB_FM_ILP of them in flight, and folds them into one
+// word.  Its GB/s is the ceiling a rank-query kernel (one 64-byte block per query) can approach.
+template <int CHUNK>
+__global__ void __launch_bounds__(256) k_random_gather(const uint4 *__restrict__ table, uint64_t n_chunks, uint64_t n_access,
+                                                       uint32_t *__restrict__ sink)
+{
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    uint32_t acc = 0;
+    for (uint64_t i0 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i0 < n_access; i0 += stride * DSB_FM_ILP) {
+        uint4 v[DSB_FM_ILP][CHUNK / 16];
+#pragma unroll
+        for (int u = 0; u < DSB_FM_ILP; u++) {
+            uint64_t x = (i0 + (uint64_t)u * stride) * 0x9E3779B97F4A7C15ull;       // splitmix-style scramble
+            x ^= x >> 29; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 32;
+            const uint4 *p = table + (x % n_chunks) * (CHUNK / 16);
+#pragma unroll
+            for (int k = 0; k < CHUNK / 16; k++) v[u][k] = __ldg(p + k);
+        }
+#pragma unroll
+        for (int u = 0; u < DSB_FM_ILP; u++)
+#pragma unroll
+            for (int k = 0; k < CHUNK / 16; k++) acc ^= v[u][k].x ^ v[u][k].y ^ v[u][k].z ^ v[u][k].w;
+    }
+    if (acc == 0x12345679u) sink[0] = acc;                  // keeps the loads alive
 }
 
 __global__ void __launch_bounds__(256) k_exist_flat(const __grid_constant__ DsbIndexView ix, const uint8_t *__restrict__ codes,
@@ -605,6 +645,41 @@ int dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint
     CU(cudaMemcpy(out, d_out, n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(c_out, d_co, n, cudaMemcpyDeviceToHost));
     cudaFree(d_row); cudaFree(d_out); cudaFree(d_c); cudaFree(d_co);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+
+int dsb_random_access_probe(int dev, uint64_t table_bytes, uint32_t chunk_bytes, uint64_t n_access, int repeat, float *ms)
+{
+    CU(cudaSetDevice(dev));
+    if (chunk_bytes != 32 && chunk_bytes != 64 && chunk_bytes != 128) { g_err = "chunk_bytes must be 32, 64 or 128"; return -1; }
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    uint4 *table = nullptr;
+    uint32_t *sink = nullptr;
+    cudaEvent_t e0, e1;
+    CU(cudaMalloc((void **)&table, table_bytes));
+    CU(cudaMalloc((void **)&sink, 64));
+    CU(cudaMemset(table, 0x5a, table_bytes));
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    const int grid = prop.multiProcessorCount * 8;
+    const uint64_t n_chunks = table_bytes / chunk_bytes;
+    if (repeat < 1) repeat = 1;
+    for (int r = -1; r < repeat; r++) {
+        if (r == 0) CU(cudaEventRecord(e0));
+        if (chunk_bytes == 32) k_random_gather<32><<<grid, 256>>>(table, n_chunks, n_access, sink);
+        else if (chunk_bytes == 64) k_random_gather<64><<<grid, 256>>>(table, n_chunks, n_access, sink);
+        else k_random_gather<128><<<grid, 256>>>(table, n_chunks, n_access, sink);
+    }
+    CU(cudaEventRecord(e1));
+    CU(cudaDeviceSynchronize());
+    CU(cudaGetLastError());
+    g_launches += repeat + 1;
+    float t = 0;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (ms) *ms = t / repeat;
+    cudaFree(table); cudaFree(sink);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return 0;
 }

@@ -45,7 +45,7 @@ struct DsbScratchDims {
     uint32_t cap_stage;     // anchors one lane may stage during fast seeding
     // byte offsets inside a slice
     size_t o_seeds0, o_seeds1, o_anchors, o_anchors_tmp, o_chains, o_chains_tmp, o_sort_a, o_sort_b, o_score_v,
-        o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms_stage, o_sms, o_head0, o_head1, o_next0, o_next1, o_kmer0, o_kmer1, o_sc_hash, o_ref_mid, o_ref_ext;
+        o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms_stage, o_sms, o_head0, o_head1, o_ent0, o_ent1, o_sc_hash, o_ref_mid, o_ref_ext;
     size_t bytes;           // slice size (multiple of 256)
 };
 
@@ -81,14 +81,12 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     DSB_TAKE(o_jobs, (size_t)d->cap_jobs * sizeof(DsbJob));
     DSB_TAKE(o_stage, (size_t)32 * d->cap_stage * sizeof(DsbAnchor));
     DSB_TAKE(o_lane_priv, (size_t)32 * DSB_LANE_PRIV_BYTES);
-    DSB_TAKE(o_sms_stage, (size_t)32 * DSB_SMS_LANE_CAP * sizeof(DsbSms));
+    DSB_TAKE(o_sms_stage, (size_t)32 * DSB_SDP_STAGE * sizeof(DsbSms));
     DSB_TAKE(o_sms, (size_t)cap_sms * sizeof(DsbSms));
     DSB_TAKE(o_head0, (size_t)d->head_entries * 4);
     DSB_TAKE(o_head1, (size_t)d->head_entries * 4);
-    DSB_TAKE(o_next0, (size_t)Lmax * 4);
-    DSB_TAKE(o_next1, (size_t)Lmax * 4);
-    DSB_TAKE(o_kmer0, (size_t)Lmax * 4);
-    DSB_TAKE(o_kmer1, (size_t)Lmax * 4);
+    DSB_TAKE(o_ent0, (size_t)Lmax * 4);
+    DSB_TAKE(o_ent1, (size_t)Lmax * 4);
     DSB_TAKE(o_sc_hash, (256 + 2 * 400 + 8) * sizeof(DsbScHash));
     DSB_TAKE(o_ref_mid, 2000 + 128);
     DSB_TAKE(o_ref_ext, 1000 + 192);
@@ -122,10 +120,8 @@ DSB_HD void dsb_bind_scratch(DsbWork *w, uint8_t *base, const DsbScratchDims *d)
     w->cap_sms = d->cap_sms;
     w->h_head[0] = (uint32_t *)(base + d->o_head0);
     w->h_head[1] = (uint32_t *)(base + d->o_head1);
-    w->h_next[0] = (uint32_t *)(base + d->o_next0);
-    w->h_next[1] = (uint32_t *)(base + d->o_next1);
-    w->h_kmer[0] = (uint32_t *)(base + d->o_kmer0);
-    w->h_kmer[1] = (uint32_t *)(base + d->o_kmer1);
+    w->h_ent[0] = (uint32_t *)(base + d->o_ent0);
+    w->h_ent[1] = (uint32_t *)(base + d->o_ent1);
     w->sc_hash = (DsbScHash *)(base + d->o_sc_hash);
     w->ref_mid = base + d->o_ref_mid;
     w->ref_ext = base + d->o_ref_ext;

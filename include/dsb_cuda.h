@@ -137,6 +137,10 @@ int  dsb_slot_rerun_device(dsb_slot *s);
  * known-answer entry of the parity tests. */
 int  dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint64_t n, uint64_t *out,
                        uint8_t *c_out, int repeat, float *ms);
+/* Random-access roofline probe (measurement aid, no index needed): gather n_access aligned pieces of
+ * chunk_bytes (32, 64 or 128) from pseudo-random places of a table_bytes device buffer; *ms = mean kernel time.
+ * n_access * chunk_bytes / time is the ceiling the FM-search kernel is reported against (bench.py). */
+int  dsb_random_access_probe(int dev, uint64_t table_bytes, uint32_t chunk_bytes, uint64_t n_access, int repeat, float *ms);
 /* Exist-k-mer probes in bulk for 2-bit coded strings (test / roofline entry): exist[i] for every
  * k-mer start of codes[0..n), same rule as k_exist.  Host pointers. */
 int  dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist, int repeat, float *ms);

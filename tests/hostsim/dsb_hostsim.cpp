@@ -278,3 +278,11 @@ int dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *ex
 }
 
 }  // extern "C"
+
+extern "C" int dsb_random_access_probe(int dev, uint64_t table_bytes, uint32_t chunk_bytes, uint64_t n_access, int repeat, float *ms)
+{
+    (void)dev; (void)table_bytes; (void)chunk_bytes; (void)n_access; (void)repeat;
+    if (ms) *ms = 0;
+    g_err = "the host simulator has no memory system to probe";
+    return -1;
+}

@@ -83,9 +83,11 @@ def test_batch_size_and_rerun_do_not_change_results(mixed):
 
 
 def test_cfg2_full_size_against_reference(have_ref_binary):
-    """BASELINE.json configs[1] at full size: 10 000 x 5 kb reads on the 50 Mbp index.  The reference's own
-    output depends on uninitialised stack bytes for a fraction of a percent of the reads (DESIGN.md
-    'reference-undefined reads'); every other read must be identical, and order must be preserved."""
+    """BASELINE.json configs[1] at full size: 10 000 x 5 kb reads on the 50 Mbp index, reads in file order.
+    Every read whose reference answer is DEFINED must be identical.  A read is reference-undefined when some
+    instrumented build of the unmodified reference sources (zero- / pattern-initialised automatic variables, -O1
+    frame layout; oracle/Makefile `twins`) classifies it differently from the stock binary, i.e. the reference's
+    own answer depends on uninitialised or out-of-bounds stack bytes."""
     if not have_ref_binary:
         pytest.skip("reference binary absent")
     import dataset
@@ -94,7 +96,11 @@ def test_cfg2_full_size_against_reference(have_ref_binary):
     gold = open(meta["golden"], "rb").read()
     got, want = sam_records(out), sam_records(gold)
     assert list(got) == list(want)                       # same reads, same order
-    bad = [k for k in want if got[k] != want[k]]
-    assert len(bad) <= 0.005 * len(want), (len(bad), bad[:5])
+    bad = {k for k in want if got[k] != want[k]}
+    undefined = dataset.undefined_reads(meta)
+    assert len(undefined) <= 0.01 * len(want), len(undefined)
+    assert bad <= undefined, sorted(bad - undefined)[:5]
+    print("cfg2: %d reads, %d reference-undefined, %d of those differ; all %d defined reads identical" %
+          (len(want), len(undefined), len(bad), len(want) - len(undefined)))
     # idempotence / batch independence at full size
     assert run_cli(meta["idx"], meta["reads"], env={"DSB_BATCH_READS": "1500"}) == out

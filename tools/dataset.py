@@ -172,6 +172,47 @@ def build(name, log=sys.stderr, golden=True):
     return meta
 
 
+TWINS = ("deSAMBA_zinit", "deSAMBA_pinit", "deSAMBA_o1")
+
+
+def _records_by_read(path):
+    out = {}
+    for line in open(path, "rb"):
+        f = line.rstrip(b"\n").split(b"\t")
+        out.setdefault(f[0], []).append((f[1:6], f[11:12]))
+    return out
+
+
+def undefined_reads(meta, log=sys.stderr):
+    """Names of the reads whose REFERENCE answer is not defined by the reference's source: any instrumented
+    build of the unmodified sources (oracle/Makefile `twins`: zero- / pattern-initialised automatic variables,
+    -O1 frame layout) classifies them differently from the stock -O3 binary at -t 1.  Cached per data set."""
+    path = os.path.join(meta["dir"], "undefined.txt")
+    if os.path.exists(path):
+        return set(open(path).read().split())
+    stock = _records_by_read(meta["golden"])
+    bad = set()
+    for tw in TWINS:
+        b = os.path.join(ROOT, "oracle", "_ref", tw)
+        if not os.path.exists(b):
+            raise RuntimeError("%s is missing: run `make -C oracle twins` where /root/reference exists" % b)
+        out = os.path.join(meta["dir"], tw + ".sam")
+        t0 = time.time()
+        with open(out, "wb") as fo:
+            r = subprocess.run([b, "classify", "-t", "1", "-f", "SAM", meta["idx"] + "/", meta["reads"]], stdout=fo,
+                               stderr=subprocess.PIPE)
+        if r.returncode != 0:
+            print("[dataset] twin %s crashed on %s (rc %d): every read it did not reach counts as undefined" %
+                  (tw, meta["name"], r.returncode), file=log)
+        other = _records_by_read(out)
+        d = {k.decode() for k in stock if other.get(k) != stock[k]}
+        print("[dataset] %s vs stock on %s: %d reads differ, %.1fs" % (tw, meta["name"], len(d), time.time() - t0), file=log)
+        bad |= d
+    with open(path, "w") as fh:
+        fh.write("\n".join(sorted(bad)) + "\n")
+    return bad
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("name")
