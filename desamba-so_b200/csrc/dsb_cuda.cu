@@ -152,7 +152,10 @@ __global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexV
 }
 
 // persistent: every warp pulls the next read of the (longest-first) order until none is left
-__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS) k_classify(
+#ifndef DSB_MIN_BLOCKS
+#define DSB_MIN_BLOCKS 6          // 80 registers -> 24 resident warps per SM: the classifier is latency bound (profiles/: 14.6 ms vs 16.9 ms at 96 registers)
+#endif
+__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classify(
     const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, const uint32_t *__restrict__ order,
     uint8_t *__restrict__ bin, const uint8_t *__restrict__ exist, uint8_t *__restrict__ scratch,
     const __grid_constant__ DsbScratchDims dims, dsb_read_result *__restrict__ results, dsb_hit *__restrict__ hits,
