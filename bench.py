@@ -47,6 +47,16 @@ LOCAL_RANK = env_int("LOCAL_RANK", 0)
 WORLD = env_int("WORLD_SIZE", 1)
 
 
+# Only the JSON line may reach stdout: native libraries (NCCL prints its version banner there) get stderr.
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line):
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
 def log(*a):
     print("[bench r%d]" % RANK, *a, file=sys.stderr, flush=True)
 
@@ -173,7 +183,7 @@ def run_reference_arm(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -412,7 +422,7 @@ def run_ours(args):
                                               (gm["n_reads"], cores, s, cpu_model())}
         except Exception as e:
             line["cpu_baseline"] = {"error": str(e)}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
