@@ -359,13 +359,22 @@ DSB_HDO void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t
 // The reference plants '#' / '$' sentinels in place and restores them; we work on private copies.
 // Both strings always have the same length here (every call site passes len, len).
 // Returns the edit distance, or `len` when no alignment with <= 4 edits exists.
+//
+// query_m1 = the byte BEFORE query[0] as the reference sees it.  The diagonal j = i + 1 starts at
+// mn_j = -1 and compares ref[j - 1] with query[-1] (src/cly.c:589); when the query is a pointer into the
+// read (the suffix side) that byte is the previous read base -- real data that decides e.g. whether a
+// 1-base extension with a mismatch returns 0 or 1 -- so callers pass it.  When the query is one of
+// map_seed's stack arrays the byte belongs to another stack object (reference-undefined): callers pass
+// DSB_LV_NO_BYTE, which matches nothing, like the bytes before ref[0].
 // ------------------------------------------------------------------------------------------
-DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len)
+#define DSB_LV_NO_BYTE 0xD0
+DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len, uint8_t query_m1)
 {
     if (len <= 0) return 0;                   // returns 0 whatever the bytes are
     uint8_t rbuf[8 + DSB_LV_L + 2], qbuf[8 + DSB_LV_L + 2];
     uint8_t *ref = rbuf + 8, *query = qbuf + 8;
-    for (int i = 0; i < 8; i++) { rbuf[i] = 0xE0; qbuf[i] = 0xD0; }   // never equal to anything
+    for (int i = 0; i < 8; i++) { rbuf[i] = 0xE0; qbuf[i] = DSB_LV_NO_BYTE; }   // never equal to anything
+    qbuf[7] = query_m1;
     for (int i = 0; i < len; i++) { ref[i] = ref_in[i]; query[i] = query_in[i]; }
     const int32_t ref_length = len, query_length = len;
     ref[ref_length] = '#';
@@ -786,7 +795,7 @@ DSB_HDO void dsb_get_new_ed(DsbWork *w, uint32_t *e_d, uint32_t *len_, uint32_t 
             }
         } while (mtc > 0);
     }
-    *e_d = (uint32_t)dsb_lv_extd(t, q, (int32_t)len);
+    *e_d = (uint32_t)dsb_lv_extd(t, q, (int32_t)len, is_fwd ? (uint8_t)DSB_LV_NO_BYTE : q[-1]);
     *len_ = len;
 }
 
@@ -850,7 +859,7 @@ DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32
             l_pre = DSB_MIN(l_pre, u_off);
             dsb_get_ref(w, t_pre, t_off - 1, l_pre, false);
         }
-        d_pre = (uint32_t)dsb_lv_extd(t_pre, q_pre, (int32_t)l_pre);
+        d_pre = (uint32_t)dsb_lv_extd(t_pre, q_pre, (int32_t)l_pre, DSB_LV_NO_BYTE);
         s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
         if (s < DSB_MIN_S_1 && l_pre == DSB_LV_L && !have_uni) { s = 0; break; }
         if (!have_uni) {
@@ -886,7 +895,7 @@ DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32
                     }
                 } while (mtc > 0);
             }
-            d_suf = (uint32_t)dsb_lv_extd(t_suf, q_suf, (int32_t)l_suf);
+            d_suf = (uint32_t)dsb_lv_extd(t_suf, q_suf, (int32_t)l_suf, q_suf[-1]);
             s += Q_LV[d_suf * 20 + l_suf];
         } else
             l_suf = d_suf = 0;

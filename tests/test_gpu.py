@@ -104,3 +104,23 @@ def test_cfg2_full_size_against_reference(have_ref_binary):
           (len(want), len(undefined), len(bad), len(want) - len(undefined)))
     # idempotence / batch independence at full size
     assert run_cli(meta["idx"], meta["reads"], env={"DSB_BATCH_READS": "1500"}) == out
+
+
+def test_length_error_sweep_against_reference(have_ref_binary):
+    """BASELINE.json configs[3] at test scale: reads of 1 / 10 / 50 kb at 5 % and 20 % error (indel-heavy mix, +-30 %
+    length jitter, 5 % junk reads) on the cfg2 index.  Same rule as cfg2: every reference-defined read identical."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    import dataset
+    summary = []
+    for name in dataset.SWEEP:
+        meta = dataset.build(name)
+        got = sam_records(run_cli(meta["idx"], meta["reads"]))
+        want = sam_records(open(meta["golden"], "rb").read())
+        assert list(got) == list(want), name
+        bad = {k for k in want if got[k] != want[k]}
+        undefined = dataset.undefined_reads(meta)
+        summary.append((name, len(want), len(undefined), len(bad)))
+        assert bad <= undefined, (name, sorted(bad - undefined)[:5])
+        assert len(undefined) <= 0.35 * len(want), (name, len(undefined))     # long reads cross more uninitialised windows
+    print(summary)

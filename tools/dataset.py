@@ -41,6 +41,15 @@ CONFIGS = {
 }
 
 
+# BASELINE.json configs[3] (read-length / error sweep) at test scale, on the cfg2 genomes: ~3 Mbp per cell
+for _L in (1000, 10000, 50000):
+    for _e in (5, 20):
+        CONFIGS["sw_L%d_e%d" % (_L, _e)] = dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
+                                                n_reads=max(40, 3000000 // _L), read_len=_L, err=_e / 100.0,
+                                                read_seed=100 + _L // 1000 + _e, junk=0.05, mix="3,3,4", jitter=0.3)
+SWEEP = [k for k in CONFIGS if k.startswith("sw_")]
+
+
 def data_root():
     return os.environ.get("DSB_DATA", "/tmp/dsb_data")
 
