@@ -1,23 +1,390 @@
-/* dsb_meta.c -- meta_analysis (reference src/cly_mt.c:1083-1235, :1329-1414): SURVEY.md 8(f)
- * rank 1, a "next" row.  Host-side text processing, no GPU involvement.
- * PLACEHOLDER until the hot path meets its parity bar: loading is a no-op and the call aborts
- * loudly instead of returning something that looks like an answer.
+/* dsb_meta.c -- meta_analysis: per-taxon tally of a SAM text (reference src/cly_mt.c:590-670 taxonTree_rank,
+ * :687-813 getOneSAM, :902-961 ana_get_tid, :848-900 ana_meta_loop_fprint, :1083-1235 meta_analysis_core,
+ * :1329-1414 meta_analysis).  SURVEY.md 8(f) rank 1.  Host-side text processing, no GPU involvement.
+ *
+ * The reference round-trips the SAM text through three tmpfiles and parses with strtok(); its answer depends on
+ * strtok's exact token rules, so the record parser below tokenises a private copy of each line with a small
+ * re-entrant tokenizer that has those rules (skip leading delimiters, end the token at the first delimiter and
+ * overwrite it with NUL), issued in the same order.  Two consequences that are kept on purpose:
+ *   * the AS:i:<n> score is never read (the token taken for it is the literal "AS"), so the per-record score is 0;
+ *   * ana_get_tid therefore stops at the first following record: EVERY SAM record, secondary and supplementary
+ *     lines included, is tallied as one "read" (weight 1, or the length of its SEQ field -- 1 for "*").
+ * Where the reference has undefined behaviour we choose a defined one and say so at the place.
  */
 #include "dsb_host.h"
 #include <stdlib.h>
+#include <string.h>
 
-typedef struct dsb_taxonomy { int unused; } dsb_taxonomy;
+#define NO_TID 0xFFFFFFFFu
+#define NAME_MAX_L 200
+
+typedef struct dsb_taxonomy {
+    uint32_t max_tid;              /* tid of the LAST line of nodes.dmp + 1 000 000 (src/cly_mt.c:606-612) */
+    uint32_t *p_tid;
+    char (*rank)[20];
+    char (*name)[NAME_MAX_L + 1];
+} dsb_taxonomy;
+
+/* strtok() with explicit state */
+typedef struct tokz { char *save; } tokz;
+static char *tok(tokz *z, char *s, const char *delim)
+{
+    if (!s) s = z->save;
+    if (!s) return NULL;
+    s += strspn(s, delim);
+    if (*s == 0) { z->save = s; return NULL; }
+    char *start = s;
+    s += strcspn(s, delim);
+    if (*s) { *s = 0; z->save = s + 1; }
+    else z->save = s;
+    return start;
+}
+
+static char *read_line(FILE *fp, char **buf, size_t *cap)
+{
+    return getline(buf, cap, fp) > 0 ? *buf : NULL;
+}
 
 dsb_taxonomy *dsb_taxonomy_load(const char *dir)
 {
-    (void)dir;
-    return NULL;
+    char path[4096];
+    snprintf(path, sizeof path, "%s/nodes.dmp", dir);
+    FILE *fp = fopen(path, "r");
+    if (!fp) return NULL;          /* the reference aborts here; we defer the failure to meta_analysis() */
+    dsb_taxonomy *t = (dsb_taxonomy *)dsb_xcalloc(1, sizeof *t);
+    char *line = NULL;
+    size_t cap = 0;
+    tokz z;
+    uint32_t last = 0;
+    while (read_line(fp, &line, &cap)) {
+        char *a = tok(&z, line, "\t|");
+        if (a) last = (uint32_t)strtoul(a, NULL, 10);
+    }
+    t->max_tid = last + 1000000u;
+    const size_t n = (size_t)t->max_tid + 1;
+    t->p_tid = (uint32_t *)dsb_xmalloc(n * sizeof(uint32_t));
+    t->rank = (char (*)[20])dsb_xcalloc(n, 20);
+    t->name = (char (*)[NAME_MAX_L + 1])dsb_xcalloc(n, NAME_MAX_L + 1);
+    for (size_t i = 0; i < n; i++) t->p_tid[i] = NO_TID;
+    rewind(fp);
+    while (read_line(fp, &line, &cap)) {
+        char *a = tok(&z, line, "\t|");
+        if (!a) continue;
+        const uint32_t tid = (uint32_t)strtoul(a, NULL, 10);
+        char *p = tok(&z, NULL, "\t|");
+        char *r = tok(&z, NULL, "\t|");
+        if (tid > t->max_tid || !p || !r) continue;     /* the reference writes out of bounds / crashes */
+        t->p_tid[tid] = (uint32_t)strtoul(p, NULL, 10);
+        strncpy(t->rank[tid], r, 19);
+    }
+    fclose(fp);
+    t->p_tid[1] = NO_TID;                               /* root of the taxonomy */
+    t->p_tid[0] = NO_TID;                               /* a second one-node tree for unclassified reads */
+    strcpy(t->rank[0], "no rank");
+    strcpy(t->name[0], "CLY_FAIL");
+    snprintf(path, sizeof path, "%s/names.dmp", dir);
+    fp = fopen(path, "r");
+    if (fp) {
+        while (read_line(fp, &line, &cap)) {
+            char *a = tok(&z, line, "|\t");
+            if (!a) continue;
+            const uint32_t tid = (uint32_t)strtoul(a, NULL, 10);
+            char *nm = tok(&z, NULL, "\t|");
+            tok(&z, NULL, "|");                         /* unique-name column */
+            char *cls = tok(&z, NULL, "|");
+            if (tid <= t->max_tid && nm && cls && strncmp("\tscien", cls, 6) == 0) {
+                strncpy(t->name[tid], nm, NAME_MAX_L);
+                t->name[tid][NAME_MAX_L] = 0;
+            }
+        }
+        fclose(fp);
+    }
+    free(line);
+    return t;
+}
+
+/* one SAM record as meta_analysis sees it (RST, src/cly_mt.h:55-63) */
+typedef struct rec {
+    char *name;
+    char cls;                       /* 'C' classified, 'U' unclassified */
+    uint32_t tid, read_length, score;
+    uint8_t mapq;
+    char *seq;
+} rec;
+
+/* getOneSAM: `line` is a private, writable, NUL-terminated copy of one record.  Returns 0, or -1 when the line
+ * is too short to hold the fields the reference dereferences (it would crash there). */
+static int parse_record(char *line, rec *r)
+{
+    tokz z;
+    char *cur = line, *t;
+#define FIELD() do { t = tok(&z, cur, "\t"); if (!t) return -1; cur += strlen(t) + 1; } while (0)
+    FIELD(); r->name = t;
+    FIELD();                                            /* FLAG */
+    r->read_length = 0;
+    r->score = 0;
+    FIELD();                                            /* RNAME */
+    char *seq;
+    if (t[0] == '*') {
+        r->cls = 'U'; r->tid = 0; r->mapq = 0;
+        for (int k = 0; k < 6; k++) FIELD();            /* POS MAPQ CIGAR RNEXT PNEXT TLEN */
+        FIELD(); seq = t;
+    } else {
+        r->cls = 'C';
+        char *ref = t;
+        FIELD();                                        /* POS */
+        FIELD(); r->mapq = (uint8_t)strtoul(t, NULL, 10);
+        for (int k = 0; k < 4; k++) FIELD();            /* CIGAR RNEXT PNEXT TLEN */
+        FIELD(); seq = t;
+        FIELD();                                        /* QUAL */
+        t = tok(&z, NULL, ":");
+        if (t && ((t[0] == 'A' && t[1] == 'S') || (t[0] == 'N' && t[1] == 'M'))) {
+            tok(&z, NULL, ":");
+            t = tok(&z, cur, "\t");                     /* restarts at the tag: yields "AS" / "NM", never the number */
+            if (t) { cur += strlen(t) + 1; r->score = (uint32_t)strtoul(t, NULL, 10); }
+            t = tok(&z, NULL, ":");
+            if (t && t[0] == 'm' && t[1] == 's') {      /* unreachable after the restart above; kept for shape */
+                tok(&z, NULL, ":");
+                t = tok(&z, cur, "\t");
+                if (t) { cur += strlen(t) + 1; r->score = (uint32_t)strtoul(t, NULL, 10); }
+            }
+        }
+        /* "tid|<taxid>|..." : the second '|' token, found by stepping over the first token's NUL */
+        char *rc = ref;
+        tok(&z, ref, "|");
+        rc += strlen(rc) + 1;
+        t = tok(&z, rc, "|");
+        r->tid = t ? (uint32_t)strtoul(t, NULL, 10) : 0;
+    }
+#undef FIELD
+    r->read_length = (uint32_t)strlen(seq);
+    r->seq = seq;
+    return 0;
+}
+
+/* ---- tally (meta_analysis_core) ------------------------------------------------------------- */
+typedef struct count_sort { uint32_t tid; long count; } count_sort;
+static int cmp_count_sort(const void *a_, const void *b_)
+{
+    /* the reference's comparator returns only 0 / 1 (src/cly_mt.c:584-587); with the host libc's qsort --
+     * the same one the reference calls -- that is a stable descending sort */
+    const count_sort *a = (const count_sort *)a_, *b = (const count_sort *)b_;
+    return a->count < b->count;
+}
+
+typedef struct node { uint64_t weight; uint32_t child_begin; } node;
+typedef struct child { uint32_t tid, next; } child;
+
+typedef struct tally {
+    const dsb_taxonomy *tax;
+    node *tab;
+    child *kids;
+    dsb_strbuf *out;
+    uint64_t total_weight;
+} tally;
+
+static void print_leaves(tally *t, uint32_t node_ID)
+{
+    const dsb_taxonomy *tax = t->tax;
+    const node *nd = t->tab + node_ID;
+    if (nd->weight == 0) return;
+    const float rate = (float)nd->weight / t->total_weight;
+    if (nd->child_begin != 0) {
+        uint32_t c = nd->child_begin;
+        for (;;) {
+            print_leaves(t, t->kids[c].tid);
+            if (t->kids[c].next == 0) break;
+            c = t->kids[c].next;
+        }
+        return;
+    }
+    const char *type = "microbe";
+    const uint32_t leaf = node_ID;
+    if (leaf == 0 || leaf == 1)
+        type = "no_match";
+    else {
+        for (uint32_t n = node_ID; n != NO_TID; n = tax->p_tid[n]) {
+            if (n == 9606) { type = "human"; break; }
+            if (n == 33208 || n == 33090) { type = "animal_and_plant"; break; }
+        }
+    }
+    dsb_strbuf_printf(t->out, "%s\t%s|%s\tnull\t%f\n", type, tax->name[leaf], tax->rank[leaf], rate);
+}
+
+/* ana_get_tid: the taxon of the read whose first record is recs[*i]; leaves *i at the first record that is
+ * not consumed (== n at the end of the list) */
+static uint32_t read_tid(const dsb_taxonomy *tax, const rec *recs, size_t n, size_t *i)
+{
+    const rec *first = recs + *i;
+    if (first->cls != 'C') { (*i)++; return 0; }
+    uint32_t tid = 0, score = 0;
+    if (first->tid <= tax->max_tid) { tid = first->tid; score = first->score; }
+    for (;;) {
+        (*i)++;
+        if (*i >= n) return tid;
+        const rec *r = recs + *i;
+        if (strcmp(first->name, r->name) != 0) break;
+        if (score == 0) break;                           /* always: see the header */
+        if (r->score != score) continue;
+        if (r->tid > tax->max_tid) continue;
+        for (uint32_t p = r->tid;;) {                    /* equal score: prefer a descendant of the current pick */
+            if (p == tid) { tid = r->tid; break; }
+            if (p < 1 || p == NO_TID) break;
+            p = tax->p_tid[p];
+        }
+    }
+    return tid;
+}
+
+typedef struct meta_row { char *type, *species, *tech; float rate; } meta_row;
+static int cmp_meta_row(const void *a, const void *b)
+{
+    const float x = ((const meta_row *)a)->rate, y = ((const meta_row *)b)->rate;
+    return x > y ? -1 : (x < y ? 1 : 0);
 }
 
 void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
                             int flag, uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
 {
-    (void)tax; (void)input; (void)input_n; (void)output; (void)output_n; (void)flag; (void)max_snapshot_len;
-    (void)human_snapshot; (void)human_snapshot_n;
-    dsb_fatal("meta_analysis is not implemented in this build yet");
+    if (input_n == 0) {
+        *output_n = 0;
+        *human_snapshot_n = 0;
+        return;
+    }
+    if (!tax) dsb_fatal("meta_analysis: the index directory has no nodes.dmp / names.dmp");
+    /* private, writable, NUL-terminated copy: records are tokenised in place */
+    char *text = (char *)dsb_xmalloc(input_n + 1);
+    memcpy(text, input, input_n);
+    text[input_n] = 0;
+    size_t n_rec = 0, m_rec = 1024;
+    rec *recs = (rec *)dsb_xmalloc(m_rec * sizeof(rec));
+    dsb_strbuf human = {NULL, 0, 0};
+    dsb_strbuf_reserve(&human, 1);
+    char *p = text, *end = text + strlen(text);          /* like getline on a text file: stops at an embedded NUL */
+    int in_header = 1;
+    while (p < end) {
+        char *nl = memchr(p, '\n', (size_t)(end - p));
+        char *next = nl ? nl + 1 : end;
+        if (in_header && *p == '@') { p = next; continue; }     /* skip_sam_head: @SQ / @PG lines */
+        in_header = 0;
+        /* getline keeps the '\n' in the buffer; it then ends up inside the last token, as in the reference */
+        char saved = *next;
+        *next = 0;
+        rec r;
+        if (parse_record(p, &r) != 0) dsb_fatal("meta_analysis: malformed SAM record (the reference crashes here)");
+        *next = saved;
+        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158)) {
+            dsb_strbuf_reserve(&human, r.read_length);
+            memcpy(human.s + human.l, r.seq, r.read_length);
+            human.l += r.read_length;
+        }
+        if (n_rec == m_rec) { m_rec *= 2; recs = (rec *)dsb_xrealloc(recs, m_rec * sizeof(rec)); }
+        recs[n_rec++] = r;
+        p = next;
+    }
+    if (n_rec == 0) {
+        /* the reference returns with *output never assigned and then dereferences it; we return an empty answer */
+        *output = (char *)dsb_xcalloc(1, 1);
+        *output_n = 0;
+        *human_snapshot = NULL;
+        *human_snapshot_n = 0;
+        free(recs); free(text); free(human.s);
+        return;
+    }
+    /* tally per taxon */
+    const size_t n_tid = (size_t)tax->max_tid + 1;
+    uint64_t *node_count = (uint64_t *)dsb_xcalloc(n_tid, sizeof(uint64_t));
+    uint64_t total_weight = 0;
+    for (size_t i = 0; i < n_rec;) {
+        const uint32_t w = ((flag & 0x1) == 0) ? 1u : recs[i].read_length;
+        total_weight += w;
+        const uint32_t tid = read_tid(tax, recs, n_rec, &i);
+        node_count[tid] += w;
+    }
+    size_t n_sort = 0;
+    for (size_t i = 0; i < n_tid; i++) n_sort += node_count[i] != 0;
+    count_sort *srt = (count_sort *)dsb_xmalloc((n_sort + 1) * sizeof(count_sort));
+    n_sort = 0;
+    for (size_t i = 0; i < n_tid; i++)
+        if (node_count[i]) { srt[n_sort].tid = (uint32_t)i; srt[n_sort++].count = (long)node_count[i]; }
+    qsort(srt, n_sort, sizeof(count_sort), cmp_count_sort);
+    /* propagate the weights to the ancestors, registering each child once, in order of first appearance */
+    tally t;
+    t.tax = tax;
+    t.tab = (node *)dsb_xcalloc(n_tid, sizeof(node));
+    t.kids = (child *)dsb_xcalloc(2 * n_tid + 2, sizeof(child));
+    t.total_weight = total_weight;
+    uint32_t n_kids = 1;
+    for (size_t i = 0; i < n_sort; i++) {
+        uint32_t c = srt[i].tid;
+        for (;;) {
+            const uint32_t par = tax->p_tid[c];
+            t.tab[c].weight += node_count[srt[i].tid];
+            if (par == NO_TID) break;
+            if (par > tax->max_tid) break;               /* a parent outside the table: the reference reads out of bounds */
+            if (t.tab[par].child_begin == 0) {
+                t.tab[par].child_begin = n_kids;
+                t.kids[n_kids++].tid = c;
+            } else {
+                uint32_t k = t.tab[par].child_begin;
+                while (t.kids[k].tid != c && t.kids[k].next != 0) k = t.kids[k].next;
+                if (t.kids[k].tid != c) {
+                    t.kids[k].next = n_kids;
+                    t.kids[n_kids++].tid = c;
+                }
+            }
+            c = par;
+        }
+    }
+    dsb_strbuf lines = {NULL, 0, 0};
+    dsb_strbuf_reserve(&lines, 1);
+    lines.s[0] = 0;
+    t.out = &lines;
+    print_leaves(&t, 0);
+    print_leaves(&t, 1);
+    /* ---- meta_analysis proper: snapshot + top-3 table ---------------------------------------- */
+    if (human.l == 0) {
+        *human_snapshot = NULL;
+        *human_snapshot_n = 0;
+    } else {
+        human.s[human.l] = 0;
+        const uint64_t nb = strlen(human.s);
+        *human_snapshot_n = nb < max_snapshot_len ? nb : max_snapshot_len;
+        *human_snapshot = (char *)dsb_xmalloc(*human_snapshot_n + 1);
+        memcpy(*human_snapshot, human.s, *human_snapshot_n);
+        (*human_snapshot)[*human_snapshot_n] = 0;
+    }
+    /* the rates go through their "%f" text (six decimals), exactly as the reference re-reads its own output */
+    size_t n_rows = 0, m_rows = 16;
+    meta_row *rows = (meta_row *)dsb_xmalloc(m_rows * sizeof(meta_row));
+    float no_match_rate = 0;
+    tokz zl;
+    for (char *ln = tok(&zl, lines.s, "\n"); ln; ln = tok(&zl, NULL, "\n")) {
+        tokz zf;
+        meta_row r;
+        r.type = tok(&zf, ln, "\t");
+        r.species = tok(&zf, NULL, "\t");
+        r.tech = tok(&zf, NULL, "\t");
+        char *rate = tok(&zf, NULL, "\t");
+        if (!r.type || !r.species || !r.tech || !rate) continue;
+        r.rate = strtof(rate, NULL);
+        if (strcmp("no_match", r.type) == 0) { no_match_rate += r.rate; continue; }
+        if (n_rows == m_rows) { m_rows *= 2; rows = (meta_row *)dsb_xrealloc(rows, m_rows * sizeof(meta_row)); }
+        rows[n_rows++] = r;
+    }
+    dsb_strbuf res = {NULL, 0, 0};
+    dsb_strbuf_reserve(&res, 64);
+    res.s[0] = 0;
+    if (no_match_rate > 0.95) {
+        dsb_strbuf_printf(&res, "no_match\tnull|null\tnull\t0\n");
+    } else {
+        for (size_t i = 0; i < n_rows; i++) rows[i].rate = rows[i].rate / (1 - no_match_rate);
+        qsort(rows, n_rows, sizeof(meta_row), cmp_meta_row);
+        for (size_t i = 0; i < n_rows; i++)
+            if (i < 3 || (strcmp("human", rows[i].type) == 0 && rows[i].rate > 0.05))
+                dsb_strbuf_printf(&res, "%s\t%s\t%s\t%f\n", rows[i].type, rows[i].species, rows[i].tech, rows[i].rate);
+    }
+    *output = res.s;                                      /* malloc'd, caller frees (desamba.h) */
+    *output_n = res.l;
+    free(rows); free(lines.s); free(t.tab); free(t.kids); free(srt); free(node_count); free(recs); free(text); free(human.s);
 }

@@ -120,3 +120,63 @@ def test_sam_full_format_carries_seq_and_qual(tiny):
     out = run_sim(tiny["idx"], [tiny["reads"]], fmt="SAM_FULL").decode().split("\n")
     prim = [ln.split("\t") for ln in out if ln and not (int(ln.split("\t")[1]) & 0x900)]
     assert prim and all(len(f[9]) == len(f[10]) and (f[9] == "*" or set(f[10]) == {"I"}) for f in prim)
+
+
+def _ref_meta(idx_dir, sams, flag, snap):
+    """meta_analysis of the UNMODIFIED reference library (oracle/_ref/libdesamba.so, the checker), in a child
+    process: the reference prints to stderr and aborts on errors."""
+    code = r'''
+import ctypes as C, sys, pickle
+lib = C.CDLL(sys.argv[1]); libc = C.CDLL(None); libc.free.argtypes = [C.c_void_p]
+idx = C.c_void_p(); lib.load_index(C.byref(idx), sys.argv[2].encode())
+lib.meta_analysis.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int, C.c_int,
+                              C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+sams, flag, snap = pickle.load(open(sys.argv[3], "rb"))
+# the reference creates a thread_id's buffers in read_classify (meta_analysis only looks them up): one short read first
+lib.read_classify.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int, C.c_int]
+fq = b"@w\n" + b"ACGT" * 20 + b"\n+\n" + b"I" * 80 + b"\n"
+o, n = C.c_void_p(), C.c_uint64(0)
+lib.read_classify(idx, fq, len(fq), C.byref(o), C.byref(n), 0, 1)
+res = []
+for s in sams:
+    out, n, hs, hn = C.c_void_p(), C.c_uint64(0), C.c_void_p(), C.c_uint64(0)
+    lib.meta_analysis(idx, s, len(s), C.byref(out), C.byref(n), 0, flag, snap, C.byref(hs), C.byref(hn))
+    res.append((C.string_at(out.value, n.value), C.string_at(hs.value, hn.value) if hs.value else None))
+pickle.dump(res, open(sys.argv[4], "wb"))
+'''
+    import pickle
+    import sys
+    import tempfile
+    d = tempfile.mkdtemp()
+    pickle.dump((sams, flag, snap), open(os.path.join(d, "in.pkl"), "wb"))
+    r = subprocess.run([sys.executable, "-c", code, os.path.join(ROOT, "oracle", "_ref", "libdesamba.so"), idx_dir + "/",
+                        os.path.join(d, "in.pkl"), os.path.join(d, "out.pkl")], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    return pickle.load(open(os.path.join(d, "out.pkl"), "rb"))
+
+
+def test_meta_analysis_equals_reference(tiny, mixed, have_ref_binary):
+    """SURVEY.md 8(f)-1: meta_analysis() on the SAM text of classified reads, both weighting flags, against the
+    reference's own libdesamba.so: SAM and SAM_FULL input, a human (tid 9606) subset for the snapshot, an
+    all-unclassified input (the 'no_match' line), headers, and a truncated snapshot."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdesamba.so")):
+        pytest.skip("reference library absent")
+    import pydsb
+    sam = open(os.path.join(GOLD, "tiny.sam"), "rb").read()
+    full = run_sim(tiny["idx"], [tiny["reads"]], fmt="SAM_FULL")
+    lines = full.split(b"\n")
+    human = b"\n".join(l.replace(b"tid|1003|", b"tid|9606|") for l in lines[:400])
+    unmapped = b"\n".join(l for l in lines if b"\t4\t*\t" in l) + b"\n"
+    header = b"@SQ\tSN:x\tLN:5\n@PG\tID:deSAMBA\n" + sam
+    mixed_sam = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
+    cases = [sam, full, human, unmapped, header, mixed_sam[: mixed_sam.rfind(b"\n", 0, 30000) + 1]]
+    d = pydsb.Desamba(hostsim=True)
+    d.load_index(tiny["idx"])
+    for flag in (0, 1):
+        for snap in (65536, 1000):
+            want = _ref_meta(tiny["idx"], cases, flag, snap)
+            for s, (w_text, w_snap) in zip(cases, want):
+                got_text, got_snap = d.meta_analysis(s, thread_id=0, flag=flag, max_snapshot_len=snap)
+                assert got_text == w_text, (flag, snap, got_text, w_text)
+                assert got_snap == w_snap
+    assert any(w[1] for w in want)                       # the human case produced a snapshot
