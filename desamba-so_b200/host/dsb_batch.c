@@ -413,6 +413,11 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
     int eof = 0;
     s->have_carry = 0;
+    {
+        double t0 = dsb_now();
+        dsb_fq_prescan(f, s->e->fmt_threads);
+        stats->t_parse += dsb_now() - t0;
+    }
     for (uint64_t b = 0; !eof; b++) {
         const int k = (int)(b % (uint64_t)s->n_slots);
         /* batch b reuses the slot of batch b - n_slots: wait until that one has been formatted */

@@ -11,6 +11,7 @@
 #include <string.h>
 #include <unistd.h>
 #include <zlib.h>
+#include <pthread.h>
 
 #define FQ_BUFSIZE (1 << 20)
 
@@ -23,6 +24,9 @@ struct dsb_fq {
     size_t begin, end;
     int is_eof;
     int last_char;
+    /* records found ahead of time by dsb_fq_prescan (memory mode) */
+    dsb_rec_view *pre;
+    size_t pre_n, pre_i;
     /* pending record when the caller's buffer was too small */
     int have_pending;
     dsb_strbuf p_name, p_seq, p_qual;
@@ -141,6 +145,7 @@ void dsb_fq_close(dsb_fq *f)
     if (f->gz) gzclose(f->gz);
     if (f->tmp) fclose(f->tmp);
     if (!f->mem) free(f->buf);
+    free(f->pre);
     free(f->p_name.s);
     free(f->p_seq.s);
     free(f->p_qual.s);
@@ -266,6 +271,7 @@ int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v)
     if (f->have_pending) {              /* a record fetched by dsb_fq_next() that did not fit its buffer */
         f->have_pending = 0;
     } else {
+        if (f->pre_i < f->pre_n) { *v = f->pre[f->pre_i++]; return (int64_t)v->seq_l; }
         if (f->mem && fq_try_fast(f, v)) return (int64_t)v->seq_l;
         f->p_ret = fq_read_record(f);
         if (f->p_ret < 0) return f->p_ret;
@@ -276,4 +282,107 @@ int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v)
     v->is_fastq = f->p_is_fastq;
     v->stable = 0;
     return f->p_ret;
+}
+
+
+/* ---- parallel pre-scan of an in-memory block --------------------------------------------------
+ * The block is cut into n_threads pieces.  Each piece starts at a GUESSED record start: an '@' at the beginning
+ * of a line whose third line starts with '+'.  Every thread runs the fast-path recogniser from its start until it
+ * reaches the next thread's start.  The guesses are then verified left to right: thread t's records are accepted
+ * only if thread t-1 ended EXACTLY where thread t began, i.e. the sequential parser would have arrived at that
+ * byte in the same state.  Whatever is not accepted is parsed by the ordinary sequential path afterwards, so the
+ * result is the sequential result by construction. */
+typedef struct scan_job {
+    const dsb_fq *f;
+    size_t start, limit, end;
+    int ok;                         /* ended by reaching `limit` (not by an unrecognised record) */
+    dsb_rec_view *v;
+    size_t n, m;
+} scan_job;
+
+static void *scan_worker(void *arg)
+{
+    scan_job *j = (scan_job *)arg;
+    dsb_fq tmp = *j->f;             /* private cursor over the shared, read-only block */
+    tmp.begin = j->start;
+    tmp.last_char = 0;
+    j->ok = 0;
+    for (;;) {
+        size_t q = tmp.begin;
+        const unsigned char *b = tmp.buf;
+        while (q < tmp.end && b[q] != '>' && b[q] != '@') q++;
+        if (q >= j->limit) { j->end = q; j->ok = 1; break; }
+        tmp.begin = q;
+        dsb_rec_view v;
+        if (!fq_try_fast(&tmp, &v)) { j->end = q; break; }
+        if (j->n == j->m) {
+            j->m = j->m ? j->m * 2 : 4096;
+            j->v = (dsb_rec_view *)dsb_xrealloc(j->v, j->m * sizeof(dsb_rec_view));
+        }
+        j->v[j->n++] = v;
+    }
+    return NULL;
+}
+
+void dsb_fq_prescan(dsb_fq *f, int n_threads)
+{
+    if (!f->mem || f->have_pending || f->last_char != 0 || f->pre_i < f->pre_n) return;
+    const size_t lo = f->begin, hi = f->end;
+    if (n_threads > 32) n_threads = 32;
+    if (n_threads < 1 || hi - lo < ((size_t)1 << 20)) return;          /* small inputs: not worth the threads */
+    scan_job jobs[32];
+    pthread_t th[32];
+    const unsigned char *b = f->buf;
+    int n = 0;
+    size_t prev = lo;
+    for (int t = 0; t < n_threads; t++) {
+        size_t s = lo + (hi - lo) / (size_t)n_threads * (size_t)t;
+        if (t > 0) {
+            if (s < prev) s = prev;
+            /* next line start holding '@' whose line + 2 starts with '+' */
+            size_t found = hi;
+            for (size_t p = s; p + 1 < hi;) {
+                const unsigned char *nl = (const unsigned char *)memchr(b + p, '\n', hi - p);
+                if (!nl) break;
+                const size_t h = (size_t)(nl - b) + 1;
+                if (h >= hi) break;
+                if (b[h] == '@') {
+                    const unsigned char *e1 = (const unsigned char *)memchr(b + h, '\n', hi - h);
+                    const unsigned char *e2 = e1 ? (const unsigned char *)memchr(e1 + 1, '\n', hi - (size_t)(e1 + 1 - b)) : NULL;
+                    if (e2 && (size_t)(e2 + 1 - b) < hi && e2[1] == '+') { found = h; break; }
+                }
+                p = h;
+            }
+            if (found >= hi) break;
+            s = found;
+            if (s <= prev && n > 0) continue;
+        }
+        memset(&jobs[n], 0, sizeof jobs[n]);
+        jobs[n].f = f;
+        jobs[n].start = s;
+        prev = s + 1;
+        n++;
+    }
+    for (int t = 0; t < n; t++) jobs[t].limit = (t + 1 < n) ? jobs[t + 1].start : hi;
+    for (int t = 1; t < n; t++)
+        if (pthread_create(&th[t], NULL, scan_worker, &jobs[t]) != 0) { jobs[t].ok = -1; }
+    scan_worker(&jobs[0]);
+    for (int t = 1; t < n; t++) if (jobs[t].ok != -1) pthread_join(th[t], NULL);
+    /* accept the verified prefix */
+    size_t total = 0;
+    int k = 0;
+    for (; k < n; k++) {
+        if (jobs[k].ok == -1) break;
+        total += jobs[k].n;
+        if (!(jobs[k].ok == 1 && k + 1 < n && jobs[k].end == jobs[k + 1].start)) { k++; break; }
+    }
+    free(f->pre);
+    f->pre = (dsb_rec_view *)dsb_xmalloc((total ? total : 1) * sizeof(dsb_rec_view));
+    f->pre_n = f->pre_i = 0;
+    for (int t = 0; t < k; t++) {
+        memcpy(f->pre + f->pre_n, jobs[t].v, jobs[t].n * sizeof(dsb_rec_view));
+        f->pre_n += jobs[t].n;
+    }
+    if (k > 0) { f->begin = jobs[k - 1].end; f->last_char = 0; }
+    for (int t = 0; t < n; t++) free(jobs[t].v);
 }

@@ -180,3 +180,64 @@ def test_meta_analysis_equals_reference(tiny, mixed, have_ref_binary):
                 assert got_text == w_text, (flag, snap, got_text, w_text)
                 assert got_snap == w_snap
     assert any(w[1] for w in want)                       # the human case produced a snapshot
+
+
+class _RecView(C.Structure):
+    _fields_ = [("name", C.c_void_p), ("seq", C.c_void_p), ("qual", C.c_void_p), ("name_l", C.c_size_t), ("seq_l", C.c_size_t),
+                ("is_fastq", C.c_int), ("stable", C.c_int)]
+
+
+def _records(lib, text, threads):
+    lib.dsb_fq_open_mem.restype = C.c_void_p
+    lib.dsb_fq_open_mem.argtypes = [C.c_char_p, C.c_uint64]
+    lib.dsb_fq_next_view.restype = C.c_int64
+    lib.dsb_fq_next_view.argtypes = [C.c_void_p, C.POINTER(_RecView)]
+    lib.dsb_fq_prescan.argtypes = [C.c_void_p, C.c_int]
+    lib.dsb_fq_close.argtypes = [C.c_void_p]
+    f = lib.dsb_fq_open_mem(text, len(text))
+    if threads:
+        lib.dsb_fq_prescan(f, threads)
+    out, v = [], _RecView()
+    while True:
+        r = lib.dsb_fq_next_view(f, C.byref(v))
+        if r < 0:
+            out.append(r)
+            break
+        out.append((C.string_at(v.name, v.name_l), C.string_at(v.seq, v.seq_l),
+                    C.string_at(v.qual, v.seq_l) if v.qual else None, v.is_fastq))
+    lib.dsb_fq_close(f)
+    return out
+
+
+def test_parallel_fastq_prescan_equals_sequential_reader(built):
+    """The threaded pre-scan of in-memory input must return exactly the sequential (kseq-semantics) reader's
+    records: plain 4-line FASTQ, qualities that start with '@' or '+', wrapped records, FASTA records, comments,
+    blank lines, a truncated tail."""
+    import random
+    lib = C.CDLL(os.path.join(ROOT, "tests", "hostsim", "libdesamba_hostsim.so"))
+    rng = random.Random(5)
+    parts = []
+    for i in range(9000):
+        L = rng.randint(40, 600)
+        seq = "".join(rng.choice("ACGTN") for _ in range(L))
+        qual = "".join(rng.choice("@+I5>!~") for _ in range(L))
+        kind = rng.random()
+        if kind < 0.90:
+            parts.append("@r%d some comment\n%s\n+\n%s\n" % (i, seq, qual))
+        elif kind < 0.94:
+            h = L // 2
+            parts.append("@w%d\n%s\n%s\n+w%d\n%s\n%s\n" % (i, seq[:h], seq[h:], i, qual[:h], qual[h:]))
+        elif kind < 0.97:
+            parts.append(">f%d\n%s\n" % (i, seq))
+        else:
+            parts.append("\n\n@b%d\n%s\n+\n%s\n\n" % (i, seq, qual))
+    parts.append("@s\nACGTACGT\n+\nIIIII\n")                                  # short quality at the end: kseq returns -2
+    text = "".join(parts).encode()
+    assert len(text) > (2 << 20)
+    want = _records(lib, text, 0)
+    assert len(want) > 8000
+    for threads in (2, 5, 8):
+        assert _records(lib, text, threads) == want
+    clean = "".join(p for p in parts if p.startswith("@r")).encode()
+    assert _records(lib, clean, 8) == _records(lib, clean, 0)
+    assert _records(lib, clean[:-7], 8) == _records(lib, clean[:-7], 0)
