@@ -66,8 +66,11 @@ struct dsb_session {
     dsb_slot **slots;
     batch_meta *meta;
     dsb_history *hist;
-    fmt_pool pool;
+    fmt_pool pool;                  /* formatter helpers (used by the drain thread) */
     fmt_worker_arg pool_arg[MAX_FMT_THREADS];
+    fmt_pool cpool;                 /* staging-copy helpers (used by the producer) */
+    fmt_worker_arg cpool_arg[MAX_FMT_THREADS];
+    const char **copy_src;          /* per read of the batch being filled: where its bases still have to be copied from */
     dsb_strbuf fmt_buf[MAX_FMT_THREADS + 1];
     /* a record that did not fit the previous batch */
     int have_carry;
@@ -97,10 +100,13 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     for (int g = 0; g < want; g++)
         if (dsb_index_upload(&ix->h, first + g, &e->dev[g]) != 0)
             dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
-    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)8 << 20);
+    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)16 << 20);
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     if (ncpu < 1) ncpu = 1;
+    /* one-process-per-GPU launchers (torchrun sets LOCAL_WORLD_SIZE) share the host cores between the ranks */
+    long share = (long)env_u64("LOCAL_WORLD_SIZE", 1);
+    if (share > 1) ncpu = ncpu / share > 0 ? ncpu / share : 1;
     e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 8 ? 8 : ncpu));
     if (e->fmt_threads < 1) e->fmt_threads = 1;
     if (e->fmt_threads > MAX_FMT_THREADS) e->fmt_threads = MAX_FMT_THREADS;
@@ -156,6 +162,28 @@ static void pool_run(fmt_pool *p, void (*fn)(void *, int, int), void *arg)
     }
 }
 
+static void pool_start(fmt_pool *p, fmt_worker_arg *args, int n_workers)
+{
+    pthread_mutex_init(&p->mu, NULL);
+    pthread_cond_init(&p->cv_go, NULL);
+    pthread_cond_init(&p->cv_done, NULL);
+    p->n = n_workers;
+    for (int i = 0; i < p->n; i++) {
+        args[i].p = p;
+        args[i].id = i;
+        if (pthread_create(&p->th[i], NULL, fmt_worker, &args[i]) != 0) { p->n = i; break; }
+    }
+}
+
+static void pool_stop(fmt_pool *p)
+{
+    pthread_mutex_lock(&p->mu);
+    p->quit = 1;
+    pthread_cond_broadcast(&p->cv_go);
+    pthread_mutex_unlock(&p->mu);
+    for (int i = 0; i < p->n; i++) pthread_join(p->th[i], NULL);
+}
+
 dsb_session *dsb_session_create(dsb_engine *e)
 {
     dsb_session *s = (dsb_session *)dsb_xcalloc(1, sizeof *s);
@@ -172,28 +200,18 @@ dsb_session *dsb_session_create(dsb_engine *e)
         s->meta[k].qual_off = (uint64_t *)dsb_xmalloc((size_t)e->batch_reads * 8);
     }
     s->hist = dsb_history_new();
-    fmt_pool *p = &s->pool;
-    pthread_mutex_init(&p->mu, NULL);
-    pthread_cond_init(&p->cv_go, NULL);
-    pthread_cond_init(&p->cv_done, NULL);
-    p->n = e->fmt_threads - 1;
-    for (int i = 0; i < p->n; i++) {
-        s->pool_arg[i].p = p;
-        s->pool_arg[i].id = i;
-        if (pthread_create(&p->th[i], NULL, fmt_worker, &s->pool_arg[i]) != 0) { p->n = i; break; }
-    }
+    pool_start(&s->pool, s->pool_arg, e->fmt_threads - 1);
+    pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > 4 ? 4 : e->fmt_threads) - 1);
+    s->copy_src = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
     return s;
 }
 
 void dsb_session_destroy(dsb_session *s)
 {
     if (!s) return;
-    fmt_pool *p = &s->pool;
-    pthread_mutex_lock(&p->mu);
-    p->quit = 1;
-    pthread_cond_broadcast(&p->cv_go);
-    pthread_mutex_unlock(&p->mu);
-    for (int i = 0; i < p->n; i++) pthread_join(p->th[i], NULL);
+    pool_stop(&s->pool);
+    pool_stop(&s->cpool);
+    free(s->copy_src);
     for (int k = 0; k < s->n_slots; k++) {
         dsb_slot_free(s->slots[k]);
         free(s->meta[k].names.s);
@@ -207,6 +225,19 @@ void dsb_session_destroy(dsb_session *s)
     free(s->meta);
     dsb_history_free(s->hist);
     free(s);
+}
+
+typedef struct copy_job { dsb_session *s; char *seq; const dsb_read_desc *desc; uint32_t n; uint64_t bases; } copy_job;
+
+static void copy_seq_part(void *arg, int part, int n_parts)
+{
+    const copy_job *j = (const copy_job *)arg;
+    const uint64_t lo = j->bases * (uint64_t)part / (uint64_t)n_parts, hi = j->bases * (uint64_t)(part + 1) / (uint64_t)n_parts;
+    /* reads whose first base falls into [lo, hi): found by bisection on the ascending offsets */
+    uint32_t a = 0, b = j->n;
+    while (a < b) { const uint32_t mid = (a + b) / 2; if (j->desc[mid].seq_off < lo) a = mid + 1; else b = mid; }
+    for (uint32_t i = a; i < j->n && j->desc[i].seq_off < hi; i++)
+        if (j->s->copy_src[i]) memcpy(j->seq + j->desc[i].seq_off, j->s->copy_src[i], j->desc[i].len);
 }
 
 /* parse up to one batch into slot k; returns number of reads (0 = input exhausted) */
@@ -240,10 +271,14 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
             s->have_carry = 1;
             break;
         }
-        memcpy(seq + bases, v.seq, L);
+        /* a stable view's bases stay where they are until the copy helpers move the whole batch at once; the
+         * history model only needs to READ them, from wherever they live */
+        const char *src = v.seq;
+        if (v.stable) s->copy_src[n] = v.seq;
+        else { memcpy(seq + bases, v.seq, L); s->copy_src[n] = NULL; src = seq + bases; }
         desc[n].seq_off = bases;
         desc[n].len = (uint32_t)L;
-        desc[n].flags = dsb_history_next(s->hist, seq + bases, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES));
+        desc[n].flags = dsb_history_next(s->hist, src, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES));
         if (L >= 40) dsb_history_note_max(s->hist, (uint32_t)L);
         m->name_off[n] = m->names.l;
         dsb_strbuf_reserve(&m->names, v.name_l + 1);
@@ -267,6 +302,10 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
     }
     m->n_reads = n;
     m->n_bases = bases;
+    if (n) {
+        copy_job cj = {s, seq, desc, n, bases};
+        pool_run(&s->cpool, copy_seq_part, &cj);
+    }
     return n;
 }
 
