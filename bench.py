@@ -62,7 +62,9 @@ def log(*a):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons of this rank's GPU, sampled during the timed region."""
+    """SM clock and throttle reasons of this rank's GPU, sampled through NVML every 10 ms during the timed regions."""
+
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
     def __init__(self, gpu):
         super().__init__(daemon=True)
@@ -71,29 +73,40 @@ class ClockSampler(threading.Thread):
         self.reasons = set()
         self.sm_max = None
         self.stop_flag = False
+        self.active = False          # samples are kept only while a timed region is open
+
+    def _nvml_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        ids = [x for x in vis.split(",") if x.strip()]
+        if ids and all(x.strip().isdigit() for x in ids) and self.gpu < len(ids):
+            return int(ids[self.gpu])
+        return self.gpu
 
     def run(self):
-        q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.hw_slowdown,clocks_throttle_reasons.hw_thermal_slowdown," \
-            "clocks_throttle_reasons.sw_thermal_slowdown,clocks_throttle_reasons.sw_power_cap"
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self._nvml_index())
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+        except Exception as e:
+            log("clock sampler: NVML unavailable (%s)" % e)
+            return
         while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
-                                     stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, timeout=5).stdout.decode().strip()
-                f = [x.strip() for x in out.split(",")]
-                self.samples.append(float(f[0]))
-                self.sm_max = float(f[1])
-                for n, v in zip(names, f[2:]):
-                    if v.lower().startswith("active"):
-                        self.reasons.add(n)
-            except Exception:
-                pass
-            time.sleep(0.2)
+            if self.active:
+                try:
+                    self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)))
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                    for n, bit in self.REASONS:
+                        if r & bit:
+                            self.reasons.add(n)
+                except Exception:
+                    pass
+            time.sleep(0.01)
 
     def result(self):
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "how": "NVML, 10 ms period, during the timed kernel loop and the timed e2e calls"}
 
 
 def dist_setup():
@@ -312,7 +325,19 @@ def fm_probe(ix_dir_unused, dev, hbm_peak):
                     "random_access_peak = k_random_gather (pure gathers, 8 GiB table) measured in the same run"}
 
 
-def e2e_leg(meta, dev, steps, warmup):
+def ncu_traffic(n_reads, n_bases):
+    """dram bytes read + written by one k_classify launch, from the committed `ncu --set full` capture of this
+    same workload (profiles/ncu_k_classify_traffic.json; a profiler number cannot be taken inside a timed run)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_k_classify_traffic.json")))
+        if t.get("n_reads") == n_reads and t.get("n_bases") == n_bases:
+            return float(t["dram_bytes_read"]) + float(t["dram_bytes_write"]), t.get("source")
+    except Exception:
+        pass
+    return None, None
+
+
+def e2e_leg(meta, dev, steps, warmup, sampler=None):
     """read_classify() of libdesamba.so on FASTQ text held in host memory; wall clock around each call."""
     import pydsb
     os.environ["DSB_GPUS"] = "1"
@@ -324,11 +349,15 @@ def e2e_leg(meta, dev, steps, warmup):
     for _ in range(max(1, warmup)):
         n_sam = len(d.read_classify(text, thread_id=0, thread_num=1))
     dt = 0.0
+    if sampler is not None:
+        sampler.active = True
     for _ in range(steps):
         t, n = d.read_classify_timed(text, thread_id=0, thread_num=1)   # the C call + free(), as a C caller would
         if n != n_sam:
             raise RuntimeError("read_classify returned %d bytes, expected %d" % (n, n_sam))
         dt += t
+    if sampler is not None:
+        sampler.active = False
     return dt / steps, n_sam
 
 
@@ -359,6 +388,7 @@ def run_ours(args):
     sampler = ClockSampler(LOCAL_RANK)
     sampler.start()
     barrier(dist)
+    sampler.active = True
     launches0 = batch.cuda.dsb_kernel_launch_count()
     ms_total = ms_exist = ms_classify = 0.0
     t0 = time.perf_counter()
@@ -368,18 +398,19 @@ def run_ours(args):
         ms_exist += b
         ms_classify += c
     wall = time.perf_counter() - t0
+    sampler.active = False
     barrier(dist)
     launches = batch.cuda.dsb_kernel_launch_count() - launches0
-    sampler.stop_flag = True
-    sampler.join(timeout=2)
     t_dev = max_over_ranks(dist, ms_total * 1e-3)
     bases_all = sum_over_ranks(dist, float(batch.n_bases))
     value = bases_all * args.steps / t_dev / 1e6
     counters = batch.counters
     d2h = batch.d2h_bytes()
     # end to end through the public API (every rank runs it; max over ranks)
-    e2e_s, n_sam = e2e_leg(meta, LOCAL_RANK, args.steps, args.warmup)
+    e2e_s, n_sam = e2e_leg(meta, LOCAL_RANK, args.steps, args.warmup, sampler)
     barrier(dist)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
     e2e_t = max_over_ranks(dist, e2e_s)
     e2e_value = bases_all / e2e_t / 1e6
     if RANK != 0:
@@ -388,6 +419,7 @@ def run_ours(args):
     alg = algorithmic_bytes(counters, batch.n_bases)
     k_ms = ms_classify / args.steps
     achieved = alg / (k_ms * 1e-3) / 1e9
+    traffic, traffic_src = ncu_traffic(batch.n_reads, batch.n_bases)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -402,7 +434,8 @@ def run_ours(args):
         "gpu_launches": launches,
         "kernel_ms": {"exist": ms_exist / args.steps, "classify": k_ms, "total": ms_total / args.steps},
         "roofline": {"bound": "hbm", "kernel": "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None, "algorithmic_bytes": alg, "peak_source": peak_src},
+                     "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "algorithmic_bytes": alg, "peak_source": peak_src},
         "counters": counters,
         "clocks": sampler.result(),
     }

@@ -22,7 +22,9 @@
 #include "dsb_core.cuh"
 #include "dsb_layout.cuh"
 
+#ifndef DSB_CLASSIFY_THREADS
 #define DSB_CLASSIFY_THREADS 128
+#endif
 
 static thread_local std::string g_err;
 static std::atomic<int> g_launches{0};
@@ -183,6 +185,10 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
         w.exist[1] = w.exist[0] + d.len;
         w.overflow = 0;
         memset(&w.st, 0, sizeof w.st);
+#if defined(DSB_READ_CYCLES)
+        unsigned long long t_begin;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
+#endif
         dsb_classify_read(&w);
         __syncwarp();
         uint32_t hit_off = 0;
@@ -208,6 +214,13 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
         if (lane == 0) {
             dsb_read_result rr;
             rr.hit_off = hit_off; rr.n_hit = w.n_chain; rr.fast_classify = w.fast_classify; rr.n_anchor = w.n_anchor;
+#if defined(DSB_READ_CYCLES)
+            // profiling build (tools/read_times.py): when this read started and how long it took, in microseconds
+            unsigned long long t_end;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+            rr.hit_off = (uint32_t)(t_begin / 1000);
+            rr.n_anchor = (uint32_t)((t_end - t_begin) / 1000);
+#endif
             results[r] = rr;
             dsb_counters *cn = &ctrl->counters;
 #define DSB_ADD(field, val) if (val) atomicAdd((unsigned long long *)&cn->field, (unsigned long long)(val))

@@ -76,7 +76,8 @@ def main():
 
     agg = {}
     keys = ["# Samples", "stall_long_sb", "stall_no_inst", "stall_wait", "stall_short_sb", "stall_branch_resolving",
-            "Instructions Executed", "Thread Instructions Executed"]
+            "Instructions Executed", "Thread Instructions Executed", "L2 Theoretical Sectors Global",
+            "L2 Theoretical Sectors Local"]
     hot = []
     for i, r in enumerate(body):
         f = func_of(i)
@@ -89,11 +90,15 @@ def main():
         hot.append((int(float(r[col["# Samples"]] or 0)), f, r[col["Source"]].strip(), int(float(r[col["stall_long_sb"]] or 0))))
     tot = sum(a[0] for a in agg.values()) or 1
     tot_i = sum(a[6] for a in agg.values()) or 1
-    print("%-28s %7s %6s %8s %8s %8s %8s %6s %6s" % ("function", "samples", "%", "long_sb", "no_inst", "wait", "inst(M)", "inst%", "thr"))
+    print("%-28s %7s %6s %8s %8s %8s %8s %6s %6s %9s %9s" % ("function", "samples", "%", "long_sb", "no_inst", "wait", "inst(M)",
+                                                             "inst%", "thr", "gsect(M)", "lsect(M)"))
     for f, a in sorted(agg.items(), key=lambda kv: -kv[1][0]):
-        print("%-28s %7d %6.1f %8d %8d %8d %8.1f %6.1f %6.1f" % (f, a[0], 100.0 * a[0] / tot, a[1], a[2], a[3], a[6] / 1e6,
-                                                              100.0 * a[6] / tot_i, a[7] / a[6] if a[6] else 0))
-    print("total samples %d, warp instructions %.2f G" % (tot, tot_i / 1e9))
+        print("%-28s %7d %6.1f %8d %8d %8d %8.1f %6.1f %6.1f %9.1f %9.1f" % (
+            f, a[0], 100.0 * a[0] / tot, a[1], a[2], a[3], a[6] / 1e6, 100.0 * a[6] / tot_i, a[7] / a[6] if a[6] else 0,
+            a[8] / 1e6, a[9] / 1e6))
+    print("total samples %d, warp instructions %.2f G; gsect/lsect = sectors the global / local accesses would move with no "
+          "L1 (L2 Theoretical Sectors), %.0f M / %.0f M in total" % (tot, tot_i / 1e9, sum(a[8] for a in agg.values()) / 1e6,
+                                                                      sum(a[9] for a in agg.values()) / 1e6))
     if n_lines:
         print()
         for s, f, src, lsb in sorted(hot, key=lambda x: -x[0])[:n_lines]:
