@@ -268,6 +268,9 @@ class DeviceBatch:
         self.n_hits = n_hits.value
         a, b, c = C.c_float(0), C.c_float(0), C.c_float(0)
         self.cuda.dsb_slot_timing(self.slot, C.byref(a), C.byref(b), C.byref(c))
+        i, sd, sc = C.c_float(0), C.c_float(0), C.c_float(0)
+        self.split = bool(self.cuda.dsb_slot_timing_stages(self.slot, C.byref(i), C.byref(sd), C.byref(sc)))
+        self.stage_ms = {"k_islands": i.value, "k_seed": sd.value, "k_classify": sc.value}
         return a.value, b.value, c.value
 
     def submit(self):
@@ -432,7 +435,8 @@ def run_ours(args):
                 "api": "read_classify() of libdesamba.so: FASTQ text -> SAM_FULL text (%d bytes)" % n_sam,
                 "ms_per_step": 1e3 * e2e_t},
         "gpu_launches": launches,
-        "kernel_ms": {"exist": ms_exist / args.steps, "classify": k_ms, "total": ms_total / args.steps},
+        "kernel_ms": {"exist": ms_exist / args.steps, "classify": k_ms, "total": ms_total / args.steps,
+                      "classify_stages_last_step": batch.stage_ms if batch.split else None},
         "roofline": {"bound": "hbm", "kernel": "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes": alg, "peak_source": peak_src},

@@ -166,6 +166,21 @@ struct DsbJob {
     uint16_t skip;                // the island ended with max_score > 512: the serial loop skips island ci+1
 };
 
+// Split pipeline (device): k_islands lists every read's top islands in one batch-wide job list, k_seed runs them ONE
+// LANE PER ISLAND with lanes of a warp working on islands of different reads, k_classify picks the anchors up again.
+struct DsbSeedJob {
+    uint32_t read;                // read index in the batch
+    uint32_t strand_ci;           // as DsbJob
+    uint32_t offset, len;         // the island (DsbSeed)
+    uint32_t a_off, count;        // its anchors in the batch's anchor pool (written by k_seed)
+    uint32_t skip;                // as DsbJob
+    uint32_t pad;
+};
+struct DsbReadSeeds {             // per read, written by k_islands
+    uint32_t job_base, n_jobs;    // its jobs, in the serial order (dir0's islands, then dir1's)
+    uint32_t total_score[2];
+};
+
 #define DSB_LANE_MEMS 8           // MEM slots of a lane working alone (fast mode keeps <= 2 rows per search)
 #define DSB_LANE_PRIV_BYTES (512 * 8 + DSB_LANE_MEMS * 32)
 
@@ -2474,6 +2489,42 @@ DSB_HDN void dsb_detect_primary(DsbWork *w)
 // src/cly.c:3059-3127).  On entry w->bin / w->exist / arenas are set; on exit w->chains[0..n_chain)
 // are the reported hits in output order.
 // ------------------------------------------------------------------------------------------
+// everything after fast seeding (src/cly.c:3096-3127); have_islands = w->seeds hold this read's islands
+DSB_HDN void dsb_classify_tail(DsbWork *w, int dir0, int dir1, bool both_direction, bool have_islands)
+{
+    DSB_PHASE_BEGIN();
+    dsb_resolve_tree(w);
+    DSB_PHASE_END(w, 2);
+    bool run_slow_mode = false;
+    if (w->n_chain <= 0)
+        run_slow_mode = true;
+    else if (w->chains[0].anchor_number < 5) {                              // super_repeat is always 0 (SURVEY.md Q14)
+        run_slow_mode = true;
+        if (w->L <= 300 && w->chains[0].sum_score > 200) run_slow_mode = false;
+    }
+    if (run_slow_mode && !w->overflow) {
+        w->st.slow++;
+        w->n_anchor = 0;
+        if (!have_islands) {                                                // split pipeline: the islands stayed in k_islands
+            dsb_islands(w, 0);
+            dsb_islands(w, 1);
+        }
+        dsb_slow_classify(w, dir0);
+        dsb_resolve_tree(w);
+        if (both_direction || w->n_chain <= 0 || (w->chains[0].anchor_number < 5)) {
+            dsb_slow_classify(w, dir1);                                     // appends (SURVEY.md Q20)
+            dsb_resolve_tree(w);
+        }
+        DSB_PHASE_END(w, 3);
+    }
+    if (w->overflow) return;
+    dsb_delete_small_score_rst(w);
+    if (w->overflow) return;
+    DSB_PHASE_BEGIN2();
+    dsb_detect_primary(w);
+    DSB_PHASE_END(w, 6);
+}
+
 DSB_HDN void dsb_classify_read(DsbWork *w)
 {
     w->n_anchor = 0;
@@ -2491,30 +2542,38 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     const bool both_direction = ((s0 - s1) <= (s0 >> 3));
     dsb_fast_seeding(w, dir0, both_direction ? dir1 : -1);
     DSB_PHASE_END(w, 1);
-    dsb_resolve_tree(w);
-    DSB_PHASE_END(w, 2);
-    bool run_slow_mode = false;
-    if (w->n_chain <= 0)
-        run_slow_mode = true;
-    else if (w->chains[0].anchor_number < 5) {                              // super_repeat is always 0 (SURVEY.md Q14)
-        run_slow_mode = true;
-        if (w->L <= 300 && w->chains[0].sum_score > 200) run_slow_mode = false;
-    }
-    if (run_slow_mode && !w->overflow) {
-        w->st.slow++;
-        w->n_anchor = 0;
-        dsb_slow_classify(w, dir0);
-        dsb_resolve_tree(w);
-        if (both_direction || w->n_chain <= 0 || (w->chains[0].anchor_number < 5)) {
-            dsb_slow_classify(w, dir1);                                     // appends (SURVEY.md Q20)
-            dsb_resolve_tree(w);
-        }
-        DSB_PHASE_END(w, 3);
-    }
-    if (w->overflow) return;
-    dsb_delete_small_score_rst(w);
-    if (w->overflow) return;
-    DSB_PHASE_BEGIN2();
-    dsb_detect_primary(w);
-    DSB_PHASE_END(w, 6);
+    dsb_classify_tail(w, dir0, dir1, both_direction, true);
 }
+
+#if defined(__CUDACC__)
+// Split pipeline, last kernel: the read's islands were searched by k_seed; append their anchors in island order and
+// drop the islands the serial loop would have skipped (the merge of dsb_fast_seeding), then carry on as usual.
+__device__ __noinline__ void dsb_classify_seeded(DsbWork *w, const DsbReadSeeds *rs, const DsbSeedJob *jobs, const DsbAnchor *pool)
+{
+    w->n_anchor = 0;
+    w->n_chain = 0;
+    w->fast_classify = 1;
+    if (w->L < 40) return;
+    w->total_score[0] = rs->total_score[0];
+    w->total_score[1] = rs->total_score[1];
+    int dir0 = 0, dir1 = 1;
+    if (w->total_score[0] < w->total_score[1]) { dir0 = 1; dir1 = 0; }
+    const uint32_t s0 = w->total_score[dir0], s1 = w->total_score[dir1];
+    const bool both_direction = ((s0 - s1) <= (s0 >> 3));
+    const DsbSeedJob *jv = jobs + rs->job_base;
+    uint32_t skip_key = 0xffffffffu;
+    for (uint32_t j = 0; j < rs->n_jobs; j++) {
+        const DsbSeedJob jb = jv[j];
+        if (jb.strand_ci == skip_key) { skip_key = 0xffffffffu; continue; }   // `ci++` of src/cly.c:1533
+        skip_key = jb.skip ? jb.strand_ci + 1 : 0xffffffffu;
+        if (jb.count == 0) continue;
+        if (w->n_anchor + jb.count > w->cap_anchor) { w->overflow = 1; return; }
+        const DsbAnchor *src = pool + jb.a_off;
+        DsbAnchor *dst = w->anchors + w->n_anchor;
+        for (uint32_t k = threadIdx.x & 31; k < jb.count; k += 32) dst[k] = src[k];
+        w->n_anchor += jb.count;
+    }
+    __syncwarp();
+    dsb_classify_tail(w, dir0, dir1, both_direction, false);
+}
+#endif

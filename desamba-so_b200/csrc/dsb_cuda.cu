@@ -46,7 +46,11 @@ static int fail(const char *what, cudaError_t e)
 struct DsbCtrl {
     uint32_t next_read;      // work queue head of k_classify
     uint32_t n_hits;         // hit arena allocator
-    uint32_t overflow;       // bit0 arena too small, bit1 reference would abort, bit2 hit arena too small
+    uint32_t overflow;       // bit0 arena too small, bit1 reference would abort, bit2 hit arena too small, bit3 anchor pool / job list too small
+    uint32_t next_island_read;   // work queue head of k_islands
+    uint32_t n_jobs;         // job list allocator (k_islands), then the job count k_seed works through
+    uint32_t next_job;       // work queue head of k_seed
+    uint32_t n_pool;         // anchor pool allocator (k_seed)
     uint32_t pad;
     dsb_counters counters;
 };
@@ -84,6 +88,12 @@ struct dsb_slot {
     uint32_t *d_order;
     uint8_t *d_scratch;
     size_t scratch_bytes;
+    // split pipeline (k_islands -> k_seed -> k_classify)
+    bool split;
+    DsbReadSeeds *d_rinfo;
+    DsbSeedJob *d_jobs;
+    DsbAnchor *d_pool;
+    uint32_t cap_jobs, cap_pool;
     uint32_t cap_hits, h_cap_hits;
     uint32_t cap_anchor, cap_sms;
     DsbScratchDims dims;
@@ -93,8 +103,8 @@ struct dsb_slot {
     uint64_t n_bases;
     uint32_t Lmax;
     bool in_flight;
-    cudaEvent_t ev[6];              // 0 start, 1 after H2D+encode, 2 after exist, 3 after classify, 4 end
-    float ms_total, ms_exist, ms_classify;
+    cudaEvent_t ev[8];              // 0 start, 1 after H2D+encode, 2 after exist, 3 after classify, 4 end, 6 after islands, 7 after seeding
+    float ms_total, ms_exist, ms_classify, ms_islands, ms_seed;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -153,6 +163,229 @@ __global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexV
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// split pipeline: k_islands -> k_seed -> k_classify (seeded)
+// ------------------------------------------------------------------------------------------
+// Split pipeline, middle kernel: the body of one persistent warp of k_seed.  Same lock-step rounds as the device
+// branch of dsb_fast_seeding, but the 32 lanes pull islands from the BATCH's job list, so a warp stays full whatever
+// the number of top islands of a single read is (5 kb reads have a handful, which left 3-4 lanes of 32 busy).
+// A finished island's anchors move from the lane's staging area to the batch's anchor pool.
+// w: bound to the warp's scratch slice; bin_base / desc: the batch.  Returns through jobs[], pool, *n_pool, w->st.
+static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_desc *desc, uint8_t *bin_base, DsbSeedJob *jobs, uint32_t n_jobs,
+                           uint32_t *next_job, DsbAnchor *pool, uint32_t cap_pool, uint32_t *n_pool)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    uint8_t *priv = w->lane_priv + (size_t)lane * DSB_LANE_PRIV_BYTES;
+    DsbSpSet sp_set = {(uint64_t *)priv, 0, DSB_SP_SET_MAX, 1};
+    DsbMem *m_r = (DsbMem *)(priv + 512 * 8);
+    w->anchors = w->stage + (size_t)lane * w->cap_stage;
+    w->cap_anchor = w->cap_stage;
+    w->n_anchor = 0;
+    w->solo = 1;
+    const int l_ek = w->ix->ek_len;
+    const int min_index = 21 - l_ek;
+    bool have = false, dry = false;
+    uint32_t jb = 0, j_strand = 0, skip_next = 0;
+    int j = 0;
+    DsbSeed sd = {0, 0, 0};
+    for (;;) {
+        const uint32_t need = __ballot_sync(0xffffffffu, !have && !dry);
+        if (need) {
+            const int leader = __ffs((int)need) - 1;
+            uint32_t base = 0;
+            if ((int)lane == leader) base = atomicAdd(next_job, (uint32_t)__popc(need));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (!have && !dry) {
+                jb = base + (uint32_t)__popc(need & ((1u << lane) - 1u));
+                if (jb < n_jobs) {
+                    const DsbSeedJob job = jobs[jb];
+                    const dsb_read_desc d = desc[job.read];
+                    w->bin = bin_base + dsb_bin_off(d.seq_off, job.read) + DSB_HEAD_PAD;
+                    w->L = d.len;
+                    j_strand = job.strand_ci >> 31;
+                    sd.offset = job.offset; sd.len = job.len;
+                    j = (int)sd.len - 1;
+                    w->n_anchor = 0;
+                    skip_next = 0;
+                    sp_set.l = 0;
+                    have = true;
+                } else
+                    dry = true;
+            }
+        }
+        if (!__any_sync(0xffffffffu, have)) break;
+        bool finish = false;
+        int n_mem = 0, string_index = 0;
+        const uint8_t *bin_read = w->bin + (j_strand ? w->L : 0);
+        if (have) {
+            if (j < min_index) finish = true;
+            else {
+                string_index = (int)sd.offset + j + l_ek - 1;
+                const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
+                n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
+            }
+        }
+        __syncwarp();
+        int max_score = 0;
+        for (int mi = 0; mi < 2; mi++) {
+            if (have && mi < n_mem) {
+                m_r[mi].read_offset = string_index - m_r[mi].match_len;
+                const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD);
+                max_score = DSB_MAX(c_score, max_score);
+            }
+            __syncwarp();
+        }
+        if (have && !finish) {
+            if (n_mem == 0) j -= 2;
+            else {
+                j -= 3;
+                if (max_score > 35) j -= 7;
+                if (max_score > 256) {
+                    if (max_score > 512) skip_next = 1;
+                    finish = true;
+                }
+            }
+        }
+        if (have && finish) {
+            dsb_mark_useless(w, 0, w->n_anchor);
+            const uint32_t cnt = w->n_anchor;
+            uint32_t off = 0;
+            if (cnt) {
+                off = atomicAdd(n_pool, cnt);
+                if (off + cnt > cap_pool) w->overflow |= 8u;
+                else
+                    for (uint32_t k = 0; k < cnt; k++) pool[off + k] = w->anchors[k];
+            }
+            jobs[jb].a_off = off;
+            jobs[jb].count = cnt;
+            jobs[jb].skip = skip_next;
+            have = false;
+        }
+    }
+    w->solo = 0;
+    __syncwarp();
+}
+
+#ifndef DSB_MIN_BLOCKS
+#define DSB_MIN_BLOCKS 6          // 80 registers -> 24 resident warps per SM: the classifier is latency bound (profiles/: 14.6 ms vs 16.9 ms at 96 registers)
+#endif
+
+// warp per read: the exist-k-mer islands of both strands, then the read's top islands as jobs of the batch-wide list
+__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_islands(
+    const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, const uint32_t *__restrict__ order,
+    uint8_t *__restrict__ bin, const uint8_t *__restrict__ exist, uint8_t *__restrict__ scratch,
+    const __grid_constant__ DsbScratchDims dims, DsbReadSeeds *__restrict__ rinfo, DsbSeedJob *__restrict__ jobs,
+    uint32_t cap_jobs, uint32_t n_reads, DsbCtrl *ctrl)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    DsbWork w;
+    memset(&w, 0, sizeof w);
+    w.ix = &ix;
+    dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
+    unsigned long long cyc = 0;
+    for (;;) {
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(&ctrl->next_island_read, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot >= n_reads) break;
+        const uint32_t r = order[slot];
+        const dsb_read_desc d = desc[r];
+        DsbReadSeeds rs = {0, 0, {0, 0}};
+        if (d.len >= 40) {
+            const long long t0 = clock64();
+            w.bin = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
+            w.L = d.len;
+            w.exist[0] = exist + 2 * d.seq_off;
+            w.exist[1] = w.exist[0] + d.len;
+            dsb_islands(&w, 0);
+            dsb_islands(&w, 1);
+            rs.total_score[0] = w.total_score[0];
+            rs.total_score[1] = w.total_score[1];
+            int dir0 = 0, dir1 = 1;
+            if (w.total_score[0] < w.total_score[1]) { dir0 = 1; dir1 = 0; }
+            const uint32_t s0 = w.total_score[dir0], s1 = w.total_score[dir1];
+            const bool both_direction = ((s0 - s1) <= (s0 >> 3));
+            // count the top islands, reserve their jobs, write them in the serial order
+            uint32_t cnt = 0;
+            for (int pass = 0; pass < (both_direction ? 2 : 1); pass++) {
+                const int strand = pass ? dir1 : dir0;
+                const DsbSeed *sv = w.seeds[strand];
+                const uint32_t nsv = w.n_seeds[strand];
+                for (uint32_t c0 = 0; c0 < nsv; c0 += 32) {
+                    const uint32_t ci = c0 + lane;
+                    cnt += (uint32_t)__popc(__ballot_sync(0xffffffffu, ci < nsv && sv[ci].top != 0));
+                }
+            }
+            uint32_t base = 0;
+            if (lane == 0 && cnt) base = atomicAdd(&ctrl->n_jobs, cnt);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + cnt > cap_jobs) {
+                if (lane == 0) atomicOr(&ctrl->overflow, 8u);
+            } else {
+                uint32_t k = base;
+                for (int pass = 0; pass < (both_direction ? 2 : 1); pass++) {
+                    const int strand = pass ? dir1 : dir0;
+                    const DsbSeed *sv = w.seeds[strand];
+                    const uint32_t nsv = w.n_seeds[strand];
+                    for (uint32_t c0 = 0; c0 < nsv; c0 += 32) {
+                        const uint32_t ci = c0 + lane;
+                        const bool top = ci < nsv && sv[ci].top != 0;
+                        const uint32_t m = __ballot_sync(0xffffffffu, top);
+                        if (top) {
+                            DsbSeedJob jb;
+                            jb.read = r; jb.strand_ci = ((uint32_t)strand << 31) | ci;
+                            jb.offset = sv[ci].offset; jb.len = sv[ci].len;
+                            jb.a_off = 0; jb.count = 0; jb.skip = 0; jb.pad = 0;
+                            jobs[k + (uint32_t)__popc(m & ((1u << lane) - 1u))] = jb;
+                        }
+                        k += (uint32_t)__popc(m);
+                    }
+                }
+                rs.job_base = base;
+                rs.n_jobs = cnt;
+            }
+            cyc += (unsigned long long)(clock64() - t0);
+        }
+        if (lane == 0) rinfo[r] = rs;
+        __syncwarp();
+    }
+    if (lane == 0 && cyc) atomicAdd((unsigned long long *)&ctrl->counters.phase_cycles[0], cyc);
+}
+
+// persistent warps, ONE LANE PER ISLAND of the whole batch
+__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_seed(
+    const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, uint8_t *__restrict__ bin,
+    uint8_t *__restrict__ scratch, const __grid_constant__ DsbScratchDims dims, DsbSeedJob *__restrict__ jobs,
+    DsbAnchor *__restrict__ pool, uint32_t cap_pool, DsbCtrl *ctrl)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_jobs = ctrl->n_jobs;
+    DsbWork w;
+    memset(&w, 0, sizeof w);
+    w.ix = &ix;
+    dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
+    const long long t0 = clock64();
+    dsb_seed_jobs(&w, desc, bin, jobs, n_jobs, &ctrl->next_job, pool, cap_pool, &ctrl->n_pool);
+    const unsigned long long cyc = (unsigned long long)(clock64() - t0);
+    // every lane counted its own work
+    if (__any_sync(0xffffffffu, w.overflow != 0)) {
+        const uint32_t of = __reduce_or_sync(0xffffffffu, w.overflow);
+        if (lane == 0) atomicOr(&ctrl->overflow, of);
+    }
+    dsb_counters *cn = &ctrl->counters;
+#define DSB_FOLD_ADD(field, val) do { const unsigned long long v_ = (val); unsigned long long s_ = v_; \
+        for (int o_ = 16; o_ > 0; o_ >>= 1) s_ += __shfl_xor_sync(0xffffffffu, s_, o_); \
+        if (lane == 0 && s_) atomicAdd((unsigned long long *)&cn->field, s_); } while (0)
+    DSB_FOLD_ADD(occ_queries, w.st.occ); DSB_FOLD_ADD(lut_lookups, w.st.lut); DSB_FOLD_ADD(sa_lookups, w.st.sa);
+    DSB_FOLD_ADD(unitig_reads, w.st.unitig); DSB_FOLD_ADD(refpos_reads, w.st.refpos);
+    DSB_FOLD_ADD(ref_window_bytes, w.st.ref_bytes); DSB_FOLD_ADD(mem_searches, w.st.mem_search);
+    DSB_FOLD_ADD(map_seeds, w.st.map_seed);
+#undef DSB_FOLD_ADD
+    if (lane == 0) atomicAdd((unsigned long long *)&cn->phase_cycles[1], cyc);
+}
+
 // persistent: every warp pulls the next read of the (longest-first) order until none is left
 #ifndef DSB_MIN_BLOCKS
 #define DSB_MIN_BLOCKS 6          // 80 registers -> 24 resident warps per SM: the classifier is latency bound (profiles/: 14.6 ms vs 16.9 ms at 96 registers)
@@ -161,7 +394,8 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
     const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, const uint32_t *__restrict__ order,
     uint8_t *__restrict__ bin, const uint8_t *__restrict__ exist, uint8_t *__restrict__ scratch,
     const __grid_constant__ DsbScratchDims dims, dsb_read_result *__restrict__ results, dsb_hit *__restrict__ hits,
-    uint32_t cap_hits, uint32_t n_reads, DsbCtrl *ctrl)
+    uint32_t cap_hits, uint32_t n_reads, DsbCtrl *ctrl,
+    const DsbReadSeeds *__restrict__ rinfo, const DsbSeedJob *__restrict__ jobs, const DsbAnchor *__restrict__ pool)
 {
     __shared__ uint32_t s_job_ctr[DSB_CLASSIFY_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31;
@@ -189,7 +423,11 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
         unsigned long long t_begin;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
 #endif
-        dsb_classify_read(&w);
+        if (rinfo) {                                   // split pipeline: islands and fast seeding were done by k_islands / k_seed
+            const DsbReadSeeds rs = rinfo[r];
+            dsb_classify_seeded(&w, &rs, jobs, pool);
+        } else
+            dsb_classify_read(&w);
         __syncwarp();
         uint32_t hit_off = 0;
         if (lane == 0) {
@@ -442,7 +680,8 @@ void dsb_slot_free(dsb_slot *s)
     cudaFreeHost(s->h_hits); cudaFreeHost(s->h_ctrl); cudaFreeHost(s->h_order);
     cudaFree(s->d_seq); cudaFree(s->d_desc); cudaFree(s->d_edge); cudaFree(s->d_bin); cudaFree(s->d_exist);
     cudaFree(s->d_results); cudaFree(s->d_hits); cudaFree(s->d_ctrl); cudaFree(s->d_order); cudaFree(s->d_scratch);
-    for (int i = 0; i < 6; i++) if (s->ev[i]) cudaEventDestroy(s->ev[i]);
+    cudaFree(s->d_rinfo); cudaFree(s->d_jobs); cudaFree(s->d_pool);
+    for (int i = 0; i < 8; i++) if (s->ev[i]) cudaEventDestroy(s->ev[i]);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
 }
@@ -460,7 +699,7 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
     int rc = 0;
 #define TRY(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { rc = fail(#call, e_); goto done; } } while (0)
     TRY(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 6; i++) TRY(cudaEventCreate(&s->ev[i]));
+    for (int i = 0; i < 8; i++) TRY(cudaEventCreate(&s->ev[i]));
     TRY(cudaHostAlloc((void **)&s->h_seq, max_bases + 64, cudaHostAllocDefault));
     TRY(cudaHostAlloc((void **)&s->h_desc, (size_t)max_reads * sizeof(dsb_read_desc), cudaHostAllocDefault));
     TRY(cudaHostAlloc((void **)&s->h_edge, edge_bytes, cudaHostAllocDefault));
@@ -488,6 +727,18 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
     }
     s->cap_anchor = 2048;
     s->cap_sms = 8192;
+    {
+        const char *e = getenv("DSB_SPLIT");
+        s->split = !(e && atoi(e) == 0);
+        if (s->split) {
+            // every read lists at most 2 * (L / 100 + 2) top islands
+            s->cap_jobs = (uint32_t)(max_bases / 50) + 12u * max_reads + 64u;
+            TRY(cudaMalloc((void **)&s->d_rinfo, (size_t)max_reads * sizeof(DsbReadSeeds)));
+            TRY(cudaMalloc((void **)&s->d_jobs, (size_t)s->cap_jobs * sizeof(DsbSeedJob)));
+            s->cap_pool = (uint32_t)(max_bases / 8) + 64u * max_reads + 1024u;
+            TRY(cudaMalloc((void **)&s->d_pool, (size_t)s->cap_pool * sizeof(DsbAnchor)));
+        }
+    }
     if (ensure_hits(s, max_reads * 8u + 4096u)) { rc = -1; goto done; }
     s->h_cap_hits = s->cap_hits;
     TRY(cudaHostAlloc((void **)&s->h_hits, (size_t)s->h_cap_hits * sizeof(dsb_hit), cudaHostAllocDefault));
@@ -521,8 +772,23 @@ static int launch_kernels(dsb_slot *s)
     const int warps_per_block = s->threads / 32;
     int blocks = (int)((n + warps_per_block - 1) / warps_per_block);
     if (blocks > s->blocks) blocks = s->blocks;
-    k_classify<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
-                                                       s->dims, s->d_results, s->d_hits, s->cap_hits, n, s->d_ctrl);
+    if (s->split) {
+        k_islands<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
+                                                          s->dims, s->d_rinfo, s->d_jobs, s->cap_jobs, n, s->d_ctrl);
+        CU(cudaEventRecord(s->ev[6], s->stream));
+        // the island jobs of the whole batch, one lane each: always the full persistent grid
+        k_seed<<<s->blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_scratch, s->dims, s->d_jobs,
+                                                         s->d_pool, s->cap_pool, s->d_ctrl);
+        CU(cudaEventRecord(s->ev[7], s->stream));
+        k_classify<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
+                                                           s->dims, s->d_results, s->d_hits, s->cap_hits, n, s->d_ctrl,
+                                                           s->d_rinfo, s->d_jobs, s->d_pool);
+        g_launches += 2;
+    } else {
+        k_classify<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
+                                                           s->dims, s->d_results, s->d_hits, s->cap_hits, n, s->d_ctrl,
+                                                           nullptr, nullptr, nullptr);
+    }
     CU(cudaEventRecord(s->ev[3], s->stream));
     CU(cudaGetLastError());
     g_launches += 3;
@@ -599,6 +865,13 @@ int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **
         if (of & 4u) {
             if (ensure_hits(s, s->cap_hits * 4u)) return -1;
         }
+        if (of & 8u) {                                 // anchor pool (or job list) of the split pipeline
+            cudaFree(s->d_pool); cudaFree(s->d_jobs);
+            s->d_pool = nullptr; s->d_jobs = nullptr;
+            s->cap_pool *= 2; s->cap_jobs *= 2;
+            CU(cudaMalloc((void **)&s->d_pool, (size_t)s->cap_pool * sizeof(DsbAnchor)));
+            CU(cudaMalloc((void **)&s->d_jobs, (size_t)s->cap_jobs * sizeof(DsbSeedJob)));
+        }
         if (launch_kernels(s)) return -1;
     }
     const uint32_t nh = s->h_ctrl->n_hits;
@@ -615,6 +888,11 @@ int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **
     cudaEventElapsedTime(&s->ms_total, s->ev[0], s->ev[4]);
     cudaEventElapsedTime(&s->ms_exist, s->ev[1], s->ev[2]);
     cudaEventElapsedTime(&s->ms_classify, s->ev[2], s->ev[3]);
+    s->ms_islands = s->ms_seed = 0.f;
+    if (s->split) {
+        cudaEventElapsedTime(&s->ms_islands, s->ev[2], s->ev[6]);
+        cudaEventElapsedTime(&s->ms_seed, s->ev[6], s->ev[7]);
+    }
     s->in_flight = false;
     *results = s->h_results;
     *hits = s->h_hits;
@@ -629,6 +907,14 @@ int dsb_slot_timing(dsb_slot *s, float *ms_total, float *ms_exist, float *ms_cla
     *ms_exist = s->ms_exist;
     *ms_classify = s->ms_classify;
     return 0;
+}
+
+int dsb_slot_timing_stages(dsb_slot *s, float *ms_islands, float *ms_seed, float *ms_score)
+{
+    *ms_islands = s->ms_islands;
+    *ms_seed = s->ms_seed;
+    *ms_score = s->ms_classify - s->ms_islands - s->ms_seed;
+    return s->split ? 1 : 0;
 }
 
 int dsb_fm_rank_batch(dsb_index *ix, const uint64_t *row, const uint8_t *c, uint64_t n, uint64_t *out, uint8_t *c_out,

@@ -125,6 +125,10 @@ int  dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit *
                    uint32_t *n_hits, dsb_counters *counters);
 /* Device time of the slot's last batch in ms: whole batch and the classify kernel alone. */
 int  dsb_slot_timing(dsb_slot *s, float *ms_total, float *ms_exist, float *ms_classify);
+/* The classify stage is three launches (k_islands, k_seed, k_classify) unless DSB_SPLIT=0 selected the single-kernel
+ * form when the slot was created: their device times of the last batch.  Returns 1 in the split form, else 0
+ * (then ms_score = the whole stage). */
+int  dsb_slot_timing_stages(dsb_slot *s, float *ms_islands, float *ms_seed, float *ms_score);
 
 /* Device-resident variants used by bench.py's `value` leg (inputs already in HBM):
  * re-run the kernels of the last submitted batch without any host<->device copy. */

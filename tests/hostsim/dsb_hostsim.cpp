@@ -239,6 +239,7 @@ int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **
     return 0;
 }
 
+int dsb_slot_timing_stages(dsb_slot *, float *a, float *b, float *c) { *a = *b = *c = 0.f; return 0; }
 int dsb_slot_timing(dsb_slot *s, float *a, float *b, float *c)
 {
     (void)s;
