@@ -166,6 +166,117 @@ __global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexV
 // ------------------------------------------------------------------------------------------
 // split pipeline: k_islands -> k_seed -> k_classify (seeded)
 // ------------------------------------------------------------------------------------------
+// Lock-step forms of the FM seeding primitives for k_seed.  Every lane of `mask` calls them together with its own
+// job and an `act` flag; loops run `while (any lane still has work)` with the work predicated, so the lanes meet again
+// at every iteration instead of finishing their loops one after the other (in the per-lane forms the single-row walk
+// ran with ONE active thread per instruction: ncu, profiles/).  Results per lane are those of dsb_sp_set_insert /
+// dsb_single_search / dsb_mem_search (dsb_core.cuh), which they restate.
+static __device__ __forceinline__ int dsb_sp_set_insert_ls(uint32_t mask, bool act, uint64_t node, DsbSpSet *s)
+{
+    int l = 0;
+    if (act) {
+        if (s->l == s->m) s->l = 0;
+        l = s->l;
+    }
+    const uint64_t *set = s->set;
+    bool found = false;
+    for (int i = 0; __any_sync(mask, act && !found && i < l); i += 2) {
+        if (act && !found && i < l) {
+            const uint64_t a = set[i];
+            const uint64_t b = set[(i + 1 < l) ? i + 1 : i];
+            found = (a == node) || (b == node);
+        }
+    }
+    if (act && !found) {
+        s->set[l] = node;
+        s->l = l + 1;
+    }
+    return (act && !found) ? 1 : 0;
+}
+
+static __device__ __noinline__ void dsb_single_search_ls(DsbWork *w, uint32_t mask, bool act, uint64_t sp, const uint8_t *str,
+                                                         int max_match_len, DsbSpSet *sp_set, DsbMem *m)
+{
+    const uint64_t *rank = w->ix->rank;
+    uint64_t sa_sp = 0xffffffffffffffffull;
+    int match_len = 0, sa_sp_l = 0;
+    bool run = act, dup = false;
+    while (__any_sync(mask, run)) {
+        bool step = false;
+        uint64_t new_sp = 0;
+        if (run) {
+            if (match_len >= max_match_len) run = false;
+            else {
+                if ((sp & DSB_SA_MASK) == 0) { sa_sp = sp; sa_sp_l = 0; }
+                else sa_sp_l--;
+                uint8_t c = 0xff;
+                new_sp = dsb_occ(w, sp, &c);
+                new_sp += rank[c];
+                if (c != *str) run = false;
+                else { match_len++; str--; step = true; }
+            }
+        }
+        const int ins = dsb_sp_set_insert_ls(mask, step, new_sp, sp_set);
+        if (step) {
+            if (!ins) { dup = true; run = false; }
+            else sp = new_sp;
+        }
+    }
+    if (act) {
+        if (dup) m->match_len = -1000;
+        else { m->sp = sp; m->match_len = match_len; m->sa_sp = sa_sp; m->sa_sp_l = sa_sp_l; }
+    }
+}
+
+static __device__ __noinline__ int dsb_mem_search_ls(DsbWork *w, uint32_t mask, bool act, const uint8_t *str, uint64_t pre_v,
+                                                     int max_rst, int l_min_mth, int l_max_mth, DsbSpSet *sp_set, DsbMem *mem)
+{
+    const uint64_t *rank = w->ix->rank;
+    int n_rst = 0;
+    uint64_t sp = 0, ep = 0, new_sp = 0, new_ep = 0;
+    int match_len = DSB_L_PRE_IDX;
+    bool run = act, ret0 = false;
+    if (act) {
+        w->st.mem_search++;
+        w->st.lut++;
+        sp = w->ix->lut[pre_v];
+        ep = w->ix->lut[pre_v + 1];
+        str -= DSB_L_PRE_IDX;
+    }
+    while (__any_sync(mask, run)) {
+        if (run) {
+            uint8_t c = *str;
+            str--;
+            new_sp = rank[c] + dsb_occ(w, sp, &c);
+            new_ep = rank[c] + dsb_occ(w, ep, &c);
+            bool brk = false;
+            if (match_len >= l_min_mth - 1) {
+                if (new_sp + (uint64_t)(int64_t)max_rst >= new_ep) brk = true;
+                else if (match_len >= l_max_mth) { ret0 = true; brk = true; }
+            }
+            if (!brk && new_sp + 1 >= new_ep) brk = true;
+            if (brk) run = false;
+            else { match_len++; sp = new_sp; ep = new_ep; }
+        }
+    }
+    // the rows left (at most max_rst): insert, walk on alone, keep what is long enough.  One row (new_sp + 1 ==
+    // new_ep) and several rows read the same in the reference (:1419-1440)
+    const bool go = act && !ret0 && new_sp < new_ep;
+    const uint64_t n_rows = go ? (new_ep - new_sp) : 0;
+    for (uint64_t k = 0; __any_sync(mask, k < n_rows); k++) {
+        const bool a = k < n_rows;
+        const uint64_t c_sp = new_sp + k;
+        const int ins = dsb_sp_set_insert_ls(mask, a, c_sp, sp_set);
+        const bool walk = a && ins;
+        dsb_single_search_ls(w, mask, walk, c_sp, str, DSB_MAX(0, l_max_mth - match_len), sp_set, mem + n_rst);
+        if (walk) {
+            mem[n_rst].match_len += match_len + 1;
+            if (mem[n_rst].match_len >= l_min_mth) n_rst++;
+        }
+    }
+    return n_rst;
+}
+
 // Split pipeline, middle kernel: the body of one persistent warp of k_seed.  Same lock-step rounds as the device
 // branch of dsb_fast_seeding, but the 32 lanes pull islands from the BATCH's job list, so a warp stays full whatever
 // the number of top islands of a single read is (5 kb reads have a handful, which left 3-4 lanes of 32 busy).
@@ -217,14 +328,17 @@ static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_des
         bool finish = false;
         int n_mem = 0, string_index = 0;
         const uint8_t *bin_read = w->bin + (j_strand ? w->L : 0);
+        bool search = false;
+        uint64_t pre_v = 0;
         if (have) {
             if (j < min_index) finish = true;
             else {
                 string_index = (int)sd.offset + j + l_ek - 1;
-                const uint64_t pre_v = dsb_prefix13(bin_read + string_index);
-                n_mem = dsb_mem_search(w, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
+                pre_v = dsb_prefix13(bin_read + string_index);
+                search = true;
             }
         }
+        n_mem = dsb_mem_search_ls(w, 0xffffffffu, search, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
         __syncwarp();
         int max_score = 0;
         for (int mi = 0; mi < 2; mi++) {

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Per-device-function breakdown of an ncu capture of k_classify.
 
-usage: tools/ncu_by_function.py <report.ncu-rep> [libdsb_cuda.so] [--lines N]
+usage: tools/ncu_by_function.py <report.ncu-rep> [libdsb_cuda.so] [--kernel k_classify] [--lines N]
 
 ncu's SASS source page lists every instruction of the kernel (the out-of-line device functions are part of
 the kernel's section) with stall samples and executed-instruction counts but without function names;
@@ -37,9 +37,12 @@ def function_ranges(so_path, kernel="k_classify"):
         m = re.match(r"^\$\S+\$(_Z\w+):", line)
         if m:
             sym = m.group(1)
-            mm = re.match(r"_Z(\d+)", sym)
+            mm = re.match(r"_ZL?(\d+)", sym)
+            if not mm:
+                names.append((idx, sym))
+                continue
             n = int(mm.group(1))
-            names.append((idx, sym[2 + len(mm.group(1)):2 + len(mm.group(1)) + n]))
+            names.append((idx, sym[mm.end():mm.end() + n]))
             continue
         if re.match(r"^\s+/\*[0-9a-f]{4,}\*/", line):
             idx += 1
@@ -50,11 +53,14 @@ def main():
     rep = sys.argv[1]
     so = "desamba-so_b200/lib/libdsb_cuda.so"
     n_lines = 0
+    kernel = "k_classify"
     args = sys.argv[2:]
     while args:
         a = args.pop(0)
         if a == "--lines":
             n_lines = int(args.pop(0))
+        elif a == "--kernel":
+            kernel = args.pop(0)
         else:
             so = a
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], stdout=subprocess.PIPE, check=True).stdout.decode()
@@ -62,7 +68,7 @@ def main():
     hdr = rows[1]
     col = {n: i for i, n in enumerate(hdr)}
     body = rows[2:]
-    ranges, n_inst = function_ranges(so)
+    ranges, n_inst = function_ranges(so, kernel)
     if n_inst != len(body):
         print("warning: nvdisasm has %d instructions, the report %d (different build?)" % (n_inst, len(body)), file=sys.stderr)
     starts = [r[0] for r in ranges]
