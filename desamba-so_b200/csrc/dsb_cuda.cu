@@ -171,6 +171,14 @@ __global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexV
 // at every iteration instead of finishing their loops one after the other (in the per-lane forms the single-row walk
 // ran with ONE active thread per instruction: ncu, profiles/).  Results per lane are those of dsb_sp_set_insert /
 // dsb_single_search / dsb_mem_search (dsb_core.cuh), which they restate.
+// start fetching the FM block of row r (one 64-byte line) into L1 without waiting for it
+static __device__ __forceinline__ void dsb_fm_prefetch(const DsbIndexView *ix, uint64_t r)
+{
+#if !defined(DSB_NO_FM_PREFETCH)
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(ix->fm + (r >> 6)));
+#endif
+}
+
 static __device__ __forceinline__ int dsb_sp_set_insert_ls(uint32_t mask, bool act, uint64_t node, DsbSpSet *s)
 {
     int l = 0;
@@ -213,7 +221,10 @@ static __device__ __noinline__ void dsb_single_search_ls(DsbWork *w, uint32_t ma
                 new_sp = dsb_occ(w, sp, &c);
                 new_sp += rank[c];
                 if (c != *str) run = false;
-                else { match_len++; str--; step = true; }
+                else {
+                    match_len++; str--; step = true;
+                    dsb_fm_prefetch(w->ix, new_sp);      // the next step's block travels while the SP_SET is scanned
+                }
             }
         }
         const int ins = dsb_sp_set_insert_ls(mask, step, new_sp, sp_set);
@@ -247,6 +258,7 @@ static __device__ __noinline__ int dsb_mem_search_ls(DsbWork *w, uint32_t mask, 
         if (run) {
             uint8_t c = *str;
             str--;
+            dsb_fm_prefetch(w->ix, ep);                  // both ends of the interval in flight together
             new_sp = rank[c] + dsb_occ(w, sp, &c);
             new_ep = rank[c] + dsb_occ(w, ep, &c);
             bool brk = false;
@@ -275,6 +287,258 @@ static __device__ __noinline__ int dsb_mem_search_ls(DsbWork *w, uint32_t mask, 
         }
     }
     return n_rst;
+}
+
+// dsb_get_new_ed (dsb_core.cuh) in lock-step form: is_fwd is the same for every lane of a call site
+static __device__ __forceinline__ void dsb_get_new_ed_ls(DsbWork *w, uint32_t mask, bool act, uint32_t *e_d, uint32_t *len_,
+                                                         uint32_t *l_mem_ext, int32_t q_off, uint64_t t_off, uint32_t l_read,
+                                                         const uint8_t *q_b, bool is_fwd)
+{
+    uint8_t q_buff[13], t_buff[13];
+    const uint8_t *q = q_buff;
+    uint8_t *t = t_buff;
+    uint32_t len = 0, max_len = 0;
+    if (act) {
+        if (is_fwd) {
+            if (q_off < 0) q_off = 0;
+            max_len = (uint32_t)q_off;
+            len = DSB_MIN(12u, max_len);
+            for (uint8_t k = 0; k < len; k++) q_buff[k] = q_b[q_off - k];
+        } else {
+            max_len = l_read - (uint32_t)q_off;
+            len = DSB_MIN(12u, max_len);
+            q = q_b + q_off;
+        }
+        dsb_get_ref(w, t, t_off, len, !is_fwd);
+    }
+    bool run = act && len > 0 && t[0] == q[0];
+    while (__any_sync(mask, run)) {
+        if (run) {
+            uint32_t mtc;
+            for (mtc = 0; mtc < len; mtc++)
+                if (t[mtc] != q[mtc]) break;
+            if (mtc > 0) {
+                *l_mem_ext += mtc;
+                max_len -= mtc;
+                len = DSB_MIN(12u, max_len);
+                if (is_fwd) {
+                    q_off -= (int32_t)mtc;
+                    t_off -= mtc;
+                    for (uint8_t k = 0; k < len; k++) q_buff[k] = q_b[q_off - k];
+                } else {
+                    t_off += mtc;
+                    q += mtc;
+                }
+                dsb_get_ref(w, t, t_off, len, !is_fwd);
+            } else
+                run = false;
+        }
+    }
+    const int32_t d = dsb_lv_extd(t, q, act ? (int32_t)len : 0, (act && !is_fwd) ? q[-1] : (uint8_t)DSB_LV_NO_BYTE);
+    if (act) { *e_d = (uint32_t)d; *len_ = len; }
+}
+
+// dsb_map_seed (dsb_core.cuh; reference map_seed src/cly.c:701-934) in lock-step form: the `break`s of its
+// do { } while (0) become an `alive` flag, its loops run while any lane of `mask` still iterates, and the Landau-
+// Vishkin calls are made by all lanes together (length 0 for the lanes with nothing to extend).
+static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask, bool act, DsbMem *m_r, const uint8_t *q_b,
+                                                       uint32_t read_L, uint8_t direction)
+{
+    const DsbIndexView *ix = w->ix;
+    const int32_t *Q_MEM = ix->q_mem;
+    const int32_t *Q_LV = ix->q_lv;
+    uint64_t b_p = 0, sa_sp = 0;
+    int32_t q_off = 0, sa_sp_l = 0;
+    uint32_t l_m = 0;
+    if (act) {
+        b_p = m_r->sp; q_off = m_r->read_offset; l_m = (uint32_t)m_r->match_len;
+        sa_sp = m_r->sa_sp; sa_sp_l = m_r->sa_sp_l;
+        w->st.map_seed++;
+    }
+    bool have_uni = false;
+    uint64_t uni = 0;
+    uint32_t uni_len = 0, u_off = 0;
+    uint64_t t_off = 0;
+    uint32_t l_pre = 0, l_suf = 0, d_pre = 0, d_suf = 0;
+    int32_t s = 0, max_s = 0;
+    uint8_t q_pre[DSB_LV_L + 1], t_pre[DSB_LV_L + 1], t_suf[DSB_LV_L + 1];
+    const uint8_t *q_suf = q_pre;
+    for (int k = 0; k <= DSB_LV_L; k++) { q_pre[k] = 0xF1; t_pre[k] = 0xF2; t_suf[k] = 0xF3; }
+    bool alive = act;
+    int s_l = 0;
+    if (act) {
+        l_pre = (uint32_t)DSB_MIN(q_off + 1, DSB_LV_L);
+        for (uint8_t k = 0; k < l_pre; k++) q_pre[k] = q_b[q_off - k];
+    }
+    // (1) to the left until a sampled SA row (or l_pre bases), collecting the BWT symbols
+    const bool walk = act && sa_sp == 0xffffffffffffffffull;
+    {
+        bool run = walk;
+        while (__any_sync(mask, run)) {
+            if (run) {
+                if ((b_p & DSB_SA_MASK) == 0) run = false;
+                else {
+                    uint8_t c = 0xff;
+                    uint64_t new_sp = dsb_occ(w, b_p, &c);
+                    new_sp += ix->rank[c];
+                    if (c == 4) run = false;
+                    else {
+                        t_pre[s_l++] = c;
+                        b_p = new_sp;
+                        if (s_l >= (int)l_pre) run = false;
+                    }
+                }
+            }
+        }
+    }
+    if (act && (!walk || (b_p & DSB_SA_MASK) == 0)) {
+        uni = dsb_get_uni(w, walk ? b_p : sa_sp, walk ? s_l : sa_sp_l, &t_off, &u_off);
+        have_uni = true;
+    } else if (walk)
+        l_pre = (uint32_t)s_l;
+    if (alive && have_uni) {
+        uni_len = (uint32_t)(ix->unitig[uni] >> 32);
+        if (uni_len < DSB_MIN_UNI_L) alive = false;
+        else {
+            l_pre = DSB_MIN(l_pre, u_off);
+            dsb_get_ref(w, t_pre, t_off - 1, l_pre, false);
+        }
+    }
+    {
+        const int32_t d = dsb_lv_extd(t_pre, q_pre, alive ? (int32_t)l_pre : 0, DSB_LV_NO_BYTE);
+        if (alive) {
+            d_pre = (uint32_t)d;
+            s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+            if (s < DSB_MIN_S_1 && l_pre == DSB_LV_L && !have_uni) { s = 0; alive = false; }
+        }
+    }
+    // (2) the rest of the way to a sampled row
+    const bool walk2 = alive && !have_uni;
+    {
+        bool run = walk2;
+        while (__any_sync(mask, run)) {
+            if (run) {
+                if ((b_p & DSB_SA_MASK) == 0) run = false;
+                else {
+                    uint8_t c = 0xff;
+                    b_p = dsb_occ(w, b_p, &c);
+                    b_p += ix->rank[c];
+                    s_l++;
+                }
+            }
+        }
+    }
+    if (walk2) {
+        uni = dsb_get_uni(w, b_p, s_l, &t_off, &u_off);
+        have_uni = true;
+        uni_len = (uint32_t)(ix->unitig[uni] >> 32);
+        if (uni_len < DSB_MIN_UNI_L) { s = 0; alive = false; }
+    }
+    // (3) right side
+    uint32_t l_max_suf = 0;
+    bool suf = false;
+    if (alive) {
+        const int32_t q_off_r = q_off + (int32_t)l_m + 1;
+        l_max_suf = DSB_MIN(uni_len - u_off - l_m, read_L - (uint32_t)q_off_r);
+        suf = (l_max_suf != 0);
+        if (suf) {
+            l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
+            q_suf = q_b + q_off_r;
+            dsb_get_ref(w, t_suf, t_off + l_m, l_suf, true);
+        } else
+            l_suf = d_suf = 0;
+    }
+    {
+        bool run = suf && t_suf[0] == q_suf[0];
+        while (__any_sync(mask, run)) {
+            if (run) {
+                uint32_t mtc;
+                for (mtc = 0; mtc < l_suf; mtc++)
+                    if (t_suf[mtc] != q_suf[mtc]) break;
+                if (mtc > 0) {
+                    l_m += mtc;
+                    s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+                    l_max_suf -= mtc;
+                    l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
+                    q_suf += mtc;
+                    dsb_get_ref(w, t_suf, t_off + l_m, l_suf, true);
+                } else
+                    run = false;
+            }
+        }
+    }
+    {
+        const int32_t d = dsb_lv_extd(t_suf, q_suf, suf ? (int32_t)l_suf : 0, suf ? q_suf[-1] : (uint8_t)DSB_LV_NO_BYTE);
+        if (suf) {
+            d_suf = (uint32_t)d;
+            s += Q_LV[d_suf * 20 + l_suf];
+        }
+    }
+    if (alive && s <= DSB_MIN_S_2 && l_suf == DSB_LV_L) { s = 0; alive = false; }
+    if (!alive) s = 0;
+
+    // (4) one anchor per occurrence of the unitig
+    uint16_t am_mtch = (uint16_t)l_m;
+    int16_t am_score = (int16_t)s;
+    uint8_t am_left_len = (uint8_t)l_pre, am_left_ED = (uint8_t)d_pre;
+    uint8_t am_rigt_len = (uint8_t)l_suf, am_rigt_ED = (uint8_t)d_suf;
+    uint32_t rp_s = 0, n_rp = 0;
+    bool ret50 = false;
+    if (act && s > 0) {
+        rp_s = (uint32_t)ix->unitig[uni];
+        const uint32_t rp_e = (uint32_t)ix->unitig[uni + 1];
+        w->st.unitig++;
+        if ((int64_t)rp_e - (int64_t)rp_s > 50 && !((int64_t)rp_e - (int64_t)rp_s < 1000)) ret50 = true;
+        else n_rp = (rp_e > rp_s) ? rp_e - rp_s : 0;
+    }
+    const bool ref_search_l = (l_pre < DSB_LV_L || d_pre == 0);
+    const bool ref_search_r = (l_suf < DSB_LV_L || d_suf == 0);
+    for (uint32_t k = 0; __any_sync(mask, k < n_rp); k++) {
+        const bool a = k < n_rp;
+        uint64_t r_global = 0;
+        uint32_t r_ref_ID = 0;
+        if (a) {
+            const uint64_t rpv = ix->ref_pos[rp_s + k];
+            w->st.refpos++;
+            r_global = rpv & 0xFFFFFFFFFFull;
+            r_ref_ID = (uint32_t)((rpv >> 40) & 0x7FFFFF);
+        }
+        uint32_t ed_l = 0, ed_r = 0, len_l = 0, len_r = 0;
+        uint32_t l_m_ext_l = 0, l_m_ext_r = 0;
+        const bool do_l = a && ref_search_l, do_r = a && ref_search_r;
+        dsb_get_new_ed_ls(w, mask, do_l, &ed_l, &len_l, &l_m_ext_l, q_off, r_global + u_off - 1, read_L, q_b, true);
+        if (do_l) { am_left_len = (uint8_t)len_l; am_left_ED = (uint8_t)ed_l; }
+        if (do_l || do_r) am_mtch = (uint16_t)(l_m + l_m_ext_l);
+        dsb_get_new_ed_ls(w, mask, do_r, &ed_r, &len_r, &l_m_ext_r, q_off + (int32_t)l_m + 1, r_global + u_off + l_m, read_L,
+                          q_b, false);
+        if (do_r) {
+            am_rigt_len = (uint8_t)len_r;
+            am_rigt_ED = (uint8_t)ed_r;
+            am_mtch = (uint16_t)(am_mtch + l_m_ext_r);
+        }
+        bool keep = a;
+        if (do_l || do_r) {
+            am_score = (int16_t)(Q_MEM[am_mtch] + Q_LV[am_left_ED * 20 + am_left_len] + Q_LV[am_rigt_ED * 20 + am_rigt_len]);
+            if (am_score < DSB_MIN_S_2) keep = false;
+        }
+        if (keep) {
+            max_s = DSB_MAX(max_s, (int32_t)am_score);
+            DsbAnchor an;
+            an.direction = direction;
+            an.index_in_read = (uint32_t)(q_off + 1) - l_m_ext_l;
+            const uint64_t g = r_global + u_off - l_m_ext_l;
+            an.ref_ID = r_ref_ID;
+            an.ref_offset = (uint32_t)(g - ix->ref_off[r_ref_ID]);
+            an.mtch_len = am_mtch;
+            an.score = am_score;
+            an.pre = -1;
+            an.useless = 0;
+            an.duplicate = 0;
+            an.pad = 0;
+            dsb_push_anchor(w, &an);
+        }
+    }
+    return ret50 ? 50 : max_s;
 }
 
 // Split pipeline, middle kernel: the body of one persistent warp of k_seed.  Same lock-step rounds as the device
@@ -342,11 +606,10 @@ static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_des
         __syncwarp();
         int max_score = 0;
         for (int mi = 0; mi < 2; mi++) {
-            if (have && mi < n_mem) {
-                m_r[mi].read_offset = string_index - m_r[mi].match_len;
-                const int c_score = dsb_map_seed(w, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD);
-                max_score = DSB_MAX(c_score, max_score);
-            }
+            const bool ms = have && mi < n_mem;
+            if (ms) m_r[mi].read_offset = string_index - m_r[mi].match_len;
+            const int c_score = dsb_map_seed_ls(w, 0xffffffffu, ms, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD);
+            if (ms) max_score = DSB_MAX(c_score, max_score);
             __syncwarp();
         }
         if (have && !finish) {
