@@ -289,6 +289,83 @@ static __device__ __noinline__ int dsb_mem_search_ls(DsbWork *w, uint32_t mask, 
     return n_rst;
 }
 
+// dsb_lv_extd (dsb_core.cuh; reference lv_extd src/cly.c:505-604) in lock-step form.  On its own a lane leaves the
+// 5 x 10 cell loops at a data-dependent `return`, so 32 lanes ran them one after the other (2.8 active threads per
+// instruction, 39 % of k_seed's instructions).  Here all lanes of `mask` walk the cells together, a finished lane just
+// stops updating; the exact-run loop of a cell is one XOR + find-first-set on the strings packed 4 bits per symbol
+// (bases 0..3; the callers' fillers 0xF1..0xF3 -> 5..7; '#' -> 8; '$' -> 9; DSB_LV_NO_BYTE -> 11; bytes before ref[0]
+// never match and are handled on use: a one-to-one map, which is all equality needs).
+static __device__ __forceinline__ uint32_t dsb_lv_sym(uint8_t b) { return (uint32_t)(b & 3u) | ((uint32_t)(b >> 5) & 4u); }
+#define DSB_LV_QOFF 3     // query index k sits in nibble k + 3 (k = -3 .. 12)
+static __device__ __noinline__ int32_t dsb_lv_extd_ls(uint32_t mask, const uint8_t *ref_in, const uint8_t *query_in, int32_t len,
+                                                      uint8_t query_m1)
+{
+    bool done = (len <= 0);                   // returns 0 whatever the bytes are
+    int32_t result = 0;
+    const int32_t ref_length = len, query_length = len;
+    uint64_t R = 0, Q = 0xbbull | ((uint64_t)((query_m1 == DSB_LV_NO_BYTE) ? 11u : dsb_lv_sym(query_m1)) << 8);
+    for (int i = 0; i < len; i++) {
+        R |= (uint64_t)dsb_lv_sym(ref_in[i]) << (4 * i);
+        Q |= (uint64_t)dsb_lv_sym(query_in[i]) << (4 * (i + DSB_LV_QOFF));
+    }
+    if (!done) {
+        R |= 8ull << (4 * len);
+        Q |= 9ull << (4 * (len + DSB_LV_QOFF));
+    }
+    int32_t mn_d[14], ed_d[14];
+    int32_t *mn = mn_d + DSB_LV_ERROR + 1, *ed = ed_d + DSB_LV_ERROR + 1;
+    for (int i = -DSB_LV_ERROR - 1; i <= DSB_LV_ERROR + 1; i++) {
+        mn[i] = -1;
+        ed[i] = (i > 0) ? i : -i;
+    }
+    mn[DSB_LV_ERROR + 2] = -1; ed[DSB_LV_ERROR + 2] = DSB_LV_ERROR + 2;
+    int32_t best_score = query_length;
+#pragma unroll 1
+    for (int i = 0; i <= DSB_LV_ERROR; i++) {
+        int32_t prev_mn = -1, cur_mn = i - 1, next_mn = mn[-i + 1];
+        int32_t prev_ed = i + 1, cur_ed = i, next_ed = ed[-i + 1];
+#pragma unroll 1
+        for (int j = -i; j <= DSB_LV_ERROR; j++) {
+            if (!__any_sync(mask, !done)) return result;
+            if (!done) {
+                int mn_v, ed_v;
+                if (cur_mn + j < ref_length - 1) {
+                    int m = cur_mn + 1 - cur_ed;
+                    mn_v = cur_mn + 1;
+                    ed_v = cur_ed + 1;
+                    if (m < next_mn + 1 - next_ed) { mn_v = next_mn + 1; ed_v = next_ed + 1; m = next_mn - next_ed; }
+                    if (m < prev_mn - prev_ed) { mn_v = prev_mn + 1; ed_v = prev_ed + 1; }
+                } else {
+                    int m = cur_mn - cur_ed;
+                    mn_v = cur_mn;
+                    ed_v = cur_ed + 1;
+                    if (m < prev_mn - prev_ed) { mn_v = prev_mn; ed_v = prev_ed + 1; m = prev_mn - prev_ed; }
+                    if (m < next_mn + 1 - next_ed) { mn_v = next_mn + 1; ed_v = next_ed + 1; }
+                }
+                int mn_j = DSB_MIN(mn_v, query_length);
+                mn_j = DSB_MIN(mn_j, ref_length - j);
+                // the exact run from (ref[mn_j + j], query[mn_j]): a sentinel ends it at the latest
+                if (mn_j + j >= 0) {
+                    const uint64_t x = (R >> (4 * (mn_j + j))) ^ (Q >> (4 * (mn_j + DSB_LV_QOFF)));
+                    const uint64_t nz = (x | (x >> 1) | (x >> 2) | (x >> 3)) & 0x1111111111111111ull;
+                    mn_j += (__ffsll((long long)nz) - 1) >> 2;
+                }
+                mn[j] = mn_j;
+                ed[j] = ed_v;
+                const uint32_t q_sym = (uint32_t)(Q >> (4 * (mn_j + DSB_LV_QOFF))) & 0xfu;
+                const uint32_t r_sym = (mn_j + j >= 0) ? ((uint32_t)(R >> (4 * (mn_j + j))) & 0xfu) : 10u;
+                if (q_sym == 9u || r_sym == 8u) {
+                    best_score = DSB_MIN(ed_v - 1, best_score);
+                    if (j <= i + 1) { result = best_score; done = true; }
+                }
+                prev_mn = cur_mn; cur_mn = next_mn; next_mn = mn[j + 2];
+                prev_ed = cur_ed; cur_ed = next_ed; next_ed = ed[j + 2];
+            }
+        }
+    }
+    return done ? result : best_score;
+}
+
 // dsb_get_new_ed (dsb_core.cuh) in lock-step form: is_fwd is the same for every lane of a call site
 static __device__ __forceinline__ void dsb_get_new_ed_ls(DsbWork *w, uint32_t mask, bool act, uint32_t *e_d, uint32_t *len_,
                                                          uint32_t *l_mem_ext, int32_t q_off, uint64_t t_off, uint32_t l_read,
@@ -334,7 +411,7 @@ static __device__ __forceinline__ void dsb_get_new_ed_ls(DsbWork *w, uint32_t ma
                 run = false;
         }
     }
-    const int32_t d = dsb_lv_extd(t, q, act ? (int32_t)len : 0, (act && !is_fwd) ? q[-1] : (uint8_t)DSB_LV_NO_BYTE);
+    const int32_t d = dsb_lv_extd_ls(mask, t, q, act ? (int32_t)len : 0, (act && !is_fwd) ? q[-1] : (uint8_t)DSB_LV_NO_BYTE);
     if (act) { *e_d = (uint32_t)d; *len_ = len; }
 }
 
@@ -405,7 +482,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
         }
     }
     {
-        const int32_t d = dsb_lv_extd(t_pre, q_pre, alive ? (int32_t)l_pre : 0, DSB_LV_NO_BYTE);
+        const int32_t d = dsb_lv_extd_ls(mask, t_pre, q_pre, alive ? (int32_t)l_pre : 0, DSB_LV_NO_BYTE);
         if (alive) {
             d_pre = (uint32_t)d;
             s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
@@ -468,7 +545,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
         }
     }
     {
-        const int32_t d = dsb_lv_extd(t_suf, q_suf, suf ? (int32_t)l_suf : 0, suf ? q_suf[-1] : (uint8_t)DSB_LV_NO_BYTE);
+        const int32_t d = dsb_lv_extd_ls(mask, t_suf, q_suf, suf ? (int32_t)l_suf : 0, suf ? q_suf[-1] : (uint8_t)DSB_LV_NO_BYTE);
         if (suf) {
             d_suf = (uint32_t)d;
             s += Q_LV[d_suf * 20 + l_suf];
