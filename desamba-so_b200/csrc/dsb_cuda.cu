@@ -419,8 +419,11 @@ static __device__ __forceinline__ void dsb_get_new_ed_ls(DsbWork *w, uint32_t ma
 // do { } while (0) become an `alive` flag, its loops run while any lane of `mask` still iterates, and the Landau-
 // Vishkin calls are made by all lanes together (length 0 for the lanes with nothing to extend).
 static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask, bool act, DsbMem *m_r, const uint8_t *q_b,
-                                                       uint32_t read_L, uint8_t direction)
+                                                       uint32_t read_L, uint8_t direction, int *smax /* 32 ints of shared memory */)
 {
+#if defined(DSB_SEED_DIAG)
+    const long long td_in = clock64();
+#endif
     const DsbIndexView *ix = w->ix;
     const int32_t *Q_MEM = ix->q_mem;
     const int32_t *Q_LV = ix->q_lv;
@@ -554,11 +557,13 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
     if (alive && s <= DSB_MIN_S_2 && l_suf == DSB_LV_L) { s = 0; alive = false; }
     if (!alive) s = 0;
 
-    // (4) one anchor per occurrence of the unitig
-    uint16_t am_mtch = (uint16_t)l_m;
-    int16_t am_score = (int16_t)s;
-    uint8_t am_left_len = (uint8_t)l_pre, am_left_ED = (uint8_t)d_pre;
-    uint8_t am_rigt_len = (uint8_t)l_suf, am_rigt_ED = (uint8_t)d_suf;
+#if defined(DSB_SEED_DIAG)
+    const long long td1 = clock64();
+#endif
+    // (4) one anchor per occurrence of the unitig.  The occurrence counts differ wildly between lanes (1 .. 999), so
+    // the (seed, occurrence) pairs of the whole warp are dealt out evenly: pair g goes to lane g % 32, which fetches the
+    // owning lane's seed by shuffle, extends both sides and writes the anchor into the OWNER's staging area at the
+    // position the owner's serial loop would have used (pairs of one owner sit in consecutive lanes in occurrence order).
     uint32_t rp_s = 0, n_rp = 0;
     bool ret50 = false;
     if (act && s > 0) {
@@ -568,26 +573,64 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
         if ((int64_t)rp_e - (int64_t)rp_s > 50 && !((int64_t)rp_e - (int64_t)rp_s < 1000)) ret50 = true;
         else n_rp = (rp_e > rp_s) ? rp_e - rp_s : 0;
     }
-    const bool ref_search_l = (l_pre < DSB_LV_L || d_pre == 0);
-    const bool ref_search_r = (l_suf < DSB_LV_L || d_suf == 0);
-    for (uint32_t k = 0; __any_sync(mask, k < n_rp); k++) {
-        const bool a = k < n_rp;
+    const uint32_t lane = threadIdx.x & 31;
+    uint32_t incl = n_rp;
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane >= o) incl += v;
+    }
+    const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) return ret50 ? 50 : 0;
+    smax[lane] = 0;
+    __syncwarp();
+    // the owner's side of a pair, packed for the shuffles
+    const uint32_t my_flags = ((l_pre < DSB_LV_L || d_pre == 0) ? 1u : 0u) | ((l_suf < DSB_LV_L || d_suf == 0) ? 2u : 0u) |
+                              ((uint32_t)direction << 8);
+    const uint32_t my_lens = (l_pre & 0xffu) | ((d_pre & 0xffu) << 8) | ((l_suf & 0xffu) << 16) | ((d_suf & 0xffu) << 24);
+    for (uint32_t g0 = 0; g0 < total; g0 += 32) {
+        const uint32_t g = g0 + lane;
+        const bool a = g < total;
+        uint32_t owner = 0;                                   // number of lanes whose inclusive count is <= g
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t v = __shfl_sync(0xffffffffu, incl, (int)(owner + step - 1));
+            if (v <= g) owner += step;
+        }
+        owner &= 31u;
+        const uint32_t o_incl = __shfl_sync(0xffffffffu, incl, (int)owner);
+        const uint32_t o_n = __shfl_sync(0xffffffffu, n_rp, (int)owner);
+        const uint32_t o_rp_s = __shfl_sync(0xffffffffu, rp_s, (int)owner);
+        const int32_t o_q_off = __shfl_sync(0xffffffffu, q_off, (int)owner);
+        const uint32_t o_l_m = __shfl_sync(0xffffffffu, l_m, (int)owner);
+        const uint32_t o_u_off = __shfl_sync(0xffffffffu, u_off, (int)owner);
+        const uint32_t o_flags = __shfl_sync(0xffffffffu, my_flags, (int)owner);
+        const uint32_t o_lens = __shfl_sync(0xffffffffu, my_lens, (int)owner);
+        const int32_t o_s = __shfl_sync(0xffffffffu, s, (int)owner);
+        const uint32_t o_read_L = __shfl_sync(0xffffffffu, read_L, (int)owner);
+        const uint8_t *o_q_b = (const uint8_t *)__shfl_sync(0xffffffffu, (unsigned long long)q_b, (int)owner);
+        const uint32_t o_base = __shfl_sync(0xffffffffu, w->n_anchor, (int)owner);
+        const uint32_t o_excl = o_incl - o_n;
+        const uint32_t k = g - o_excl;
         uint64_t r_global = 0;
         uint32_t r_ref_ID = 0;
         if (a) {
-            const uint64_t rpv = ix->ref_pos[rp_s + k];
+            const uint64_t rpv = ix->ref_pos[o_rp_s + k];
             w->st.refpos++;
             r_global = rpv & 0xFFFFFFFFFFull;
             r_ref_ID = (uint32_t)((rpv >> 40) & 0x7FFFFF);
         }
+        uint16_t am_mtch = (uint16_t)o_l_m;
+        int16_t am_score = (int16_t)o_s;
+        uint8_t am_left_len = (uint8_t)(o_lens & 0xffu), am_left_ED = (uint8_t)((o_lens >> 8) & 0xffu);
+        uint8_t am_rigt_len = (uint8_t)((o_lens >> 16) & 0xffu), am_rigt_ED = (uint8_t)(o_lens >> 24);
         uint32_t ed_l = 0, ed_r = 0, len_l = 0, len_r = 0;
         uint32_t l_m_ext_l = 0, l_m_ext_r = 0;
-        const bool do_l = a && ref_search_l, do_r = a && ref_search_r;
-        dsb_get_new_ed_ls(w, mask, do_l, &ed_l, &len_l, &l_m_ext_l, q_off, r_global + u_off - 1, read_L, q_b, true);
+        const bool do_l = a && (o_flags & 1u), do_r = a && (o_flags & 2u);
+        dsb_get_new_ed_ls(w, mask, do_l, &ed_l, &len_l, &l_m_ext_l, o_q_off, r_global + o_u_off - 1, o_read_L, o_q_b, true);
         if (do_l) { am_left_len = (uint8_t)len_l; am_left_ED = (uint8_t)ed_l; }
-        if (do_l || do_r) am_mtch = (uint16_t)(l_m + l_m_ext_l);
-        dsb_get_new_ed_ls(w, mask, do_r, &ed_r, &len_r, &l_m_ext_r, q_off + (int32_t)l_m + 1, r_global + u_off + l_m, read_L,
-                          q_b, false);
+        if (do_l || do_r) am_mtch = (uint16_t)(o_l_m + l_m_ext_l);
+        dsb_get_new_ed_ls(w, mask, do_r, &ed_r, &len_r, &l_m_ext_r, o_q_off + (int32_t)o_l_m + 1, r_global + o_u_off + o_l_m,
+                          o_read_L, o_q_b, false);
         if (do_r) {
             am_rigt_len = (uint8_t)len_r;
             am_rigt_ED = (uint8_t)ed_r;
@@ -598,23 +641,48 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
             am_score = (int16_t)(Q_MEM[am_mtch] + Q_LV[am_left_ED * 20 + am_left_len] + Q_LV[am_rigt_ED * 20 + am_rigt_len]);
             if (am_score < DSB_MIN_S_2) keep = false;
         }
+        // where the anchor goes: after the owner's earlier anchors and the kept pairs of this owner in lower lanes
+        const uint32_t kept = __ballot_sync(0xffffffffu, keep);
+        const uint32_t o_lo = (o_excl > g0) ? (o_excl - g0) : 0u;                 // the owner's first lane of this wave
+        const uint32_t below = kept & ((1u << lane) - 1u) & ~((1u << o_lo) - 1u);
         if (keep) {
-            max_s = DSB_MAX(max_s, (int32_t)am_score);
-            DsbAnchor an;
-            an.direction = direction;
-            an.index_in_read = (uint32_t)(q_off + 1) - l_m_ext_l;
-            const uint64_t g = r_global + u_off - l_m_ext_l;
-            an.ref_ID = r_ref_ID;
-            an.ref_offset = (uint32_t)(g - ix->ref_off[r_ref_ID]);
-            an.mtch_len = am_mtch;
-            an.score = am_score;
-            an.pre = -1;
-            an.useless = 0;
-            an.duplicate = 0;
-            an.pad = 0;
-            dsb_push_anchor(w, &an);
+            atomicMax(&smax[owner], (int)am_score);
+            const uint32_t pos = o_base + (uint32_t)__popc(below);
+            if (pos >= w->cap_stage) w->overflow = 1;
+            else {
+                DsbAnchor an;
+                an.direction = (uint8_t)(o_flags >> 8);
+                an.index_in_read = (uint32_t)(o_q_off + 1) - l_m_ext_l;
+                const uint64_t gpos = r_global + o_u_off - l_m_ext_l;
+                an.ref_ID = r_ref_ID;
+                an.ref_offset = (uint32_t)(gpos - ix->ref_off[r_ref_ID]);
+                an.mtch_len = am_mtch;
+                an.score = am_score;
+                an.pre = -1;
+                an.useless = 0;
+                an.duplicate = 0;
+                an.pad = 0;
+                w->stage[(size_t)owner * w->cap_stage + pos] = an;
+            }
         }
+        // every owner takes note of what was appended to its area in this wave
+        {
+            const uint32_t my_excl = incl - n_rp;
+            const uint32_t lo = (my_excl > g0) ? (my_excl - g0) : 0u;
+            const uint32_t hi = (incl > g0) ? DSB_MIN(incl - g0, 32u) : 0u;
+            if (n_rp && hi > lo) {
+                const uint32_t range = ((hi >= 32u) ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                w->n_anchor = DSB_MIN(w->n_anchor + (uint32_t)__popc(kept & range), w->cap_stage);
+            }
+        }
+        __syncwarp();
     }
+    max_s = smax[lane];
+#if defined(DSB_SEED_DIAG)
+    __syncwarp(mask);
+    w->st.cyc[7] += (unsigned long long)(clock64() - td1);
+    w->st.cyc[6] += (unsigned long long)(td1 - td_in);
+#endif
     return ret50 ? 50 : max_s;
 }
 
@@ -624,7 +692,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
 // A finished island's anchors move from the lane's staging area to the batch's anchor pool.
 // w: bound to the warp's scratch slice; bin_base / desc: the batch.  Returns through jobs[], pool, *n_pool, w->st.
 static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_desc *desc, uint8_t *bin_base, DsbSeedJob *jobs, uint32_t n_jobs,
-                           uint32_t *next_job, DsbAnchor *pool, uint32_t cap_pool, uint32_t *n_pool)
+                           uint32_t *next_job, DsbAnchor *pool, uint32_t cap_pool, uint32_t *n_pool, int *smax)
 {
     const uint32_t lane = threadIdx.x & 31;
     uint8_t *priv = w->lane_priv + (size_t)lane * DSB_LANE_PRIV_BYTES;
@@ -679,13 +747,19 @@ static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_des
                 search = true;
             }
         }
+#if defined(DSB_SEED_DIAG)
+        const long long td0 = clock64();
+#endif
         n_mem = dsb_mem_search_ls(w, 0xffffffffu, search, bin_read + string_index, pre_v, 2, 21 - 1, string_index, &sp_set, m_r);
         __syncwarp();
+#if defined(DSB_SEED_DIAG)
+        w->st.cyc[5] += (unsigned long long)(clock64() - td0);
+#endif
         int max_score = 0;
         for (int mi = 0; mi < 2; mi++) {
             const bool ms = have && mi < n_mem;
             if (ms) m_r[mi].read_offset = string_index - m_r[mi].match_len;
-            const int c_score = dsb_map_seed_ls(w, 0xffffffffu, ms, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD);
+            const int c_score = dsb_map_seed_ls(w, 0xffffffffu, ms, m_r + mi, bin_read, w->L, j_strand ? DSB_REVERSE : DSB_FORWARD, smax);
             if (ms) max_score = DSB_MAX(c_score, max_score);
             __syncwarp();
         }
@@ -821,7 +895,8 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_seed(
     w.ix = &ix;
     dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
     const long long t0 = clock64();
-    dsb_seed_jobs(&w, desc, bin, jobs, n_jobs, &ctrl->next_job, pool, cap_pool, &ctrl->n_pool);
+    __shared__ int s_seed_max[DSB_CLASSIFY_THREADS / 32][32];
+    dsb_seed_jobs(&w, desc, bin, jobs, n_jobs, &ctrl->next_job, pool, cap_pool, &ctrl->n_pool, s_seed_max[threadIdx.x >> 5]);
     const unsigned long long cyc = (unsigned long long)(clock64() - t0);
     // every lane counted its own work
     if (__any_sync(0xffffffffu, w.overflow != 0)) {
@@ -838,6 +913,9 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_seed(
     DSB_FOLD_ADD(map_seeds, w.st.map_seed);
 #undef DSB_FOLD_ADD
     if (lane == 0) atomicAdd((unsigned long long *)&cn->phase_cycles[1], cyc);
+#if defined(DSB_SEED_DIAG)
+    if (lane == 0) for (int ph = 5; ph < 8; ph++) atomicAdd((unsigned long long *)&cn->phase_cycles[ph], w.st.cyc[ph]);
+#endif
 }
 
 // persistent: every warp pulls the next read of the (longest-first) order until none is left
