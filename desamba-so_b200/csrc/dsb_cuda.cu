@@ -98,6 +98,7 @@ struct dsb_slot {
     uint32_t cap_anchor, cap_sms;
     DsbScratchDims dims;
     int n_warps, blocks, threads;
+    int seed_blocks;                // grid of k_seed (its own occupancy)
     // state of the batch in flight
     uint32_t n_reads;
     uint64_t n_bases;
@@ -882,7 +883,10 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_island
 }
 
 // persistent warps, ONE LANE PER ISLAND of the whole batch
-__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_seed(
+#ifndef DSB_SEED_MIN_BLOCKS
+#define DSB_SEED_MIN_BLOCKS 8        // 64 registers, 32 warps per SM: 2.66 -> 2.49 ms (10 blocks / 48 registers: 2.59)
+#endif
+__global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_SEED_MIN_BLOCKS) k_seed(
     const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, uint8_t *__restrict__ bin,
     uint8_t *__restrict__ scratch, const __grid_constant__ DsbScratchDims dims, DsbSeedJob *__restrict__ jobs,
     DsbAnchor *__restrict__ pool, uint32_t cap_pool, DsbCtrl *ctrl)
@@ -1256,6 +1260,11 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
         s->threads = DSB_CLASSIFY_THREADS;
         s->blocks = per_sm * ix->sm_count;
         s->n_warps = s->blocks * (DSB_CLASSIFY_THREADS / 32);
+        int per_sm_seed = 0;
+        TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_seed, k_seed, DSB_CLASSIFY_THREADS, 0));
+        if (per_sm_seed < 1) per_sm_seed = 1;
+        s->seed_blocks = per_sm_seed * ix->sm_count;
+        if (s->seed_blocks * (DSB_CLASSIFY_THREADS / 32) > s->n_warps) s->n_warps = s->seed_blocks * (DSB_CLASSIFY_THREADS / 32);
     }
     s->cap_anchor = 2048;
     s->cap_sms = 8192;
@@ -1309,7 +1318,7 @@ static int launch_kernels(dsb_slot *s)
                                                           s->dims, s->d_rinfo, s->d_jobs, s->cap_jobs, n, s->d_ctrl);
         CU(cudaEventRecord(s->ev[6], s->stream));
         // the island jobs of the whole batch, one lane each: always the full persistent grid
-        k_seed<<<s->blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_scratch, s->dims, s->d_jobs,
+        k_seed<<<s->seed_blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_scratch, s->dims, s->d_jobs,
                                                          s->d_pool, s->cap_pool, s->d_ctrl);
         CU(cudaEventRecord(s->ev[7], s->stream));
         k_classify<<<blocks, s->threads, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_order, s->d_bin, s->d_exist, s->d_scratch,
