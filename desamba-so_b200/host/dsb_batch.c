@@ -29,6 +29,8 @@ struct dsb_engine {
     int n_gpu;
     dsb_index **dev;
     uint64_t batch_bases;
+    uint64_t batch_first;      /* size of the first batch of a run (DSB_BATCH_FIRST) */
+    int batch_taper;           /* shrink the last batches when the input size is known (DSB_BATCH_TAPER, default 0) */
     uint32_t batch_reads;
     int fmt_threads;
 };
@@ -102,6 +104,9 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
             dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
     e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)16 << 20);
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
+    e->batch_first = env_u64("DSB_BATCH_FIRST", e->batch_bases);      /* measured: ramping up from 1-4 Mbases costs 1-3 ms on a 50 Mbase call */
+    if (e->batch_first > e->batch_bases) e->batch_first = e->batch_bases;
+    e->batch_taper = (int)env_u64("DSB_BATCH_TAPER", 0);
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     if (ncpu < 1) ncpu = 1;
     /* one-process-per-GPU launchers (torchrun sets LOCAL_WORLD_SIZE) share the host cores between the ranks */
@@ -241,7 +246,7 @@ static void copy_seq_part(void *arg, int part, int n_parts)
 }
 
 /* parse up to one batch into slot k; returns number of reads (0 = input exhausted) */
-static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *eof)
+static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *eof, uint64_t limit_bases)
 {
     dsb_engine *e = s->e;
     batch_meta *m = &s->meta[k];
@@ -264,6 +269,11 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
         }
         const uint64_t L = v.seq_l;
         if (L > 0x7fffffff) dsb_fatal("read too long");
+        if (n > 0 && bases + L > limit_bases && L <= e->batch_bases) {   /* this batch is meant to be a small one */
+            s->carry = v;
+            s->have_carry = 1;
+            break;
+        }
         if (L > e->batch_bases - bases) {
             if (n == 0) dsb_fatal("a single read is longer than the batch capacity (%llu bases); raise DSB_BATCH_BASES",
                                   (unsigned long long)e->batch_bases);
@@ -466,8 +476,20 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         /* the history borrows sequence pointers from the staging of earlier batches: before any
          * staging is overwritten it must own what it still needs */
         dsb_history_end_batch(s->hist);
+        /* Optional batch-size schedule (both off by default: a batch of any size costs the device one read's latency,
+         * 4-5 ms, so small batches lose more than their earlier start wins; profiles/): DSB_BATCH_FIRST starts small
+         * and doubles; DSB_BATCH_TAPER=1 halves towards the end when the amount of input left is known. */
+        uint64_t limit = s->e->batch_first << (b < 16 ? b : 16);
+        if (limit > s->e->batch_bases || limit == 0) limit = s->e->batch_bases;
+        {
+            const uint64_t left = dsb_fq_remaining_bytes(f);
+            if (left != UINT64_MAX && s->e->batch_taper) {
+                const uint64_t half = left / 4;                 /* ~2 input bytes per base: half of what is left */
+                if (half < limit) limit = half > s->e->batch_first ? half : s->e->batch_first;
+            }
+        }
         double t0 = dsb_now();
-        uint32_t n = fill_slot(s, k, f, want_qual, &eof);
+        uint32_t n = fill_slot(s, k, f, want_qual, &eof, limit);
         stats->t_parse += dsb_now() - t0;
         if (n == 0) break;
         stats->n_reads += n;

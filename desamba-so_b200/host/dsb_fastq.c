@@ -386,3 +386,16 @@ void dsb_fq_prescan(dsb_fq *f, int n_threads)
     if (k > 0) { f->begin = jobs[k - 1].end; f->last_char = 0; }
     for (int t = 0; t < n; t++) free(jobs[t].v);
 }
+
+/* Input bytes not yet handed out (memory mode: exact; stream mode: unknown = UINT64_MAX).  The batcher sizes its
+ * last batches with it. */
+uint64_t dsb_fq_remaining_bytes(const dsb_fq *f)
+{
+    if (f->gz || !f->mem) return UINT64_MAX;
+    if (f->pre && f->pre_i < f->pre_n) {
+        const unsigned char *next = (const unsigned char *)f->pre[f->pre_i].name;
+        if (next >= f->mem && next <= f->mem + f->mem_n) return (uint64_t)(f->mem + f->mem_n - next);
+    }
+    return f->end > f->begin ? (uint64_t)(f->end - f->begin) : 0;
+}
+

@@ -59,6 +59,7 @@ typedef struct dsb_fq dsb_fq;
 dsb_fq *dsb_fq_open_path(const char *path);                 /* plain or gzip */
 dsb_fq *dsb_fq_open_mem(const char *buf, uint64_t n);       /* plain or gzip bytes */
 void dsb_fq_close(dsb_fq *f);
+uint64_t dsb_fq_remaining_bytes(const dsb_fq *f);           /* UINT64_MAX when unknown (streams) */
 
 typedef struct dsb_strbuf { char *s; size_t l, m; } dsb_strbuf;
 /* next record: >= 0 sequence length, -1 end of input, -2 malformed quality (kseq_read codes).
