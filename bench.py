@@ -437,7 +437,7 @@ def run_ours(args):
         "gpu_launches": launches,
         "kernel_ms": {"exist": ms_exist / args.steps, "classify": k_ms, "total": ms_total / args.steps,
                       "classify_stages_last_step": batch.stage_ms if batch.split else None},
-        "roofline": {"bound": "hbm", "kernel": "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "classify stage = k_islands + k_seed + k_classify (the path's work counters span the three launches)" if batch.split else "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes": alg, "peak_source": peak_src},
         "counters": counters,

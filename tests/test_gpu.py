@@ -82,6 +82,15 @@ def test_batch_size_and_rerun_do_not_change_results(mixed):
     assert run_cli(mixed["idx"], mixed["reads"], env={"DSB_BLOCKS_PER_SM": "1"}) == want
 
 
+@pytest.mark.parametrize("name", ["tiny", "mixed"])
+def test_single_kernel_form_equals_split_pipeline(name, request):
+    """DSB_SPLIT=0 (everything in k_classify) and the default k_islands -> k_seed -> k_classify give the same bytes."""
+    meta = request.getfixturevalue(name)
+    want = open(os.path.join(GOLD, name + ".sam"), "rb").read()
+    assert run_cli(meta["idx"], meta["reads"], env={"DSB_SPLIT": "0"}) == want
+    assert run_cli(meta["idx"], meta["reads"], env={"DSB_SPLIT": "1", "DSB_BATCH_BASES": "300000"}) == want
+
+
 def test_cfg2_full_size_against_reference(have_ref_binary):
     """BASELINE.json configs[1] at full size: 10 000 x 5 kb reads on the 50 Mbp index, reads in file order.
     Every read whose reference answer is DEFINED must be identical.  A read is reference-undefined when some

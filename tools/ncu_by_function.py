@@ -63,11 +63,16 @@ def main():
             kernel = args.pop(0)
         else:
             so = a
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], stdout=subprocess.PIPE, check=True).stdout.decode()
+    out = subprocess.run(["ncu", "-i", rep, "--kernel-name", "regex:^" + kernel, "--page", "source", "--csv"],
+                         stdout=subprocess.PIPE, check=True).stdout.decode()
     rows = list(csv.reader(out.splitlines()))
     hdr = rows[1]
     col = {n: i for i, n in enumerate(hdr)}
-    body = rows[2:]
+    body = []
+    for r in rows[2:]:                      # one section per captured launch of the kernel: keep the first
+        if r and r[0] == "Kernel Name":
+            break
+        body.append(r)
     ranges, n_inst = function_ranges(so, kernel)
     if n_inst != len(body):
         print("warning: nvdisasm has %d instructions, the report %d (different build?)" % (n_inst, len(body)), file=sys.stderr)
