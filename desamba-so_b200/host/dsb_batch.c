@@ -362,7 +362,7 @@ static void copy_part(void *arg, int part, int n_parts)
     if (text->l) memcpy(j->dst + j->off[part], text->s, text->l);
 }
 
-static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *st)
+static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *st, double t_start)
 {
     batch_meta *m = &s->meta[k];
     fmt_job j;
@@ -411,7 +411,9 @@ static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn 
         st->gpu_ms_total += a; st->gpu_ms_exist += b; st->gpu_ms_classify += d;
         st->t_gpu_wait += t1 - t0;
         st->t_format += t2 - t1;
-        if (getenv("DSB_VERBOSE")) fprintf(stderr, "[dsb]   slot %d: wait %.1f ms, format %.1f ms, sink %.1f ms\n", k, 1e3 * (t1 - t0), 1e3 * (t_f - t1), 1e3 * (t2 - t_f));
+        if (getenv("DSB_VERBOSE"))
+            fprintf(stderr, "[dsb]   slot %d: wait %.1f ms, format %.1f ms, sink %.1f ms | gpu %.2f ms | t: waited from %.2f, results at %.2f, text at %.2f, sunk at %.2f\n",
+                    k, 1e3 * (t1 - t0), 1e3 * (t_f - t1), 1e3 * (t2 - t_f), a, 1e3 * (t0 - t_start), 1e3 * (t1 - t_start), 1e3 * (t_f - t_start), 1e3 * (t2 - t_start));
         add_counters(&st->counters, &c);
     }
 }
@@ -427,6 +429,8 @@ typedef struct run_ctx {
     pthread_cond_t cv;
     uint64_t submitted, drained;
     int done;
+    double t_start;
+    int verbose;
 } run_ctx;
 
 static void *drain_thread(void *argp)
@@ -438,7 +442,7 @@ static void *drain_thread(void *argp)
         const int have = r->submitted > b;
         pthread_mutex_unlock(&r->mu);
         if (!have) return NULL;
-        drain_slot(r->s, (int)(b % (uint64_t)r->s->n_slots), r->o, r->sink, r->ctx, r->stats);
+        drain_slot(r->s, (int)(b % (uint64_t)r->s->n_slots), r->o, r->sink, r->ctx, r->stats, r->t_start);
         pthread_mutex_lock(&r->mu);
         r->drained = b + 1;
         pthread_cond_broadcast(&r->cv);
@@ -456,6 +460,8 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     run_ctx r;
     memset(&r, 0, sizeof r);
     r.s = s; r.o = o; r.sink = sink; r.ctx = ctx; r.stats = stats;
+    r.t_start = t_start;
+    r.verbose = getenv("DSB_VERBOSE") != NULL;
     pthread_mutex_init(&r.mu, NULL);
     pthread_cond_init(&r.cv, NULL);
     pthread_t th;
@@ -466,6 +472,7 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         double t0 = dsb_now();
         dsb_fq_prescan(f, s->e->fmt_threads);
         stats->t_parse += dsb_now() - t0;
+        if (r.verbose) fprintf(stderr, "[dsb]   prescan done at %.2f ms\n", 1e3 * (dsb_now() - t_start));
     }
     for (uint64_t b = 0; !eof; b++) {
         const int k = (int)(b % (uint64_t)s->n_slots);
@@ -495,7 +502,11 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         stats->n_reads += n;
         stats->n_bases += s->meta[k].n_bases;
         stats->n_batches++;
+        const double t_filled = dsb_now();
         if (dsb_slot_submit(s->slots[k], n, s->meta[k].n_bases) != 0) dsb_fatal("submit failed: %s", dsb_last_error());
+        if (r.verbose)
+            fprintf(stderr, "[dsb]   batch %llu -> slot %d: %u reads %llu bases, fill %.2f..%.2f, submitted at %.2f ms\n", (unsigned long long)b, k, n,
+                    (unsigned long long)s->meta[k].n_bases, 1e3 * (t0 - t_start), 1e3 * (t_filled - t_start), 1e3 * (dsb_now() - t_start));
         pthread_mutex_lock(&r.mu);
         r.submitted = b + 1;
         pthread_cond_broadcast(&r.cv);

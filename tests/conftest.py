@@ -67,3 +67,43 @@ def sam_records(text):
         f = line.split("\t")
         d.setdefault(f[0], []).append(tuple(f[:6] + f[11:12]))
     return d
+
+
+def ref_resident_session(idx_dir, slices, flag, snap):
+    """The UNMODIFIED reference library (oracle/_ref/libdesamba.so, the checker) driven the way BASELINE.json
+    configs[4] describes: one load_index, then read_classify + meta_analysis per slice on one thread_id.  Runs in
+    a child process (the reference prints to stderr and aborts on errors)."""
+    code = r'''
+import ctypes as C, sys, pickle
+lib = C.CDLL(sys.argv[1]); libc = C.CDLL(None); libc.free.argtypes = [C.c_void_p]
+idx = C.c_void_p(); lib.load_index(C.byref(idx), sys.argv[2].encode())
+lib.read_classify.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int, C.c_int]
+lib.meta_analysis.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int, C.c_int,
+                              C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+slices, flag, snap = pickle.load(open(sys.argv[3], "rb"))
+res = []
+for fq in slices:
+    o, n = C.c_void_p(), C.c_uint64(0)
+    lib.read_classify(idx, fq, len(fq), C.byref(o), C.byref(n), 7, 1)
+    sam = C.string_at(o.value, n.value)
+    out, m, hs, hn = C.c_void_p(), C.c_uint64(0), C.c_void_p(), C.c_uint64(0)
+    lib.meta_analysis(idx, sam, len(sam), C.byref(out), C.byref(m), 7, flag, snap, C.byref(hs), C.byref(hn))
+    res.append((sam, C.string_at(out.value, m.value), C.string_at(hs.value, hn.value) if hs.value else None))
+pickle.dump(res, open(sys.argv[4], "wb"))
+'''
+    import pickle
+    import sys
+    import tempfile
+    d = tempfile.mkdtemp()
+    pickle.dump((slices, flag, snap), open(os.path.join(d, "in.pkl"), "wb"))
+    r = subprocess.run([sys.executable, "-c", code, os.path.join(ROOT, "oracle", "_ref", "libdesamba.so"), idx_dir + "/",
+                        os.path.join(d, "in.pkl"), os.path.join(d, "out.pkl")], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    return pickle.load(open(os.path.join(d, "out.pkl"), "rb"))
+
+
+def fastq_slices(path, n_slices):
+    recs = open(path, "rb").read().split(b"\n")
+    n_rec = len(recs) // 4
+    per = (n_rec + n_slices - 1) // n_slices
+    return [b"\n".join(recs[4 * i:4 * min(i + per, n_rec)]) + b"\n" for i in range(0, n_rec, per)]

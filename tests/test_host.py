@@ -241,3 +241,23 @@ def test_parallel_fastq_prescan_equals_sequential_reader(built):
     clean = "".join(p for p in parts if p.startswith("@r")).encode()
     assert _records(lib, clean, 8) == _records(lib, clean, 0)
     assert _records(lib, clean[:-7], 8) == _records(lib, clean[:-7], 0)
+
+
+def test_resident_index_call_sequence_through_hostsim(mixed, have_ref_binary):
+    """BASELINE.json configs[4], host logic on CPU: one load_index, consecutive read_classify slices on one thread_id,
+    meta_analysis after each; the whole call sequence equals the unmodified reference library driven the same way
+    (the buffer history carries across calls).  The GPU twin is tests/test_gpu.py::test_resident_index_repeated_batches_with_meta_analysis."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdesamba.so")):
+        pytest.skip("reference library absent")
+    import pydsb
+    from conftest import fastq_slices, ref_resident_session
+    slices = fastq_slices(mixed["reads"], 5)
+    slices = slices + slices[:2]
+    want = ref_resident_session(mixed["idx"], slices, 1, 65536)
+    d = pydsb.Desamba(hostsim=True)
+    d.load_index(mixed["idx"])
+    for i, (fq, (w_sam, w_meta, w_snap)) in enumerate(zip(slices, want)):
+        sam = d.read_classify(fq, thread_id=7, thread_num=1)
+        assert sam == w_sam, i
+        meta, snap = d.meta_analysis(sam, thread_id=7, flag=1, max_snapshot_len=65536)
+        assert (meta, snap) == (w_meta, w_snap), i

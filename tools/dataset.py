@@ -38,6 +38,11 @@ CONFIGS = {
                  n_reads=10000, read_len=5000, err=0.10, read_seed=43, junk=0.05, mix="1,1,1", jitter=0.0),
     "ont10k": dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
                    n_reads=4000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5),
+    # BASELINE.json configs[2] scaled to what the reference's index builder finishes in minutes on the GPU box
+    # (4 Gbp needs > 60 GB of host memory and hours): 200 Mbp = 40 families x 5 strains x 1 Mbp,
+    # 20 000 ONT-like 10 kb reads (10 % error, 30/30/40 sub/ins/del)
+    "cfg3s": dict(families=40, strains=5, length=1000000, snp=0.01, ref_seed=44, human_first=False,
+                  n_reads=20000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5),
 }
 
 
