@@ -59,6 +59,7 @@ struct dsb_index {
     int dev;
     DsbIndexView v;                 // pointers are DEVICE pointers
     std::vector<void *> allocs;
+    std::vector<size_t> alloc_bytes;   // same order as allocs (dsb_index_clone copies array by array)
     uint64_t bytes;
     int sm_count;
 };
@@ -1077,6 +1078,63 @@ __global__ void __launch_bounds__(256) k_exist_flat(const __grid_constant__ DsbI
 // ------------------------------------------------------------------------------------------
 // C-ABI: index
 // ------------------------------------------------------------------------------------------
+
+// ---------------------------------------------------------------------------------------
+// FM re-blocking on the device (the index upload's only transform): one thread per 64-symbol block.
+// Input = the reference's occ array as it is on disk: blocks of 168 B = 5 x u64 counts of A,C,G,T,# before
+// symbol 256*b, then 256 symbols as nibbles, low nibble first (reference src/bwt.c:32-41,52,214-220).
+// Output = DsbFmBlock (dsb_layout.cuh): cumulative A/C/G/T counts + four bit planes.  Device twin of the
+// host function dsb_fm_reblock (kept for the test-only host simulator and as the checker of this kernel).
+// ---------------------------------------------------------------------------------------
+static __device__ __forceinline__ uint64_t dsb_gather_every_4th_bit(uint64_t y)   // bits 4k of y -> bits k
+{
+    y = (y | (y >> 3)) & 0x0303030303030303ull;
+    y = (y | (y >> 6)) & 0x000f000f000f000full;
+    y = (y | (y >> 12)) & 0x000000ff000000ffull;
+    y = (y | (y >> 24)) & 0xffffull;
+    return y;
+}
+
+static __device__ __forceinline__ void dsb_count_nibbles(uint64_t x, uint64_t cnt[4])
+{
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        uint64_t z = x ^ (0x1111111111111111ull * (uint64_t)c);
+        z |= z >> 1;
+        z |= z >> 2;                                     // bit 0 of every nibble = the nibble differs from c
+        cnt[c] += 16u - (uint32_t)__popcll(z & 0x1111111111111111ull);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_fm_reblock(const uint64_t *__restrict__ occ, uint64_t nb, DsbFmBlock *__restrict__ out)
+{
+    const uint64_t t = (uint64_t)blockIdx.x * 256u + threadIdx.x;
+    if (t >= nb * 4) return;
+    const uint64_t b = t >> 2;
+    const int s = (int)(t & 3);
+    const uint64_t *blk = occ + b * 21;                  // 168 B = 21 words
+    uint64_t cnt[4] = {blk[0], blk[1], blk[2], blk[3]};
+    const uint64_t *data = blk + 5;                      // 16 words x 16 nibbles
+    for (int w = 0; w < 4 * s; w++) dsb_count_nibbles(data[w], cnt);
+    DsbFmBlock o;
+#pragma unroll
+    for (int c = 0; c < 4; c++) { o.cnt[c] = cnt[c]; o.plane[c] = 0; }
+#pragma unroll
+    for (int w = 0; w < 4; w++) {
+        const uint64_t x = data[4 * s + w];
+#pragma unroll
+        for (int pl = 0; pl < 4; pl++)
+            o.plane[pl] |= dsb_gather_every_4th_bit((x >> pl) & 0x1111111111111111ull) << (16 * w);
+    }
+    out[t] = o;
+    if (t == nb * 4 - 1) {                               // terminal block: counts after the last symbol, so that r == n works
+        for (int w = 0; w < 4; w++) dsb_count_nibbles(data[4 * s + w], cnt);
+        DsbFmBlock e;
+        for (int c = 0; c < 4; c++) { e.cnt[c] = cnt[c]; e.plane[c] = 0; }
+        out[nb * 4] = e;
+    }
+}
+
 template <typename T>
 static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_zero, const T **out)
 {
@@ -1084,6 +1142,7 @@ static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_ze
     const size_t bytes = (size_t)(count + extra_zero) * sizeof(T);
     CU(cudaMalloc(&d, bytes ? bytes : 16));
     ix->allocs.push_back(d);
+    ix->alloc_bytes.push_back(bytes ? bytes : 16);
     if (count) CU(cudaMemcpy(d, src, (size_t)count * sizeof(T), cudaMemcpyHostToDevice));
     if (extra_zero) CU(cudaMemset((char *)d + (size_t)count * sizeof(T), 0, (size_t)extra_zero * sizeof(T)));
     ix->bytes += bytes;
@@ -1129,17 +1188,39 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     DsbIndexView &v = ix->v;
     memset(&v, 0, sizeof v);
     int rc = 0;
-    {   // FM index: re-block on the host into 64-symbol / 64-byte blocks, then one copy
+    {   // FM index: the occ array goes up as it is on disk and is re-blocked into 64-symbol / 64-byte blocks by k_fm_reblock
+        const uint64_t nb = h->bwt_bytes / 168;
         const uint64_t nblk = dsb_fm_blocks_needed(h->bwt_bytes);
-        std::vector<DsbFmBlock> fm(nblk);
-        uint64_t bad = 0;
-        dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, fm.data(), &bad);
-        // `bad` counts blocks whose stored '#' checkpoint differs from the one derived from A/C/G/T
-        // (padding after the last BWT symbol); the classifier never consumes a '#' rank, so it is
-        // informational only.
-        (void)bad;
+        void *d_fm = nullptr, *d_raw = nullptr;
+        CU(cudaMalloc(&d_fm, nblk * sizeof(DsbFmBlock)));
+        ix->allocs.push_back(d_fm);
+        ix->alloc_bytes.push_back(nblk * sizeof(DsbFmBlock));
+        ix->bytes += nblk * sizeof(DsbFmBlock);
+        v.fm = (const DsbFmBlock *)d_fm;
         v.n_fm_blocks = nblk;
-        rc |= upload(ix, fm.data(), nblk, 1, &v.fm);
+        if (nb == 0) {
+            CU(cudaMemset(d_fm, 0, nblk * sizeof(DsbFmBlock)));
+        } else {
+            CU(cudaMalloc(&d_raw, nb * 168));
+            CU(cudaMemcpy(d_raw, h->bwt_occ, nb * 168, cudaMemcpyHostToDevice));
+            k_fm_reblock<<<(unsigned)((nb * 4 + 255) / 256), 256>>>((const uint64_t *)d_raw, nb, (DsbFmBlock *)d_fm);
+            g_launches++;
+            cudaError_t e = cudaDeviceSynchronize();
+            cudaFree(d_raw);
+            if (e != cudaSuccess) { fail("k_fm_reblock", e); dsb_index_free(ix); return -1; }
+        }
+        if (getenv("DSB_VERIFY_REBLOCK")) {              // tests: the device blocks equal the host function's, byte for byte
+            std::vector<DsbFmBlock> want(nblk), got(nblk);
+            uint64_t bad = 0;
+            dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, want.data(), &bad);
+            CU(cudaMemcpy(got.data(), d_fm, nblk * sizeof(DsbFmBlock), cudaMemcpyDeviceToHost));
+            if (memcmp(want.data(), got.data(), nblk * sizeof(DsbFmBlock)) != 0) {
+                g_err = "k_fm_reblock differs from the host re-blocking";
+                dsb_index_free(ix);
+                return -1;
+            }
+            fprintf(stderr, "[dsb] k_fm_reblock verified against the host re-blocking: %llu blocks identical\n", (unsigned long long)nblk);
+        }
     }
     memcpy(v.rank, h->rank, sizeof v.rank);
     v.dollar_pos = h->dollar_pos;
@@ -1169,6 +1250,76 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     v.filter_min_score_lv3 = h->filter_min_score_lv3;
     if (rc) { dsb_index_free(ix); return -1; }
     // the classifier's frames are deep (LV tables, merge-sort stacks): give them room
+    cudaDeviceSetLimit(cudaLimitStackSize, 8192);
+    *out = ix;
+    return 0;
+}
+
+// A replica of a resident index on another GPU of the box, copied array by array from the first GPU's HBM
+// (cudaMemcpyPeer: NVLink / NVSwitch when peer access is possible, staged by the driver otherwise) instead of being
+// uploaded and re-blocked from host memory again.
+int dsb_index_clone(const dsb_index *src, int dev, dsb_index **out)
+{
+    *out = nullptr;
+    if (!src) { g_err = "dsb_index_clone: no source index"; return -1; }
+    CU(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, dev));
+    if (prop.major < 10) {
+        g_err = "device is not sm_100-class; this library carries sm_100a code only";
+        return -1;
+    }
+    if (dev != src->dev) {
+        int can = 0;
+        if (cudaDeviceCanAccessPeer(&can, dev, src->dev) == cudaSuccess && can) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(src->dev, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { fail("cudaDeviceEnablePeerAccess", e); return -1; }
+            cudaGetLastError();
+        }
+    }
+    dsb_index *ix = new dsb_index();
+    ix->dev = dev;
+    ix->bytes = 0;
+    ix->sm_count = prop.multiProcessorCount;
+    ix->v = src->v;
+    for (size_t i = 0; i < src->allocs.size(); i++) {
+        void *d = nullptr;
+        const size_t bytes = src->alloc_bytes[i];
+        cudaError_t e = cudaMalloc(&d, bytes);
+        if (e == cudaSuccess) {
+            ix->allocs.push_back(d);
+            ix->alloc_bytes.push_back(bytes);
+            ix->bytes += bytes;
+            e = cudaMemcpyPeer(d, dev, src->allocs[i], src->dev, bytes);
+        }
+        if (e != cudaSuccess) { fail("dsb_index_clone", e); dsb_index_free(ix); return -1; }
+    }
+    CU(cudaDeviceSynchronize());
+    // every device pointer of the view moves to the same offset of the corresponding new array
+    bool ok = true;
+    auto remap = [&](const void *p) -> const void * {
+        if (!p) return nullptr;
+        for (size_t i = 0; i < src->allocs.size(); i++) {
+            const char *b = (const char *)src->allocs[i];
+            if ((const char *)p >= b && (const char *)p < b + src->alloc_bytes[i]) return (const char *)ix->allocs[i] + ((const char *)p - b);
+        }
+        ok = false;
+        return nullptr;
+    };
+    DsbIndexView &v = ix->v;
+    v.fm = (const DsbFmBlock *)remap(v.fm);
+    v.lut = (const uint64_t *)remap(v.lut);
+    v.sa = (const uint64_t *)remap(v.sa);
+    v.ek0 = (const uint8_t *)remap(v.ek0);
+    v.ek1 = (const uint8_t *)remap(v.ek1);
+    v.unitig = (const uint64_t *)remap(v.unitig);
+    v.ref_pos = (const uint64_t *)remap(v.ref_pos);
+    v.ref_bin = (const uint8_t *)remap(v.ref_bin);
+    v.ref_off = (const uint64_t *)remap(v.ref_off);
+    v.ref_len = (const uint64_t *)remap(v.ref_len);
+    v.q_mem = (const int32_t *)remap(v.q_mem);
+    v.q_lv = (const int32_t *)remap(v.q_lv);
+    if (!ok) { g_err = "dsb_index_clone: a view pointer lies outside the index's arrays"; dsb_index_free(ix); return -1; }
     cudaDeviceSetLimit(cudaLimitStackSize, 8192);
     *out = ix;
     return 0;

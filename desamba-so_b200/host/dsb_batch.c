@@ -99,9 +99,20 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     /* DSB_GPU_FIRST: first device ordinal (one-process-per-GPU launchers give each rank its own) */
     int first = (int)env_u64("DSB_GPU_FIRST", 0);
     if (first + want > have) first = 0;
-    for (int g = 0; g < want; g++)
-        if (dsb_index_upload(&ix->h, first + g, &e->dev[g]) != 0)
-            dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
+    /* the first GPU gets the index from host memory; the others copy it from the first GPU's HBM (DSB_INDEX_CLONE=0:
+     * every GPU uploads from the host, for timing comparisons) */
+    const int clone = (int)env_u64("DSB_INDEX_CLONE", 1);
+    for (int g = 0; g < want; g++) {
+        const double t0 = dsb_now();
+        if (g == 0 || !clone) {
+            if (dsb_index_upload(&ix->h, first + g, &e->dev[g]) != 0)
+                dsb_fatal("index upload to GPU %d failed: %s", first + g, dsb_last_error());
+        } else if (dsb_index_clone(e->dev[0], first + g, &e->dev[g]) != 0)
+            dsb_fatal("index copy GPU %d -> GPU %d failed: %s", first, first + g, dsb_last_error());
+        if (getenv("DSB_VERBOSE"))
+            fprintf(stderr, "[dsb] index on GPU %d in %.1f ms (%s, %.1f MB)\n", first + g, 1e3 * (dsb_now() - t0),
+                    (g == 0 || !clone) ? "host upload + k_fm_reblock" : "peer copy", dsb_index_device_bytes(e->dev[g]) / 1e6);
+    }
     e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)16 << 20);
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
     e->batch_first = env_u64("DSB_BATCH_FIRST", e->batch_bases);      /* measured: ramping up from 1-4 Mbases costs 1-3 ms on a 50 Mbase call */

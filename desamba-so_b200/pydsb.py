@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_DIR = os.environ.get("DSB_LIB_DIR") or os.path.join(HERE, "lib")     # DSB_LIB_DIR: A/B builds of the CUDA layer
 
 API_SYMBOLS = ["load_index", "read_classify", "meta_analysis"]
-CUDA_SYMBOLS = ["dsb_gpu_count", "dsb_index_upload", "dsb_index_free", "dsb_index_device_bytes", "dsb_slot_create",
+CUDA_SYMBOLS = ["dsb_gpu_count", "dsb_index_upload", "dsb_index_clone", "dsb_index_free", "dsb_index_device_bytes", "dsb_slot_create",
                 "dsb_slot_free", "dsb_slot_staging", "dsb_slot_submit", "dsb_slot_wait", "dsb_slot_timing",
                 "dsb_slot_rerun_device", "dsb_last_error", "dsb_kernel_launch_count", "dsb_fm_rank_batch",
                 "dsb_exist_batch"]

@@ -50,8 +50,12 @@ typedef struct dsb_host_index {
 typedef struct dsb_index dsb_index;   /* device-resident, immutable after upload */
 
 int  dsb_gpu_count(void);
-/* Re-block the FM index for 128-bit loads, copy every array to device `dev`. */
+/* Copy every array to device `dev`; the FM occ array (reference src/bwt.c:68-104 layout) is re-blocked for
+ * 128-bit loads by a kernel on the device.  Replaces the per-process load of reference src/idx.c:1103-1160. */
 int  dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out);
+/* A replica of `src` on device `dev`, copied GPU to GPU (peer copy over NVLink when available): how the second
+ * and later GPUs of a box get the index. */
+int  dsb_index_clone(const dsb_index *src, int dev, dsb_index **out);
 void dsb_index_free(dsb_index *ix);
 /* bytes resident on the device for this index */
 uint64_t dsb_index_device_bytes(const dsb_index *ix);

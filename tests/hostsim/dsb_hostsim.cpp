@@ -110,6 +110,18 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
 }
 
 void dsb_index_free(dsb_index *ix) { delete ix; }
+
+int dsb_index_clone(const dsb_index *src, int dev, dsb_index **out)
+{
+    (void)dev;
+    dsb_index *ix = new dsb_index(*src);                  // simulated "devices" share nothing: a deep copy, pointers rebound
+    DsbIndexView &v = ix->v;
+    v.fm = ix->fm.data(); v.lut = ix->lut.data(); v.sa = ix->sa.data(); v.ek0 = ix->ek0.data(); v.ek1 = ix->ek1.data();
+    v.unitig = ix->unitig.data(); v.ref_pos = ix->ref_pos.data(); v.ref_bin = ix->ref_bin.data();
+    v.ref_off = ix->ref_off.data(); v.ref_len = ix->ref_len.data(); v.q_mem = ix->q_mem.data(); v.q_lv = ix->q_lv.data();
+    *out = ix;
+    return 0;
+}
 uint64_t dsb_index_device_bytes(const dsb_index *ix) { return ix->bytes; }
 
 int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_slot **out)

@@ -196,3 +196,29 @@ def test_cfg3_scaled_against_reference(have_ref_binary):
           (len(want), len(undefined), len(bad), len(want) - len(undefined)))
     assert bad <= undefined, sorted(bad - undefined)[:5]
     assert len(undefined) <= 0.05 * len(want), len(undefined)
+
+
+def test_device_reblocking_equals_host_reblocking(tiny):
+    """Index upload: k_fm_reblock (device) writes the same FM blocks, byte for byte, as the host re-blocking function
+    that the host simulator uses (DSB_VERIFY_REBLOCK makes dsb_index_upload compare them and fail otherwise)."""
+    e = dict(os.environ, DSB_VERIFY_REBLOCK="1")
+    r = subprocess.run([CLI, "classify", "-g", "1", "-f", "SAM", tiny["idx"], tiny["reads"]], stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE, env=e)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    assert b"k_fm_reblock verified" in r.stderr
+    assert r.stdout == open(os.path.join(GOLD, "tiny.sam"), "rb").read()
+
+
+def test_two_gpus_of_one_process_equal_one_gpu(mixed):
+    """index replicated (GPU 1 gets it by peer copy from GPU 0), batches alternate between the devices,
+    output order and bytes unchanged.  Needs a box with two GPUs."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU on this box")
+    want = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
+    for env in ({"DSB_BATCH_READS": "23"}, {"DSB_BATCH_READS": "23", "DSB_INDEX_CLONE": "0"}):
+        e = dict(os.environ, **env)
+        r = subprocess.run([CLI, "classify", "-g", "2", "-f", "SAM", mixed["idx"], mixed["reads"]], stdout=subprocess.PIPE,
+                           stderr=subprocess.PIPE, env=e)
+        assert r.returncode == 0, r.stderr.decode()[-2000:]
+        assert r.stdout == want
