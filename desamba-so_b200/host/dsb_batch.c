@@ -72,8 +72,9 @@ struct dsb_session {
     fmt_worker_arg pool_arg[MAX_FMT_THREADS];
     fmt_pool cpool;                 /* staging-copy helpers (used by the producer) */
     fmt_worker_arg cpool_arg[MAX_FMT_THREADS];
-    const char **copy_src;          /* per read of the batch being filled: where its bases still have to be copied from */
+    const char ***copy_src;         /* [slot][read]: where the read's bases still have to be copied from (NULL: already in staging) */
     dsb_strbuf fmt_buf[MAX_FMT_THREADS + 1];
+    size_t *fmt_ins, *fmt_end;      /* per read of the batch being formatted (SAM_FULL, direct mode): splice point / end of its fields */
     /* a record that did not fit the previous batch */
     int have_carry;
     dsb_rec_view carry;
@@ -216,9 +217,12 @@ dsb_session *dsb_session_create(dsb_engine *e)
         s->meta[k].qual_off = (uint64_t *)dsb_xmalloc((size_t)e->batch_reads * 8);
     }
     s->hist = dsb_history_new();
+    s->fmt_ins = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
+    s->fmt_end = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
     pool_start(&s->pool, s->pool_arg, e->fmt_threads - 1);
-    pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > 4 ? 4 : e->fmt_threads) - 1);
-    s->copy_src = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
+    pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > 6 ? 6 : e->fmt_threads) - 1);
+    s->copy_src = (const char ***)dsb_xcalloc((size_t)s->n_slots, sizeof(char **));
+    for (int k = 0; k < s->n_slots; k++) s->copy_src[k] = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
     return s;
 }
 
@@ -227,6 +231,7 @@ void dsb_session_destroy(dsb_session *s)
     if (!s) return;
     pool_stop(&s->pool);
     pool_stop(&s->cpool);
+    for (int k = 0; k < s->n_slots; k++) free(s->copy_src[k]);
     free(s->copy_src);
     for (int k = 0; k < s->n_slots; k++) {
         dsb_slot_free(s->slots[k]);
@@ -237,13 +242,15 @@ void dsb_session_destroy(dsb_session *s)
         free(s->meta[k].qual_off);
     }
     for (int i = 0; i <= MAX_FMT_THREADS; i++) free(s->fmt_buf[i].s);
+    free(s->fmt_ins);
+    free(s->fmt_end);
     free(s->slots);
     free(s->meta);
     dsb_history_free(s->hist);
     free(s);
 }
 
-typedef struct copy_job { dsb_session *s; char *seq; const dsb_read_desc *desc; uint32_t n; uint64_t bases; } copy_job;
+typedef struct copy_job { const char **src; char *seq; const dsb_read_desc *desc; uint32_t n; uint64_t bases; } copy_job;
 
 static void copy_seq_part(void *arg, int part, int n_parts)
 {
@@ -253,10 +260,13 @@ static void copy_seq_part(void *arg, int part, int n_parts)
     uint32_t a = 0, b = j->n;
     while (a < b) { const uint32_t mid = (a + b) / 2; if (j->desc[mid].seq_off < lo) a = mid + 1; else b = mid; }
     for (uint32_t i = a; i < j->n && j->desc[i].seq_off < hi; i++)
-        if (j->s->copy_src[i]) memcpy(j->seq + j->desc[i].seq_off, j->s->copy_src[i], j->desc[i].len);
+        if (j->src[i]) memcpy(j->seq + j->desc[i].seq_off, j->src[i], j->desc[i].len);
 }
 
-/* parse up to one batch into slot k; returns number of reads (0 = input exhausted) */
+/* Record loop of one batch: descriptors, history bytes, names, quality views of up to one batch go into slot k's staging,
+ * in read order.  The bases of stable (zero-copy) records are NOT moved here: the submit thread copies them with the copy
+ * pool and launches the batch while this thread already runs the record loop of the next one.  Returns the number of
+ * reads (0 = input exhausted). */
 static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *eof, uint64_t limit_bases)
 {
     dsb_engine *e = s->e;
@@ -295,8 +305,8 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
         /* a stable view's bases stay where they are until the copy helpers move the whole batch at once; the
          * history model only needs to READ them, from wherever they live */
         const char *src = v.seq;
-        if (v.stable) s->copy_src[n] = v.seq;
-        else { memcpy(seq + bases, v.seq, L); s->copy_src[n] = NULL; src = seq + bases; }
+        if (v.stable) s->copy_src[k][n] = v.seq;
+        else { memcpy(seq + bases, v.seq, L); s->copy_src[k][n] = NULL; src = seq + bases; }
         desc[n].seq_off = bases;
         desc[n].len = (uint32_t)L;
         desc[n].flags = dsb_history_next(s->hist, src, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES));
@@ -323,10 +333,6 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
     }
     m->n_reads = n;
     m->n_bases = bases;
-    if (n) {
-        copy_job cj = {s, seq, desc, n, bases};
-        pool_run(&s->cpool, copy_seq_part, &cj);
-    }
     return n;
 }
 
@@ -348,6 +354,7 @@ typedef struct fmt_job {
     uint32_t cut[MAX_FMT_THREADS + 2];     /* part p formats reads [cut[p], cut[p+1]) */
     char *dst;                             /* direct mode: where part p's text goes = dst + off[p] */
     size_t off[MAX_FMT_THREADS + 2];
+    size_t len[MAX_FMT_THREADS + 2];       /* SAM_FULL direct mode: bytes part p will write */
 } fmt_job;
 
 static void fmt_part(void *arg, int part, int n_parts)
@@ -362,6 +369,50 @@ static void fmt_part(void *arg, int part, int n_parts)
         if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
         dsb_format_read(text, j->s->e->ix, j->o, m->names.s + m->name_off[i], j->seq + j->desc[i].seq_off, q, j->desc[i].len,
                         &j->res[i], j->hits + j->res[i].hit_off);
+    }
+}
+
+/* SAM_FULL in direct mode.  SEQ and QUAL are 99 % of a record and already sit in memory (pinned staging, caller's input):
+ * pass 1 formats only the record FIELDS and thereby learns every record's exact size, pass 2 writes fields, SEQ, QUAL
+ * straight into the caller's output block -- the bases and qualities are moved once, not twice. */
+static void fmt_fields_part(void *arg, int part, int n_parts)
+{
+    (void)n_parts;
+    fmt_job *j = (fmt_job *)arg;
+    const batch_meta *m = j->m;
+    dsb_strbuf *text = &j->s->fmt_buf[part];
+    text->l = 0;
+    size_t total = 0;
+    for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
+        const int has_q = m->qual_ptr[i] || m->qual_off[i] != UINT64_MAX;
+        dsb_format_sam_full_fields(text, j->s->e->ix, j->o, m->names.s + m->name_off[i], j->desc[i].len, &j->res[i],
+                                   j->hits + j->res[i].hit_off, &j->s->fmt_ins[i]);
+        j->s->fmt_end[i] = text->l;
+        total += (size_t)j->desc[i].len + 1 + (has_q ? (size_t)j->desc[i].len : 6);
+    }
+    j->len[part] = text->l + total;
+}
+
+static void splice_part(void *arg, int part, int n_parts)
+{
+    (void)n_parts;
+    fmt_job *j = (fmt_job *)arg;
+    const batch_meta *m = j->m;
+    const char *text = j->s->fmt_buf[part].s;
+    char *d = j->dst + j->off[part];
+    size_t from = 0;
+    for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
+        const size_t ins = j->s->fmt_ins[i], end = j->s->fmt_end[i];
+        const uint32_t L = j->desc[i].len;
+        const char *q = m->qual_ptr[i];
+        if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
+        memcpy(d, text + from, ins - from); d += ins - from;
+        memcpy(d, j->seq + j->desc[i].seq_off, L); d += L;
+        *d++ = '\t';
+        if (q) { memcpy(d, q, L); d += L; }
+        else { memcpy(d, "(null)", 6); d += 6; }
+        memcpy(d, text + ins, end - ins); d += end - ins;
+        from = end;
     }
 }
 
@@ -399,9 +450,18 @@ static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn 
         }
         j.cut[parts] = m->n_reads;
     }
-    pool_run(&s->pool, fmt_part, &j);
+    const int splice = (!sink && o->format == DSB_OUT_SAM_FULL);
+    pool_run(&s->pool, splice ? fmt_fields_part : fmt_part, &j);
     const double t_f = dsb_now();
-    if (sink) {
+    if (splice) {
+        dsb_strbuf *out = (dsb_strbuf *)ctx;
+        size_t total = 0;
+        for (int p = 0; p < parts; p++) { j.off[p] = total; total += j.len[p]; }
+        dsb_strbuf_reserve(out, total);
+        j.dst = out->s + out->l;
+        pool_run(&s->pool, splice_part, &j);
+        out->l += total;
+    } else if (sink) {
         for (int p = 0; p < parts; p++)
             if (s->fmt_buf[p].l) sink(ctx, s->fmt_buf[p].s, s->fmt_buf[p].l);
     } else {
@@ -438,8 +498,8 @@ typedef struct run_ctx {
     dsb_run_stats *stats;
     pthread_mutex_t mu;
     pthread_cond_t cv;
-    uint64_t submitted, drained;
-    int done;
+    uint64_t filled, submitted, drained;
+    int fill_done, done;
     double t_start;
     int verbose;
 } run_ctx;
@@ -461,6 +521,43 @@ static void *drain_thread(void *argp)
     }
 }
 
+/* batch b's record loop is done -> copy its bases into the pinned staging (copy pool), launch it, tell the drain thread */
+static void *submit_thread(void *argp)
+{
+    run_ctx *r = (run_ctx *)argp;
+    dsb_session *s = r->s;
+    for (uint64_t b = 0;; b++) {
+        pthread_mutex_lock(&r->mu);
+        while (r->filled <= b && !r->fill_done) pthread_cond_wait(&r->cv, &r->mu);
+        const int have = r->filled > b;
+        pthread_mutex_unlock(&r->mu);
+        if (!have) break;
+        const int k = (int)(b % (uint64_t)s->n_slots);
+        const batch_meta *m = &s->meta[k];
+        char *seq;
+        dsb_read_desc *desc;
+        uint8_t *edge;
+        if (dsb_slot_staging(s->slots[k], &seq, &desc, &edge) != 0) dsb_fatal("staging: %s", dsb_last_error());
+        const double t0 = dsb_now();
+        copy_job cj = {s->copy_src[k], seq, desc, m->n_reads, m->n_bases};
+        pool_run(&s->cpool, copy_seq_part, &cj);
+        const double t1 = dsb_now();
+        if (dsb_slot_submit(s->slots[k], m->n_reads, m->n_bases) != 0) dsb_fatal("submit failed: %s", dsb_last_error());
+        if (r->verbose)
+            fprintf(stderr, "[dsb]   batch %llu -> slot %d: base copy %.2f..%.2f, submitted at %.2f ms\n", (unsigned long long)b, k,
+                    1e3 * (t0 - r->t_start), 1e3 * (t1 - r->t_start), 1e3 * (dsb_now() - r->t_start));
+        pthread_mutex_lock(&r->mu);
+        r->submitted = b + 1;
+        pthread_cond_broadcast(&r->cv);
+        pthread_mutex_unlock(&r->mu);
+    }
+    pthread_mutex_lock(&r->mu);
+    r->done = 1;
+    pthread_cond_broadcast(&r->cv);
+    pthread_mutex_unlock(&r->mu);
+    return NULL;
+}
+
 void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *stats)
 {
     dsb_run_stats local;
@@ -475,8 +572,9 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     r.verbose = getenv("DSB_VERBOSE") != NULL;
     pthread_mutex_init(&r.mu, NULL);
     pthread_cond_init(&r.cv, NULL);
-    pthread_t th;
+    pthread_t th, th_submit;
     if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
+    if (pthread_create(&th_submit, NULL, submit_thread, &r) != 0) dsb_fatal("pthread_create failed");
     int eof = 0;
     s->have_carry = 0;
     {
@@ -513,20 +611,19 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         stats->n_reads += n;
         stats->n_bases += s->meta[k].n_bases;
         stats->n_batches++;
-        const double t_filled = dsb_now();
-        if (dsb_slot_submit(s->slots[k], n, s->meta[k].n_bases) != 0) dsb_fatal("submit failed: %s", dsb_last_error());
         if (r.verbose)
-            fprintf(stderr, "[dsb]   batch %llu -> slot %d: %u reads %llu bases, fill %.2f..%.2f, submitted at %.2f ms\n", (unsigned long long)b, k, n,
-                    (unsigned long long)s->meta[k].n_bases, 1e3 * (t0 - t_start), 1e3 * (t_filled - t_start), 1e3 * (dsb_now() - t_start));
+            fprintf(stderr, "[dsb]   batch %llu -> slot %d: %u reads %llu bases, record loop %.2f..%.2f ms\n", (unsigned long long)b, k, n,
+                    (unsigned long long)s->meta[k].n_bases, 1e3 * (t0 - t_start), 1e3 * (dsb_now() - t_start));
         pthread_mutex_lock(&r.mu);
-        r.submitted = b + 1;
+        r.filled = b + 1;
         pthread_cond_broadcast(&r.cv);
         pthread_mutex_unlock(&r.mu);
     }
     pthread_mutex_lock(&r.mu);
-    r.done = 1;
+    r.fill_done = 1;
     pthread_cond_broadcast(&r.cv);
     pthread_mutex_unlock(&r.mu);
+    pthread_join(th_submit, NULL);
     pthread_join(th, NULL);
     dsb_history_end_batch(s->hist);
     pthread_mutex_destroy(&r.mu);

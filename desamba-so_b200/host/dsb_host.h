@@ -102,6 +102,8 @@ typedef struct dsb_out_opt { int format; int max_sec_N; } dsb_out_opt;
 void dsb_format_read(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_opt *o, const char *name,
                      const char *seq, const char *qual, uint32_t read_len, const dsb_read_result *r,
                      const dsb_hit *hits);
+void dsb_format_sam_full_fields(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_opt *o, const char *name,
+                                uint32_t read_len, const dsb_read_result *r, const dsb_hit *hits, size_t *ins);
 void dsb_strbuf_reserve(dsb_strbuf *b, size_t extra);
 void dsb_strbuf_printf(dsb_strbuf *b, const char *fmt, ...) __attribute__((format(printf, 2, 3)));
 

@@ -41,15 +41,20 @@ static void sb_puts(dsb_strbuf *b, const char *s, size_t n)
     b->s[b->l] = 0;
 }
 
+/* ins != NULL: SEQ "\t" QUAL are left out and *ins receives the offset in `out` where they belong (the caller puts the
+ * three pieces straight into the final text, dsb_batch.c) */
 static void format_sam(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_opt *o, const char *name,
                        const char *seq_s, size_t seq_n, const char *qual_s, size_t qual_n, uint32_t read_l,
-                       const dsb_read_result *r, const dsb_hit *h)
+                       const dsb_read_result *r, const dsb_hit *h, size_t *ins)
 {
     if (r->n_hit == 0) {
         dsb_strbuf_printf(out, "%s\t4\t*\t0\t0\t*\t*\t0\t0\t", name);
-        sb_puts(out, seq_s, seq_n);
-        sb_puts(out, "\t", 1);
-        sb_puts(out, qual_s, qual_n);
+        if (ins) *ins = out->l;
+        else {
+            sb_puts(out, seq_s, seq_n);
+            sb_puts(out, "\t", 1);
+            sb_puts(out, qual_s, qual_n);
+        }
         sb_puts(out, "\t\n", 2);
         return;
     }
@@ -62,9 +67,12 @@ static void format_sam(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_ou
         mapQ_PRI = (int)((c_s->sum_score - c_s[1].sum_score) << 2);
     dsb_strbuf_printf(out, "%s\t%d\t%s\t%d\t%d\t%dS%dM%dS\t*\t0\t0\t", name, flag, ix->ref_info[c_s->ref_ID].ref_name,
                       (int)c_s->t_st, mapQ_PRI, (int)c_s->q_st, (int)(c_s->q_ed - c_s->q_st), (int)(read_l - c_s->q_ed));
-    sb_puts(out, seq_s, seq_n);
-    sb_puts(out, "\t", 1);
-    sb_puts(out, qual_s, qual_n);
+    if (ins) *ins = out->l;
+    else {
+        sb_puts(out, seq_s, seq_n);
+        sb_puts(out, "\t", 1);
+        sb_puts(out, qual_s, qual_n);
+    }
     dsb_strbuf_printf(out, "\tAS:i:%d\t\n", (int)c_s->sum_score);
     for (int loop = 0; loop <= 1; loop++) {
         for (uint32_t i = 1; i < r->n_hit; i++) {
@@ -115,13 +123,13 @@ void dsb_format_read(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_
 {
     switch (o->format) {
     case DSB_OUT_SAM:
-        format_sam(out, ix, o, name, "*", 1, "*", 1, read_len, r, hits);
+        format_sam(out, ix, o, name, "*", 1, "*", 1, read_len, r, hits, NULL);
         break;
     case DSB_OUT_SAM_FULL: {
         /* FASTA records have no quality: the reference prints whatever the recycled kseq slot
          * holds, "(null)" for a never-used slot; we always print "(null)" */
         const char *q = qual ? qual : "(null)";
-        format_sam(out, ix, o, name, seq, read_len, q, qual ? read_len : 6, read_len, r, hits);
+        format_sam(out, ix, o, name, seq, read_len, q, qual ? read_len : 6, read_len, r, hits, NULL);
         break;
     }
     case DSB_OUT_DES:
@@ -131,4 +139,11 @@ void dsb_format_read(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_
         format_des(out, ix, o, name, read_len, r, hits, 1);
         break;
     }
+}
+
+/* SAM_FULL without SEQ and QUAL: the record fields go to `out`, *ins = where "SEQ\tQUAL" has to be spliced in */
+void dsb_format_sam_full_fields(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_out_opt *o, const char *name,
+                                uint32_t read_len, const dsb_read_result *r, const dsb_hit *hits, size_t *ins)
+{
+    format_sam(out, ix, o, name, NULL, 0, NULL, 0, read_len, r, hits, ins);
 }

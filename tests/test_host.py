@@ -261,3 +261,18 @@ def test_resident_index_call_sequence_through_hostsim(mixed, have_ref_binary):
         assert sam == w_sam, i
         meta, snap = d.meta_analysis(sam, thread_id=7, flag=1, max_snapshot_len=65536)
         assert (meta, snap) == (w_meta, w_snap), i
+
+
+def test_api_splice_formatter_equals_cli_formatter(mixed, tmp_path):
+    """read_classify() writes SAM_FULL by splicing SEQ / QUAL straight into the output block (dsb_batch.c splice_part);
+    the CLI formats whole records through the sink.  Same bytes, for FASTQ and for FASTA (no qualities) input."""
+    import pydsb
+    fq = open(mixed["reads"], "rb").read()
+    lines = fq.split(b"\n")
+    fa = b"".join(b">" + lines[i][1:] + b"\n" + lines[i + 1] + b"\n" for i in range(0, len(lines) - 1, 4))
+    fa_path = str(tmp_path / "reads.fa")
+    open(fa_path, "wb").write(fa)
+    for data, path in ((fq, mixed["reads"]), (fa, fa_path)):
+        d = pydsb.Desamba(hostsim=True)
+        d.load_index(mixed["idx"])
+        assert d.read_classify(data, thread_id=3) == run_sim(mixed["idx"], [path], fmt="SAM_FULL")
