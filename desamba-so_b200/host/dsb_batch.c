@@ -18,7 +18,7 @@
 #include <string.h>
 #include <unistd.h>
 
-#define SLOTS_PER_GPU 4
+#define SLOTS_PER_GPU 4          /* default; DSB_SLOTS overrides (1..8) */
 #define MAX_FMT_THREADS 32
 
 uint32_t dsb_history_max(const dsb_history *h);
@@ -205,7 +205,10 @@ dsb_session *dsb_session_create(dsb_engine *e)
 {
     dsb_session *s = (dsb_session *)dsb_xcalloc(1, sizeof *s);
     s->e = e;
-    s->n_slots = e->n_gpu * SLOTS_PER_GPU;
+    int per_gpu = (int)env_u64("DSB_SLOTS", SLOTS_PER_GPU);
+    if (per_gpu < 1) per_gpu = 1;
+    if (per_gpu > 8) per_gpu = 8;
+    s->n_slots = e->n_gpu * per_gpu;
     s->slots = (dsb_slot **)dsb_xcalloc((size_t)s->n_slots, sizeof(dsb_slot *));
     s->meta = (batch_meta *)dsb_xcalloc((size_t)s->n_slots, sizeof(batch_meta));
     for (int k = 0; k < s->n_slots; k++) {

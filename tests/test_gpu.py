@@ -222,3 +222,26 @@ def test_two_gpus_of_one_process_equal_one_gpu(mixed):
                            stderr=subprocess.PIPE, env=e)
         assert r.returncode == 0, r.stderr.decode()[-2000:]
         assert r.stdout == want
+
+
+def test_cfg1_demo_standin_against_reference(have_ref_binary):
+    """BASELINE.json configs[0] (`classify demo_index/human demo/human.fq`): the demo files are not in the reference tree
+    (.gitignore:3-4), so the stand-in is a synthetic 5 x 1 Mbp "human" (tid 9606) contig set with 2 000 x 5 kb reads
+    (SURVEY 8c/8d).  Same rule as cfg2; the SAM_FULL text feeds meta_analysis, whose human snapshot must be non-empty."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    import dataset
+    import pydsb
+    meta = dataset.build("cfg1")
+    got = sam_records(run_cli(meta["idx"], meta["reads"]))
+    want = sam_records(open(meta["golden"], "rb").read())
+    assert list(got) == list(want)
+    bad = {k for k in want if got[k] != want[k]}
+    undefined = dataset.undefined_reads(meta)
+    assert bad <= undefined, sorted(bad - undefined)[:5]
+    assert len(undefined) <= 0.02 * len(want), len(undefined)
+    d = pydsb.Desamba()
+    d.load_index(meta["idx"])
+    sam = d.read_classify(meta["reads"], thread_id=0, thread_num=1)
+    text, snap = d.meta_analysis(sam, thread_id=0, flag=1, max_snapshot_len=65536)
+    assert text and snap
