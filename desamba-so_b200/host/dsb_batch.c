@@ -31,8 +31,10 @@ struct dsb_engine {
     uint64_t batch_bases;
     uint64_t batch_first;      /* size of the first batch of a run (DSB_BATCH_FIRST) */
     int batch_taper;           /* shrink the last batches when the input size is known (DSB_BATCH_TAPER, default 0) */
+    uint64_t batch_small;      /* batch size of a call whose input is known to be small (a few batches in all) */
     uint32_t batch_reads;
     int fmt_threads;
+    int scan_threads;          /* FASTQ pre-scan: nothing else runs yet, so it may use every core of the rank's share */
 };
 
 typedef struct batch_meta {
@@ -114,9 +116,14 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
             fprintf(stderr, "[dsb] index on GPU %d in %.1f ms (%s, %.1f MB)\n", first + g, 1e3 * (dsb_now() - t0),
                     (g == 0 || !clone) ? "host upload + k_fm_reblock" : "peer copy", dsb_index_device_bytes(e->dev[g]) / 1e6);
     }
-    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)16 << 20);
+    /* Slot capacity = the batch size of long inputs.  Measured on the 198 Mbase / 10 kb-read set: 32 Mbase batches 70 ms,
+     * 16 Mbase 80 ms, 64 Mbase 71 ms per call (a batch needs more reads than the device has warp slots to keep them
+     * busy); a 50 Mbase call is fastest with three 16 Mbase batches (DSB_BATCH_SMALL). */
+    e->batch_bases = env_u64("DSB_BATCH_BASES", (uint64_t)32 << 20);
+    e->batch_small = env_u64("DSB_BATCH_SMALL", (uint64_t)16 << 20);
+    if (e->batch_small > e->batch_bases) e->batch_small = e->batch_bases;
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
-    e->batch_first = env_u64("DSB_BATCH_FIRST", e->batch_bases);      /* measured: ramping up from 1-4 Mbases costs 1-3 ms on a 50 Mbase call */
+    e->batch_first = env_u64("DSB_BATCH_FIRST", e->batch_bases);      /* off by default: ramping up from 4 Mbases is within noise on a 50 Mbase call */
     if (e->batch_first > e->batch_bases) e->batch_first = e->batch_bases;
     e->batch_taper = (int)env_u64("DSB_BATCH_TAPER", 0);
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
@@ -124,7 +131,10 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     /* one-process-per-GPU launchers (torchrun sets LOCAL_WORLD_SIZE) share the host cores between the ranks */
     long share = (long)env_u64("LOCAL_WORLD_SIZE", 1);
     if (share > 1) ncpu = ncpu / share > 0 ? ncpu / share : 1;
-    e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 8 ? 8 : ncpu));
+    /* formatter / copy helpers: all but a few cores (producer, submit and drain threads, the CUDA driver's own) up to 12:
+     * 16 cores: 8 -> 12 helpers took 1.4 ms off a 22 ms call */
+    e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 12 ? (ncpu - 4 > 12 ? 12 : ncpu - 4) : (ncpu > 8 ? 8 : ncpu)));
+    e->scan_threads = (int)(ncpu > 32 ? 32 : ncpu);
     if (e->fmt_threads < 1) e->fmt_threads = 1;
     if (e->fmt_threads > MAX_FMT_THREADS) e->fmt_threads = MAX_FMT_THREADS;
     return e;
@@ -503,13 +513,29 @@ typedef struct run_ctx {
     pthread_cond_t cv;
     uint64_t filled, submitted, drained;
     int fill_done, done;
+    char *prefault_lo;              /* direct mode: region of the caller's output block to touch before the first batch is back */
+    size_t prefault_n;
     double t_start;
     int verbose;
 } run_ctx;
 
+static void prefault_part(void *arg, int part, int n_parts)
+{
+    run_ctx *r = (run_ctx *)arg;
+    const size_t page = 4096;
+    const size_t lo = r->prefault_n * (size_t)part / (size_t)n_parts, hi = r->prefault_n * (size_t)(part + 1) / (size_t)n_parts;
+    volatile char *p = r->prefault_lo;
+    for (size_t i = (lo + page - 1) & ~(page - 1); i < hi; i += page) p[i] = 0;
+}
+
 static void *drain_thread(void *argp)
 {
     run_ctx *r = (run_ctx *)argp;
+    if (r->prefault_n) {
+        const double t0 = dsb_now();
+        pool_run(&r->s->pool, prefault_part, r);
+        if (r->verbose) fprintf(stderr, "[dsb]   output block touched: %.1f MB in %.2f ms (until %.2f ms)\n", r->prefault_n / 1e6, 1e3 * (dsb_now() - t0), 1e3 * (dsb_now() - r->t_start));
+    }
     for (uint64_t b = 0;; b++) {
         pthread_mutex_lock(&r->mu);
         while (r->submitted <= b && !r->done) pthread_cond_wait(&r->cv, &r->mu);
@@ -576,16 +602,33 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     pthread_mutex_init(&r.mu, NULL);
     pthread_cond_init(&r.cv, NULL);
     pthread_t th, th_submit;
-    if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
-    if (pthread_create(&th_submit, NULL, submit_thread, &r) != 0) dsb_fatal("pthread_create failed");
     int eof = 0;
     s->have_carry = 0;
+    /* a call that is only a few batches long (in-memory input of known size, ~2 bytes per base) uses the small batch
+     * size: the device starts earlier and the last batch's text is shorter */
+    uint64_t call_batch = s->e->batch_bases;
+    {
+        const uint64_t bytes = dsb_fq_remaining_bytes(f);
+        if (bytes != UINT64_MAX && bytes / 2 <= 4 * s->e->batch_small) call_batch = s->e->batch_small;
+    }
+    if (!sink && s->e->fmt_threads > 1) {
+        /* direct mode: the caller's output block is fresh memory; the formatter helpers, idle until the first batch
+         * comes back from the device, touch its pages now instead of faulting them in on the critical path */
+        dsb_strbuf *out = (dsb_strbuf *)ctx;
+        if (out->m - out->l >= ((size_t)8 << 20)) {
+            r.prefault_lo = out->s + out->l;
+            r.prefault_n = out->m - out->l;
+        }
+    }
     {
         double t0 = dsb_now();
-        dsb_fq_prescan(f, s->e->fmt_threads);
+        dsb_fq_prescan(f, s->e->scan_threads);
         stats->t_parse += dsb_now() - t0;
         if (r.verbose) fprintf(stderr, "[dsb]   prescan done at %.2f ms\n", 1e3 * (dsb_now() - t_start));
     }
+    /* the helpers start once the pre-scan (which uses every core) is over */
+    if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
+    if (pthread_create(&th_submit, NULL, submit_thread, &r) != 0) dsb_fatal("pthread_create failed");
     for (uint64_t b = 0; !eof; b++) {
         const int k = (int)(b % (uint64_t)s->n_slots);
         /* batch b reuses the slot of batch b - n_slots: wait until that one has been formatted */
@@ -599,7 +642,7 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
          * 4-5 ms, so small batches lose more than their earlier start wins; profiles/): DSB_BATCH_FIRST starts small
          * and doubles; DSB_BATCH_TAPER=1 halves towards the end when the amount of input left is known. */
         uint64_t limit = s->e->batch_first << (b < 16 ? b : 16);
-        if (limit > s->e->batch_bases || limit == 0) limit = s->e->batch_bases;
+        if (limit > call_batch || limit == 0) limit = call_batch;
         {
             const uint64_t left = dsb_fq_remaining_bytes(f);
             if (left != UINT64_MAX && s->e->batch_taper) {
