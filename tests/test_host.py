@@ -276,3 +276,23 @@ def test_api_splice_formatter_equals_cli_formatter(mixed, tmp_path):
         d = pydsb.Desamba(hostsim=True)
         d.load_index(mixed["idx"])
         assert d.read_classify(data, thread_id=3) == run_sim(mixed["idx"], [path], fmt="SAM_FULL")
+
+
+def test_mapped_file_input_equals_stream_reader(mixed, tmp_path):
+    """A plain reads file is mapped and parsed in memory mode (threaded pre-scan, zero-copy views); DSB_NO_MMAP=1 keeps
+    the kseq-style stream reader the reference uses.  Same records, same output: FASTQ, FASTA with wrapped lines, and a
+    file without a final newline."""
+    want = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
+    assert run_sim(mixed["idx"], [mixed["reads"]]) == want
+    assert run_sim(mixed["idx"], [mixed["reads"]], env={"DSB_NO_MMAP": "1"}) == want
+    fq = open(mixed["reads"], "rb").read()
+    lines = fq.split(b"\n")
+    fa = b"".join(b">" + lines[i][1:] + b" some comment\n" + b"\n".join(lines[i + 1][k:k + 70] for k in range(0, len(lines[i + 1]), 70)) + b"\n"
+                  for i in range(0, len(lines) - 1, 4))
+    p1, p2 = str(tmp_path / "wrapped.fa"), str(tmp_path / "nonl.fq")
+    open(p1, "wb").write(fa)
+    open(p2, "wb").write(fq.rstrip(b"\n"))
+    for p in (p1, p2):
+        a = run_sim(mixed["idx"], [p])
+        assert a == run_sim(mixed["idx"], [p], env={"DSB_NO_MMAP": "1"})
+        assert sam_records(a) == sam_records(want)
