@@ -80,7 +80,8 @@ struct DsbIndexView {
     const DsbFmBlock *fm;
     uint64_t n_fm_blocks;
     uint64_t rank[6];
-    uint64_t dollar_pos;
+    uint64_t dollar_pos;          // what occ returns for '$' (src/bwt.c:53-54): DOLLOR_POS = unitig count - 2, NOT a BWT row
+    uint64_t dollar_row;          // the BWT row that holds '$' (found while re-blocking); ~0 if none
     const uint64_t *lut;          // 2^26+1
     const uint64_t *sa;           // lo32 unitig_ID, hi32 offset
     uint64_t sa_n;
@@ -309,9 +310,10 @@ DSB_HD uint64_t dsb_occ_ix(const DsbIndexView *ix, uint64_t r, uint8_t *c)
     if (cc < 4) {
         base = cnt_c;
     } else {
-        // '#': everything before the block that is not A/C/G/T/$
+        // '#': everything before the block that is not A/C/G/T/$.  The second LF walk of map_seed (src/cly.c:776-781)
+        // does not stop at '#', so this rank IS consumed (rarely) and has to equal the reference's stored count.
         const uint64_t start = blk << 6;
-        base = start - cnt_sum - ((ix->dollar_pos < start) ? 1 : 0);
+        base = start - cnt_sum - ((ix->dollar_row < start) ? 1 : 0);
     }
     const uint64_t x = (p0 ^ (0ull - (uint64_t)(cc & 1))) | (p1 ^ (0ull - (uint64_t)((cc >> 1) & 1))) |
                        (p2 ^ (0ull - (uint64_t)((cc >> 2) & 1))) | (p3 ^ (0ull - (uint64_t)((cc >> 3) & 1)));

@@ -1106,7 +1106,8 @@ static __device__ __forceinline__ void dsb_count_nibbles(uint64_t x, uint64_t cn
     }
 }
 
-__global__ void __launch_bounds__(256) k_fm_reblock(const uint64_t *__restrict__ occ, uint64_t nb, DsbFmBlock *__restrict__ out)
+__global__ void __launch_bounds__(256) k_fm_reblock(const uint64_t *__restrict__ occ, uint64_t nb, DsbFmBlock *__restrict__ out,
+                                                    unsigned long long *__restrict__ dollar_row)
 {
     const uint64_t t = (uint64_t)blockIdx.x * 256u + threadIdx.x;
     if (t >= nb * 4) return;
@@ -1127,6 +1128,10 @@ __global__ void __launch_bounds__(256) k_fm_reblock(const uint64_t *__restrict__
             o.plane[pl] |= dsb_gather_every_4th_bit((x >> pl) & 0x1111111111111111ull) << (16 * w);
     }
     out[t] = o;
+    {   // the one row that holds '$' (symbol 5 = planes 0 and 2 set, 1 and 3 clear)
+        const uint64_t is5 = o.plane[0] & ~o.plane[1] & o.plane[2] & ~o.plane[3];
+        if (is5) atomicMin(dollar_row, (unsigned long long)(t * 64 + (uint64_t)(__ffsll((long long)is5) - 1)));
+    }
     if (t == nb * 4 - 1) {                               // terminal block: counts after the last symbol, so that r == n works
         for (int w = 0; w < 4; w++) dsb_count_nibbles(data[4 * s + w], cnt);
         DsbFmBlock e;
@@ -1198,23 +1203,34 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
         ix->bytes += nblk * sizeof(DsbFmBlock);
         v.fm = (const DsbFmBlock *)d_fm;
         v.n_fm_blocks = nblk;
+        v.dollar_row = ~0ull;
         if (nb == 0) {
             CU(cudaMemset(d_fm, 0, nblk * sizeof(DsbFmBlock)));
         } else {
+            unsigned long long *d_row = nullptr, h_row = ~0ull;
             CU(cudaMalloc(&d_raw, nb * 168));
+            CU(cudaMalloc((void **)&d_row, 8));
+            CU(cudaMemcpy(d_row, &h_row, 8, cudaMemcpyHostToDevice));
             CU(cudaMemcpy(d_raw, h->bwt_occ, nb * 168, cudaMemcpyHostToDevice));
-            k_fm_reblock<<<(unsigned)((nb * 4 + 255) / 256), 256>>>((const uint64_t *)d_raw, nb, (DsbFmBlock *)d_fm);
+            k_fm_reblock<<<(unsigned)((nb * 4 + 255) / 256), 256>>>((const uint64_t *)d_raw, nb, (DsbFmBlock *)d_fm, d_row);
             g_launches++;
-            cudaError_t e = cudaDeviceSynchronize();
+            cudaError_t e = cudaMemcpy(&h_row, d_row, 8, cudaMemcpyDeviceToHost);
             cudaFree(d_raw);
+            cudaFree(d_row);
             if (e != cudaSuccess) { fail("k_fm_reblock", e); dsb_index_free(ix); return -1; }
+            v.dollar_row = h_row;
         }
         if (getenv("DSB_VERIFY_REBLOCK")) {              // tests: the device blocks equal the host function's, byte for byte
             std::vector<DsbFmBlock> want(nblk), got(nblk);
-            uint64_t bad = 0;
-            dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, want.data(), &bad);
+            uint64_t bad = 0, want_row = ~0ull;
+            dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, &want_row, want.data(), &bad);
             CU(cudaMemcpy(got.data(), d_fm, nblk * sizeof(DsbFmBlock), cudaMemcpyDeviceToHost));
-            if (memcmp(want.data(), got.data(), nblk * sizeof(DsbFmBlock)) != 0) {
+            if (bad) {
+                g_err = "FM index: the stored '#' checkpoints differ from the derived ones in " + std::to_string(bad) + " blocks";
+                dsb_index_free(ix);
+                return -1;
+            }
+            if (want_row != v.dollar_row || memcmp(want.data(), got.data(), nblk * sizeof(DsbFmBlock)) != 0) {
                 g_err = "k_fm_reblock differs from the host re-blocking";
                 dsb_index_free(ix);
                 return -1;

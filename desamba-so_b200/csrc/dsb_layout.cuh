@@ -135,11 +135,22 @@ DSB_HD void dsb_bind_scratch(DsbWork *w, uint8_t *base, const DsbScratchDims *d)
 // ---------------------------------------------------------------------------------------
 static inline uint64_t dsb_fm_blocks_needed(uint64_t bwt_bytes) { return (bwt_bytes / 168) * 4 + 1; }
 
-static inline uint64_t dsb_fm_reblock(const uint8_t *bwt_occ, uint64_t bwt_bytes, uint64_t dollar_pos, DsbFmBlock *out,
+// *dollar_row = the row whose symbol is '$' (nibble 5), ~0 if there is none; *mismatch_hash_count = reference blocks whose
+// stored '#' count differs from start - (A+C+G+T) - ['$' before start], the value dsb_occ_ix derives (must be 0).
+static inline uint64_t dsb_fm_reblock(const uint8_t *bwt_occ, uint64_t bwt_bytes, uint64_t *dollar_row, DsbFmBlock *out,
                                       uint64_t *mismatch_hash_count)
 {
     const uint64_t nb = bwt_bytes / 168;
     uint64_t bad = 0;
+    uint64_t d_row = ~0ull;
+    for (uint64_t b = 0; b < nb && d_row == ~0ull; b++) {
+        const uint8_t *data = bwt_occ + b * 168 + 40;
+        for (int i = 0; i < 128; i++) {
+            if ((data[i] & 0xf) == 5) { d_row = b * 256 + 2 * (uint64_t)i; break; }
+            if ((data[i] >> 4) == 5) { d_row = b * 256 + 2 * (uint64_t)i + 1; break; }
+        }
+    }
+    if (dollar_row) *dollar_row = d_row;
     uint64_t run[4] = {0, 0, 0, 0};
     for (uint64_t b = 0; b < nb; b++) {
         const uint8_t *blk = bwt_occ + b * 168;
@@ -150,7 +161,7 @@ static inline uint64_t dsb_fm_reblock(const uint8_t *bwt_occ, uint64_t bwt_bytes
         // cross-check our derived '#' count against the stored one
         {
             const uint64_t start = b * 256;
-            const uint64_t hash = start - (cnt[0] + cnt[1] + cnt[2] + cnt[3]) - ((dollar_pos < start) ? 1 : 0);
+            const uint64_t hash = start - (cnt[0] + cnt[1] + cnt[2] + cnt[3]) - ((d_row < start) ? 1 : 0);
             if (hash != base[4]) bad++;
         }
         for (int s = 0; s < 4; s++) {

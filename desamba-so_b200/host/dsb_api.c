@@ -79,7 +79,12 @@ void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint
     dsb_out_opt o = {DSB_OUT_SAM_FULL, 5};          /* reference src/cly_mt.c:970-976 */
     dsb_strbuf out = {NULL, 0, 0};
     /* SAM_FULL repeats SEQ and QUAL of every read: about the size of the input plus the record fields */
-    dsb_strbuf_reserve(&out, input_n == (uint64_t)-1 ? 1 : (size_t)(input_n + input_n / 16 + 4096));
+    if (input_n == (uint64_t)-1)
+        dsb_strbuf_reserve(&out, 1);
+    else {                                          /* exactly this much (dsb_strbuf_reserve would add half again) */
+        out.m = (size_t)(input_n + input_n / 16 + 4096);
+        out.s = (char *)dsb_xmalloc(out.m);
+    }
 #ifdef MADV_HUGEPAGE
     if (out.m >= ((size_t)4 << 20)) {
         /* a fresh block this large comes straight from mmap: ask for huge pages so that filling it

@@ -123,8 +123,10 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     e->batch_small = env_u64("DSB_BATCH_SMALL", (uint64_t)16 << 20);
     if (e->batch_small > e->batch_bases) e->batch_small = e->batch_bases;
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
-    e->batch_first = env_u64("DSB_BATCH_FIRST", e->batch_bases);      /* off by default: ramping up from 4 Mbases is within noise on a 50 Mbase call */
-    if (e->batch_first > e->batch_bases) e->batch_first = e->batch_bases;
+    /* short calls ramp up 4, 8, 16 Mbases (the device starts 1 ms earlier: 19.7 -> 19.3 ms on a 50 Mbase call, two rounds of
+     * tools/e2e_sweep.py); long inputs start with full batches */
+    e->batch_first = env_u64("DSB_BATCH_FIRST", (uint64_t)4 << 20);
+    if (e->batch_first > e->batch_bases || e->batch_first == 0) e->batch_first = e->batch_bases;
     e->batch_taper = (int)env_u64("DSB_BATCH_TAPER", 0);
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
     if (ncpu < 1) ncpu = 1;
@@ -532,6 +534,10 @@ static void *drain_thread(void *argp)
 {
     run_ctx *r = (run_ctx *)argp;
     if (r->prefault_n) {
+        /* not before the first batch is on its way: until then the copy pool's work is on the critical path */
+        pthread_mutex_lock(&r->mu);
+        while (r->submitted == 0 && !r->done) pthread_cond_wait(&r->cv, &r->mu);
+        pthread_mutex_unlock(&r->mu);
         const double t0 = dsb_now();
         pool_run(&r->s->pool, prefault_part, r);
         if (r->verbose) fprintf(stderr, "[dsb]   output block touched: %.1f MB in %.2f ms (until %.2f ms)\n", r->prefault_n / 1e6, 1e3 * (dsb_now() - t0), 1e3 * (dsb_now() - r->t_start));
@@ -641,7 +647,7 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         /* Optional batch-size schedule (both off by default: a batch of any size costs the device one read's latency,
          * 4-5 ms, so small batches lose more than their earlier start wins; profiles/): DSB_BATCH_FIRST starts small
          * and doubles; DSB_BATCH_TAPER=1 halves towards the end when the amount of input left is known. */
-        uint64_t limit = s->e->batch_first << (b < 16 ? b : 16);
+        uint64_t limit = (call_batch == s->e->batch_small) ? (s->e->batch_first << (b < 16 ? b : 16)) : call_batch;
         if (limit > call_batch || limit == 0) limit = call_batch;
         {
             const uint64_t left = dsb_fq_remaining_bytes(f);

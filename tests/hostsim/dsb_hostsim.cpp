@@ -58,7 +58,8 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     const uint64_t nblk = dsb_fm_blocks_needed(h->bwt_bytes);
     ix->fm.resize(nblk);
     uint64_t bad = 0;
-    dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, h->dollar_pos, ix->fm.data(), &bad);
+    uint64_t dollar_row = ~0ull;
+    dsb_fm_reblock(h->bwt_occ, h->bwt_bytes, &dollar_row, ix->fm.data(), &bad);
     if (bad) fprintf(stderr, "[hostsim] warning: %llu FM blocks where the derived '#' count differs from the stored one\n",
                      (unsigned long long)bad);
     const uint64_t lut_n = (1ull << 26) + 1;
@@ -80,6 +81,7 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     v.n_fm_blocks = nblk;
     memcpy(v.rank, h->rank, sizeof v.rank);
     v.dollar_pos = h->dollar_pos;
+    v.dollar_row = dollar_row;
     v.lut = ix->lut.data();
     v.sa = ix->sa.data();
     v.sa_n = h->sa_n;

@@ -57,10 +57,11 @@ def test_fm_rank_kernel_equals_reference_occ(api, tiny):
     ix = api.DeviceIndex(tiny["idx"])
     got, c_out, _ms = ix.fm_rank(r, ci)
     ix.close()
-    sel = co < 4                      # a '#' rank is never consumed by the classifier; '$' returns dollar_pos
+    # every symbol, '#' included: map_seed's second LF walk (src/cly.c:776-781) does not stop at '#', so its rank is
+    # consumed (rarely) and must equal the reference's stored checkpoint; '$' returns dollar_pos
     assert (c_out == co).all()
-    assert (got[sel] == res[sel]).all()
-    assert (got[co == 5] == res[co == 5]).all()
+    assert (got == res).all()
+    assert (co == 4).any() and (co < 4).any()
 
 
 def test_exist_kernel_equals_reference_probes(api, tiny):

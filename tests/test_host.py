@@ -296,3 +296,24 @@ def test_mapped_file_input_equals_stream_reader(mixed, tmp_path):
         a = run_sim(mixed["idx"], [p])
         assert a == run_sim(mixed["idx"], [p], env={"DSB_NO_MMAP": "1"})
         assert sam_records(a) == sam_records(want)
+
+
+def test_reblocked_fm_rank_equals_reference_occ_for_every_symbol(tiny):
+    """The re-blocked FM layout (bit planes + A/C/G/T counts; '#' derived from the true '$' row) answers the reference's
+    occ known answers for every symbol, '#' and '$' included: map_seed's second LF walk does consume a '#' rank.  Host twin
+    of tests/test_gpu.py::test_fm_rank_kernel_equals_reference_occ (same layout code, compiled for the host)."""
+    import struct
+    import numpy as np
+    import pydsb
+    raw = open(os.path.join(GOLD, "kat_tiny", "occ.bin"), "rb").read()
+    n = struct.unpack_from("<Q", raw, 0)[0]
+    o = 8
+    r = np.frombuffer(raw, dtype=np.uint64, count=n, offset=o); o += 8 * n
+    ci = np.frombuffer(raw, dtype=np.uint8, count=n, offset=o); o += n
+    co = np.frombuffer(raw, dtype=np.uint8, count=n, offset=o); o += n
+    res = np.frombuffer(raw, dtype=np.uint64, count=n, offset=o)
+    ix = pydsb.DeviceIndex(tiny["idx"], hostsim=True)
+    got, c_out, _ms = ix.fm_rank(r, ci)
+    ix.close()
+    assert (c_out == co).all() and (got == res).all()
+    assert (co == 4).any()
