@@ -1569,6 +1569,23 @@ DSB_HDN void dsb_resolve_tree(DsbWork *w)
 // order; we keep that order with head/next arrays filled from the highest position down.
 // Bucket key = low key_len bits of the 18-bit 9-mer; entries store pos+1, 0 terminates.
 // ------------------------------------------------------------------------------------------
+// Bucket-index width of the read's 9-mer table.  The reference takes the smallest 2^k >= L, k in 10..17
+// (src/cly.c:2179-2182); the width only decides how the positions with equal 9-mers are FOUND, never which ones or in what
+// order (every chain lists them in ascending position and compares the whole 9-mer), so it is a free parameter here.
+#ifndef DSB_KEYLEN_BIAS
+#define DSB_KEYLEN_BIAS 0
+#endif
+DSB_HD int dsb_read_hash_key_len(uint32_t L)
+{
+    int key_len = 10;
+    for (; key_len < 18; key_len++)
+        if ((1u << key_len) >= L) break;
+    key_len += DSB_KEYLEN_BIAS;
+    if (key_len < 10) key_len = 10;
+    if (key_len > 18) key_len = 18;
+    return key_len;
+}
+
 DSB_HD uint32_t dsb_kmer9(const uint8_t *s)
 {
     uint32_t v = 0;
@@ -1584,9 +1601,7 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         if (both_dir == 3) break;
     }
     const int q_len = (int)w->L;
-    int key_len = 10;
-    for (; key_len < 18; key_len++)
-        if ((int)(1u << key_len) >= q_len) break;
+    const int key_len = dsb_read_hash_key_len((uint32_t)q_len);
     const uint32_t key_mask = (1u << key_len) - 1u;
     const uint32_t n_pos = (uint32_t)(q_len - DSB_KMER9 + 1);
     if (w->L >= (1u << 24)) { w->overflow = 2; return key_len; }     // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes)

@@ -58,10 +58,7 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     d->Lmax = Lmax;
     d->cap_anchor = cap_anchor;
     d->cap_sms = cap_sms;
-    int key_len = 10;                                   // src/cly.c:2179-2182
-    for (; key_len < 18; key_len++)
-        if ((1u << key_len) >= Lmax) break;
-    d->head_entries = 1u << key_len;
+    d->head_entries = 1u << dsb_read_hash_key_len(Lmax);
     size_t o = 0;
 #define DSB_TAKE(field, nbytes) d->field = o; o = dsb_align_up(o + (nbytes), 64)
     const size_t n_seed = (size_t)(Lmax / 4) + 8;       // < L/4 islands per strand
