@@ -385,6 +385,10 @@ DSB_HDO void dsb_get_ref(DsbWork *w, uint8_t *dst, uint64_t uni_offset, uint32_t
 // DSB_LV_NO_BYTE, which matches nothing, like the bytes before ref[0].
 // ------------------------------------------------------------------------------------------
 #define DSB_LV_NO_BYTE 0xD0
+// Q_MEM has 2000 entries (src/idx.h:61); an exact match of 2000 bases or more makes the reference read past its table
+// (whatever follows it on the heap; reference-undefined, and modelling glibc's chunk layout there did not
+// reproduce it).  Here such a seed scores like a 1999-base one instead of faulting on the device.
+#define DSB_QMEM_IX(l) ((uint32_t)(l) < 2000u ? (uint32_t)(l) : 1999u)
 DSB_HDO int32_t dsb_lv_extd(const uint8_t *ref_in, const uint8_t *query_in, int32_t len, uint8_t query_m1)
 {
     if (len <= 0) return 0;                   // returns 0 whatever the bytes are
@@ -877,7 +881,7 @@ DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32
             dsb_get_ref(w, t_pre, t_off - 1, l_pre, false);
         }
         d_pre = (uint32_t)dsb_lv_extd(t_pre, q_pre, (int32_t)l_pre, DSB_LV_NO_BYTE);
-        s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+        s = Q_MEM[DSB_QMEM_IX(l_m)] + Q_LV[d_pre * 20 + l_pre];
         if (s < DSB_MIN_S_1 && l_pre == DSB_LV_L && !have_uni) { s = 0; break; }
         if (!have_uni) {
             while (b_p & DSB_SA_MASK) {
@@ -904,7 +908,7 @@ DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32
                         if (t_suf[mtc] != q_suf[mtc]) break;
                     if (mtc > 0) {
                         l_m += mtc;
-                        s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+                        s = Q_MEM[DSB_QMEM_IX(l_m)] + Q_LV[d_pre * 20 + l_pre];
                         l_max_suf -= mtc;
                         l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
                         q_suf += mtc;
@@ -954,7 +958,7 @@ DSB_HDN int32_t dsb_map_seed(DsbWork *w, DsbMem *m_r, const uint8_t *q_b, uint32
                     am_rigt_ED = (uint8_t)ed_r;
                     am_mtch = (uint16_t)(am_mtch + l_m_ext_r);
                 }
-                am_score = (int16_t)(Q_MEM[am_mtch] + Q_LV[am_left_ED * 20 + am_left_len] +
+                am_score = (int16_t)(Q_MEM[DSB_QMEM_IX(am_mtch)] + Q_LV[am_left_ED * 20 + am_left_len] +
                                      Q_LV[am_rigt_ED * 20 + am_rigt_len]);
                 if (am_score < DSB_MIN_S_2) continue;
             }
@@ -1586,6 +1590,20 @@ DSB_HD int dsb_read_hash_key_len(uint32_t L)
     return key_len;
 }
 
+// Bucket heads of the read's 9-mer table hold position + 1.  Reads shorter than 65 535 bases keep them in 16 bits (half
+// the heads' random-access footprint: classify stage 10.34 -> 10.07 ms in a same-box A/B, output identical); longer reads
+// use 32 bits in the same arena.  -DDSB_NO_HEAD16 keeps 32 bits throughout.  (Prefetching the heads one to three chunks
+// ahead while the table is built changed nothing: 10.32-10.41 ms.)
+#if !defined(DSB_NO_HEAD16) && defined(DSB_DEVICE_CODE)
+#define DSB_HEAD_GET(head, narrow, k) ((narrow) ? (uint32_t)((const uint16_t *)(head))[k] : (head)[k])
+#define DSB_HEAD_SET(head, narrow, k, v) do { if (narrow) ((uint16_t *)(head))[k] = (uint16_t)(v); else (head)[k] = (v); } while (0)
+#define DSB_HEAD_NARROW(L) ((L) < 65535u)
+#else
+#define DSB_HEAD_GET(head, narrow, k) ((head)[k])
+#define DSB_HEAD_SET(head, narrow, k, v) do { (head)[k] = (v); } while (0)
+#define DSB_HEAD_NARROW(L) false
+#endif
+
 DSB_HD uint32_t dsb_kmer9(const uint8_t *s)
 {
     uint32_t v = 0;
@@ -1612,7 +1630,9 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
 #if defined(DSB_DEVICE_CODE)
         const uint32_t lane = threadIdx.x & 31;
-        for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
+        const bool narrow = DSB_HEAD_NARROW(w->L);
+        if (narrow) { for (uint32_t i = lane; i <= (key_mask >> 1); i += 32) head[i] = 0; }
+        else for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
         __syncwarp();
         // Buckets must list positions in ascending order (the reference appends to the tail).  32
         // positions per step, from the highest chunk down: inside a chunk, lanes with the same key
@@ -1626,11 +1646,11 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
             const uint32_t peers = __match_any_sync(0xffffffffu, key);
             const uint32_t higher = peers & ~((2u << lane) - 1u);
             uint32_t nx = 0;
-            if (valid) nx = higher ? ((uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u) : head[key];
+            if (valid) nx = higher ? ((uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u) : DSB_HEAD_GET(head, narrow, key);
             __syncwarp();
             if (valid) {
                 ent[p] = (nx << 8) | (km >> key_len);
-                if ((peers & ((1u << lane) - 1u)) == 0) head[key] = p + 1;
+                if ((peers & ((1u << lane) - 1u)) == 0) DSB_HEAD_SET(head, narrow, key, p + 1);
             }
             __syncwarp();
         }
@@ -1734,6 +1754,8 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
     const uint32_t key_mask = (1u << key_len) - 1u;
     const uint32_t t_kmer_num = t_len - DSB_KMER9 + 1;
     const uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
+    const bool narrow = DSB_HEAD_NARROW(w->L);
+    (void)narrow;
     w->st.sdp_win++;
 #if defined(DSB_DEVICE_CODE)
     {
@@ -1750,7 +1772,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             uint32_t kmer = 0, node = 0;
             if (mine < n_i) {
                 kmer = dsb_kmer9(t_str + off_l);
-                node = head[kmer & key_mask];
+                node = DSB_HEAD_GET(head, narrow, kmer & key_mask);
                 while (node != 0) {
                     const uint32_t qp = node - 1;
                     const uint32_t e = ent[qp];

@@ -490,7 +490,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
         const int32_t d = dsb_lv_extd_ls(mask, t_pre, q_pre, alive ? (int32_t)l_pre : 0, DSB_LV_NO_BYTE);
         if (alive) {
             d_pre = (uint32_t)d;
-            s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+            s = Q_MEM[DSB_QMEM_IX(l_m)] + Q_LV[d_pre * 20 + l_pre];
             if (s < DSB_MIN_S_1 && l_pre == DSB_LV_L && !have_uni) { s = 0; alive = false; }
         }
     }
@@ -539,7 +539,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
                     if (t_suf[mtc] != q_suf[mtc]) break;
                 if (mtc > 0) {
                     l_m += mtc;
-                    s = Q_MEM[l_m] + Q_LV[d_pre * 20 + l_pre];
+                    s = Q_MEM[DSB_QMEM_IX(l_m)] + Q_LV[d_pre * 20 + l_pre];
                     l_max_suf -= mtc;
                     l_suf = DSB_MIN(l_max_suf, (uint32_t)DSB_LV_L);
                     q_suf += mtc;
@@ -640,7 +640,7 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
         }
         bool keep = a;
         if (do_l || do_r) {
-            am_score = (int16_t)(Q_MEM[am_mtch] + Q_LV[am_left_ED * 20 + am_left_len] + Q_LV[am_rigt_ED * 20 + am_rigt_len]);
+            am_score = (int16_t)(Q_MEM[DSB_QMEM_IX(am_mtch)] + Q_LV[am_left_ED * 20 + am_left_len] + Q_LV[am_rigt_ED * 20 + am_rigt_len]);
             if (am_score < DSB_MIN_S_2) keep = false;
         }
         // where the anchor goes: after the owner's earlier anchors and the kept pairs of this owner in lower lanes

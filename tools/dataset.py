@@ -52,6 +52,9 @@ for _L in (1000, 10000, 50000):
         CONFIGS["sw_L%d_e%d" % (_L, _e)] = dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
                                                 n_reads=max(40, 3000000 // _L), read_len=_L, err=_e / 100.0,
                                                 read_seed=100 + _L // 1000 + _e, junk=0.05, mix="3,3,4", jitter=0.3)
+# reads longer than 65 535 bases: the 32-bit form of the read's 9-mer table heads (dsb_core.cuh DSB_HEAD_NARROW)
+CONFIGS["sw_L80000_e10"] = dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
+                                n_reads=40, read_len=80000, err=0.10, read_seed=190, junk=0.05, mix="3,3,4", jitter=0.1)
 SWEEP = [k for k in CONFIGS if k.startswith("sw_")]
 
 
