@@ -14,6 +14,9 @@
 #include "dsb_host.h"
 #include <stdlib.h>
 #include <string.h>
+#include <pthread.h>
+#include <unistd.h>
+#include <sys/mman.h>
 
 #define NO_TID 0xFFFFFFFFu
 #define NAME_MAX_L 200
@@ -105,11 +108,12 @@ dsb_taxonomy *dsb_taxonomy_load(const char *dir)
 
 /* one SAM record as meta_analysis sees it (RST, src/cly_mt.h:55-63) */
 typedef struct rec {
-    char *name;
+    const char *name;
+    size_t name_l;
     char cls;                       /* 'C' classified, 'U' unclassified */
     uint32_t tid, read_length, score;
     uint8_t mapq;
-    char *seq;
+    const char *seq;
 } rec;
 
 /* getOneSAM: `line` is a private, writable, NUL-terminated copy of one record.  Returns 0, or -1 when the line
@@ -119,7 +123,7 @@ static int parse_record(char *line, rec *r)
     tokz z;
     char *cur = line, *t;
 #define FIELD() do { t = tok(&z, cur, "\t"); if (!t) return -1; cur += strlen(t) + 1; } while (0)
-    FIELD(); r->name = t;
+    FIELD(); r->name = t; r->name_l = strlen(t);
     FIELD();                                            /* FLAG */
     r->read_length = 0;
     r->score = 0;
@@ -162,6 +166,50 @@ static int parse_record(char *line, rec *r)
     return 0;
 }
 
+/* The same record WITHOUT writing into the text, for lines of the usual shape: at least eleven non-empty tab-separated
+ * fields in front of the line's '\n' (strtok merges empty fields, so those lines take the tokenising path above), RNAME
+ * either starting with '*' or of the form <no '|'>...|<digit>..., MAPQ starting with a digit.  For such a line
+ * parse_record yields exactly: name = field 1, tid = the number after RNAME's first '|', mapq = field 5 as uint8,
+ * seq = field 10, score = 0 (the AS tag is never read, see the header).  Returns 0 when the line is not of that shape. */
+static int parse_record_fast(const char *p, const char *nl, rec *r)
+{
+    const char *f[11];
+    size_t fl[11];
+    const char *c = p;
+    for (int k = 0; k < 11; k++) {
+        const char *t = (const char *)memchr(c, '\t', (size_t)(nl - c));
+        if (!t || t == c) return 0;
+        f[k] = c; fl[k] = (size_t)(t - c); c = t + 1;
+    }
+    r->name = f[0]; r->name_l = fl[0];
+    r->score = 0;
+    r->seq = f[9]; r->read_length = (uint32_t)fl[9];
+    if (fl[9] > 0xffffffffu) return 0;
+    if (f[2][0] == '*') {
+        r->cls = 'U'; r->tid = 0; r->mapq = 0;
+        return 1;
+    }
+    r->cls = 'C';
+    {   /* MAPQ: strtoul of a short digit string */
+        if (f[4][0] < '0' || f[4][0] > '9' || fl[4] > 9) return 0;
+        unsigned long v = 0;
+        for (size_t i = 0; i < fl[4] && f[4][i] >= '0' && f[4][i] <= '9'; i++) v = v * 10 + (unsigned long)(f[4][i] - '0');
+        r->mapq = (uint8_t)v;
+    }
+    {   /* "tid|<taxid>|...": strtok(ref, "|") then the token behind its NUL */
+        const char *ref = f[2], *re = f[2] + fl[2];
+        if (ref[0] == '|') return 0;
+        const char *bar = (const char *)memchr(ref, '|', fl[2]);
+        if (!bar || bar + 1 >= re || bar[1] < '0' || bar[1] > '9') return 0;
+        unsigned long v = 0;
+        size_t nd = 0;
+        for (const char *q = bar + 1; q < re && *q >= '0' && *q <= '9'; q++, nd++) v = v * 10 + (unsigned long)(*q - '0');
+        if (nd > 9) return 0;
+        r->tid = (uint32_t)v;
+    }
+    return 1;
+}
+
 /* ---- tally (meta_analysis_core) ------------------------------------------------------------- */
 typedef struct count_sort { uint32_t tid; long count; } count_sort;
 static int cmp_count_sort(const void *a_, const void *b_)
@@ -170,6 +218,22 @@ static int cmp_count_sort(const void *a_, const void *b_)
      * the same one the reference calls -- that is a stable descending sort */
     const count_sort *a = (const count_sort *)a_, *b = (const count_sort *)b_;
     return a->count < b->count;
+}
+
+/* zeroed tables over the whole taxonomy id range of which only a few entries are touched: anonymous mappings are
+ * zero pages until written (calloc may hand out recycled heap memory and clear all of it: 40 MB per call here) */
+static void *lazy_zeros(size_t bytes)
+{
+    void *p = mmap(NULL, bytes ? bytes : 1, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+    if (p == MAP_FAILED) dsb_fatal("meta_analysis: cannot map %zu bytes", bytes);
+    return p;
+}
+static void lazy_free(void *p, size_t bytes) { munmap(p, bytes ? bytes : 1); }
+
+static int cmp_u32(const void *a, const void *b)
+{
+    const uint32_t x = *(const uint32_t *)a, y = *(const uint32_t *)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
 }
 
 typedef struct node { uint64_t weight; uint32_t child_begin; } node;
@@ -223,7 +287,7 @@ static uint32_t read_tid(const dsb_taxonomy *tax, const rec *recs, size_t n, siz
         (*i)++;
         if (*i >= n) return tid;
         const rec *r = recs + *i;
-        if (strcmp(first->name, r->name) != 0) break;
+        if (first->name_l != r->name_l || memcmp(first->name, r->name, r->name_l) != 0) break;
         if (score == 0) break;                           /* always: see the header */
         if (r->score != score) continue;
         if (r->tid > tax->max_tid) continue;
@@ -243,6 +307,95 @@ static int cmp_meta_row(const void *a, const void *b)
     return x > y ? -1 : (x < y ? 1 : 0);
 }
 
+/* ---- threaded copy + tokenising of the SAM text ------------------------------------------------ */
+#define META_MAX_THREADS 16
+typedef struct parse_job {
+    const char *lo, *hi;                                 /* scan phase: bytes [lo, hi) */
+    const char *first_nul;
+    const char *beg, *end;                               /* parse phase: whole lines in [beg, end) */
+    rec *recs; size_t n_rec, m_rec;
+    dsb_strbuf human; uint64_t snap_cap;
+    char **priv; size_t n_priv, m_priv;                  /* private copies of the lines that had to be tokenised in place */
+    size_t n_slow;
+    int bad;
+} parse_job;
+
+static int meta_threads(uint64_t input_n)
+{
+    const char *e = getenv("DSB_META_THREADS");
+    long n = e && *e ? atol(e) : 0;
+    if (n <= 0) {
+        n = sysconf(_SC_NPROCESSORS_ONLN);
+        const char *w = getenv("LOCAL_WORLD_SIZE");
+        if (w && atol(w) > 1) n /= atol(w);
+    }
+    if (n > META_MAX_THREADS) n = META_MAX_THREADS;
+    if (n < 1 || input_n < ((uint64_t)4 << 20)) n = 1;
+    return (int)n;
+}
+
+static void run_jobs(pthread_t *th, parse_job *jobs, int n, void *(*fn)(void *))
+{
+    int started[META_MAX_THREADS] = {0};
+    for (int t = 1; t < n; t++) started[t] = pthread_create(&th[t], NULL, fn, &jobs[t]) == 0;
+    fn(&jobs[0]);
+    for (int t = 1; t < n; t++) {
+        if (started[t]) pthread_join(th[t], NULL);
+        else fn(&jobs[t]);
+    }
+}
+
+static void *scan_nul_worker(void *arg)
+{
+    parse_job *j = (parse_job *)arg;
+    j->first_nul = (const char *)memchr(j->lo, 0, (size_t)(j->hi - j->lo));
+    return NULL;
+}
+
+static void *parse_worker(void *arg)
+{
+    parse_job *j = (parse_job *)arg;
+    const char *p = j->beg, *end = j->end;
+    j->m_rec = 1024;
+    j->recs = (rec *)dsb_xmalloc(j->m_rec * sizeof(rec));
+    dsb_strbuf_reserve(&j->human, 1);
+    while (p < end) {
+        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
+        const char *next = nl ? nl + 1 : end;
+        rec r;
+        if (!(nl && parse_record_fast(p, nl, &r))) {
+            /* unusual line (or the text's last line without '\n'): the strtok-faithful parser, on a private NUL-terminated
+             * copy that lives as long as the records (getline keeps the '\n' in the buffer, so does the copy) */
+            const size_t n = (size_t)(next - p);
+            char *line = (char *)dsb_xmalloc(n + 1);
+            memcpy(line, p, n);
+            line[n] = 0;
+            if (j->n_priv == j->m_priv) { j->m_priv = j->m_priv ? 2 * j->m_priv : 16; j->priv = (char **)dsb_xrealloc(j->priv, j->m_priv * sizeof(char *)); }
+            j->priv[j->n_priv++] = line;
+            j->n_slow++;
+            if (parse_record(line, &r) != 0) { j->bad = 1; return NULL; }
+        }
+        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158) && j->human.l < j->snap_cap) {
+            /* only the first max_snapshot_len bases of the whole text are ever returned */
+            dsb_strbuf_reserve(&j->human, r.read_length);
+            memcpy(j->human.s + j->human.l, r.seq, r.read_length);
+            j->human.l += r.read_length;
+        }
+        if (j->n_rec == j->m_rec) { j->m_rec *= 2; j->recs = (rec *)dsb_xrealloc(j->recs, j->m_rec * sizeof(rec)); }
+        j->recs[j->n_rec++] = r;
+        p = next;
+    }
+    return NULL;
+}
+
+static void free_priv(parse_job *jobs)
+{
+    for (int k = 0; k < META_MAX_THREADS; k++) {
+        for (size_t i = 0; i < jobs[k].n_priv; i++) free(jobs[k].priv[i]);
+        free(jobs[k].priv);
+    }
+}
+
 void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
                             int flag, uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
 {
@@ -252,35 +405,70 @@ void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input
         return;
     }
     if (!tax) dsb_fatal("meta_analysis: the index directory has no nodes.dmp / names.dmp");
-    /* private, writable, NUL-terminated copy: records are tokenised in place */
-    char *text = (char *)dsb_xmalloc(input_n + 1);
-    memcpy(text, input, input_n);
-    text[input_n] = 0;
-    size_t n_rec = 0, m_rec = 1024;
-    rec *recs = (rec *)dsb_xmalloc(m_rec * sizeof(rec));
+    /* The text is read in place by several threads (contiguous pieces cut at line ends; records and human bases are
+     * joined in text order, so the result is that of one pass).  Lines of the usual shape are parsed without being
+     * modified (parse_record_fast); any other line is copied and tokenised by the strtok-faithful parse_record.  The first
+     * version copied the whole text and tokenised it on one thread: 165-210 ms for 104 MB of SAM_FULL, 9 x the
+     * classification that produced it. */
+    const int verbose = getenv("DSB_VERBOSE") != NULL;
+    const double t_0 = dsb_now();
+    int n_thr = meta_threads(input_n);
+    parse_job jobs[META_MAX_THREADS];
+    pthread_t th[META_MAX_THREADS];
+    memset(jobs, 0, sizeof jobs);
+    for (int t = 0; t < n_thr; t++) {
+        jobs[t].lo = input + (size_t)(input_n * (uint64_t)t / (uint64_t)n_thr);
+        jobs[t].hi = input + (size_t)(input_n * (uint64_t)(t + 1) / (uint64_t)n_thr);
+        jobs[t].snap_cap = max_snapshot_len;
+    }
+    run_jobs(th, jobs, n_thr, scan_nul_worker);
+    const double t_1 = dsb_now();
+    const char *end = input + input_n;                   /* like getline on a text file: stops at an embedded NUL */
+    for (int t = 0; t < n_thr; t++)
+        if (jobs[t].first_nul) { end = jobs[t].first_nul; break; }
+    const char *p = input;
+    while (p < end && *p == '@') {                       /* skip_sam_head: @SQ / @PG lines */
+        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
+        p = nl ? nl + 1 : end;
+    }
+    /* pieces of the body, each starting at a line start */
+    {
+        const size_t body = (size_t)(end - p);
+        if (body < ((size_t)1 << 20)) n_thr = 1;
+        const char *cut = p;
+        for (int t = 0; t < n_thr; t++) {
+            jobs[t].beg = cut;
+            const char *want = p + body * (size_t)(t + 1) / (size_t)n_thr;
+            if (t + 1 == n_thr || want >= end) cut = end;
+            else {
+                if (want < cut) want = cut;
+                const char *nl = (const char *)memchr(want, '\n', (size_t)(end - want));
+                cut = nl ? nl + 1 : end;
+            }
+            jobs[t].end = cut;
+        }
+    }
+    run_jobs(th, jobs, n_thr, parse_worker);
+    const double t_2 = dsb_now();
+    size_t n_rec = 0;
+    for (int t = 0; t < n_thr; t++) {
+        if (jobs[t].bad) dsb_fatal("meta_analysis: malformed SAM record (the reference crashes here)");
+        n_rec += jobs[t].n_rec;
+    }
+    rec *recs = (rec *)dsb_xmalloc((n_rec ? n_rec : 1) * sizeof(rec));
     dsb_strbuf human = {NULL, 0, 0};
     dsb_strbuf_reserve(&human, 1);
-    char *p = text, *end = text + strlen(text);          /* like getline on a text file: stops at an embedded NUL */
-    int in_header = 1;
-    while (p < end) {
-        char *nl = memchr(p, '\n', (size_t)(end - p));
-        char *next = nl ? nl + 1 : end;
-        if (in_header && *p == '@') { p = next; continue; }     /* skip_sam_head: @SQ / @PG lines */
-        in_header = 0;
-        /* getline keeps the '\n' in the buffer; it then ends up inside the last token, as in the reference */
-        char saved = *next;
-        *next = 0;
-        rec r;
-        if (parse_record(p, &r) != 0) dsb_fatal("meta_analysis: malformed SAM record (the reference crashes here)");
-        *next = saved;
-        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158)) {
-            dsb_strbuf_reserve(&human, r.read_length);
-            memcpy(human.s + human.l, r.seq, r.read_length);
-            human.l += r.read_length;
+    n_rec = 0;
+    for (int t = 0; t < n_thr; t++) {
+        memcpy(recs + n_rec, jobs[t].recs, jobs[t].n_rec * sizeof(rec));
+        n_rec += jobs[t].n_rec;
+        if (jobs[t].human.l) {
+            dsb_strbuf_reserve(&human, jobs[t].human.l);
+            memcpy(human.s + human.l, jobs[t].human.s, jobs[t].human.l);
+            human.l += jobs[t].human.l;
         }
-        if (n_rec == m_rec) { m_rec *= 2; recs = (rec *)dsb_xrealloc(recs, m_rec * sizeof(rec)); }
-        recs[n_rec++] = r;
-        p = next;
+        free(jobs[t].recs);
+        free(jobs[t].human.s);
     }
     if (n_rec == 0) {
         /* the reference returns with *output never assigned and then dereferences it; we return an empty answer */
@@ -288,31 +476,40 @@ void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input
         *output_n = 0;
         *human_snapshot = NULL;
         *human_snapshot_n = 0;
-        free(recs); free(text); free(human.s);
+        free(recs); free(human.s);
+        free_priv(jobs);
         return;
     }
     /* tally per taxon */
     const size_t n_tid = (size_t)tax->max_tid + 1;
-    uint64_t *node_count = (uint64_t *)dsb_xcalloc(n_tid, sizeof(uint64_t));
+    /* the tables span the taxonomy's whole id range (millions); calloc hands them out as untouched zero pages, so only
+     * the ids that occur are ever written or read: they are listed as they first appear instead of scanning the range */
+    uint64_t *node_count = (uint64_t *)lazy_zeros(n_tid * sizeof(uint64_t));
     uint64_t total_weight = 0;
+    size_t n_seen = 0, m_seen = 256;
+    uint32_t *seen = (uint32_t *)dsb_xmalloc(m_seen * sizeof(uint32_t));
     for (size_t i = 0; i < n_rec;) {
         const uint32_t w = ((flag & 0x1) == 0) ? 1u : recs[i].read_length;
         total_weight += w;
         const uint32_t tid = read_tid(tax, recs, n_rec, &i);
+        if (node_count[tid] == 0 && w != 0) {
+            if (n_seen == m_seen) { m_seen *= 2; seen = (uint32_t *)dsb_xrealloc(seen, m_seen * sizeof(uint32_t)); }
+            seen[n_seen++] = tid;
+        }
         node_count[tid] += w;
     }
+    qsort(seen, n_seen, sizeof(uint32_t), cmp_u32);       /* ascending id: the order the range scan produced (ties of the count sort) */
     size_t n_sort = 0;
-    for (size_t i = 0; i < n_tid; i++) n_sort += node_count[i] != 0;
-    count_sort *srt = (count_sort *)dsb_xmalloc((n_sort + 1) * sizeof(count_sort));
-    n_sort = 0;
-    for (size_t i = 0; i < n_tid; i++)
-        if (node_count[i]) { srt[n_sort].tid = (uint32_t)i; srt[n_sort++].count = (long)node_count[i]; }
+    count_sort *srt = (count_sort *)dsb_xmalloc((n_seen + 1) * sizeof(count_sort));
+    for (size_t i = 0; i < n_seen; i++)
+        if (node_count[seen[i]]) { srt[n_sort].tid = seen[i]; srt[n_sort++].count = (long)node_count[seen[i]]; }
+    free(seen);
     qsort(srt, n_sort, sizeof(count_sort), cmp_count_sort);
     /* propagate the weights to the ancestors, registering each child once, in order of first appearance */
     tally t;
     t.tax = tax;
-    t.tab = (node *)dsb_xcalloc(n_tid, sizeof(node));
-    t.kids = (child *)dsb_xcalloc(2 * n_tid + 2, sizeof(child));
+    t.tab = (node *)lazy_zeros(n_tid * sizeof(node));
+    t.kids = (child *)lazy_zeros((2 * n_tid + 2) * sizeof(child));
     t.total_weight = total_weight;
     uint32_t n_kids = 1;
     for (size_t i = 0; i < n_sort; i++) {
@@ -386,5 +583,15 @@ void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input
     }
     *output = res.s;                                      /* malloc'd, caller frees (desamba.h) */
     *output_n = res.l;
-    free(rows); free(lines.s); free(t.tab); free(t.kids); free(srt); free(node_count); free(recs); free(text); free(human.s);
+    const double t_3 = dsb_now();
+    free(rows); free(lines.s); free(srt); free(recs); free(human.s);
+    lazy_free(t.tab, n_tid * sizeof(node));
+    lazy_free(t.kids, (2 * n_tid + 2) * sizeof(child));
+    lazy_free(node_count, n_tid * sizeof(uint64_t));
+    size_t n_slow = 0;
+    for (int k = 0; k < META_MAX_THREADS; k++) n_slow += jobs[k].n_slow;
+    free_priv(jobs);
+    if (verbose)
+        fprintf(stderr, "[dsb] meta_analysis: %d threads, NUL scan %.1f ms, records %.1f ms, tally + report %.1f ms, free %.1f ms (%zu records, %zu through the tokenising parser)\n",
+                n_thr, 1e3 * (t_1 - t_0), 1e3 * (t_2 - t_1), 1e3 * (t_3 - t_2), 1e3 * (dsb_now() - t_3), n_rec, n_slow);
 }

@@ -170,6 +170,32 @@ def test_meta_analysis_equals_reference(tiny, mixed, have_ref_binary):
     header = b"@SQ\tSN:x\tLN:5\n@PG\tID:deSAMBA\n" + sam
     mixed_sam = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
     cases = [sam, full, human, unmapped, header, mixed_sam[: mixed_sam.rfind(b"\n", 0, 30000) + 1]]
+    # lines the non-modifying fast parser must hand to the strtok-faithful one (or parse to the same record): RNAME
+    # without '|' (the reference then takes POS for the taxid), signs and doubled / leading '|', MAPQ with a leading blank,
+    # RNAME ending right after the taxid, and a text whose last line has no newline
+    recs = [l for l in sam.split(b"\n") if l][:120]
+
+    def mutated(kind):
+        out = []
+        for i, l in enumerate(recs):
+            f = l.split(b"\t")
+            if f[2] != b"*" and i % 3 == 0:
+                if kind == 0:
+                    f[2] = b"chr1"
+                elif kind == 1:
+                    f[2] = f[2].replace(b"tid|", b"tid|+")
+                elif kind == 2:
+                    f[2] = f[2].replace(b"tid|", b"tid||")
+                elif kind == 3:
+                    f[2] = b"|" + f[2]
+                elif kind == 4:
+                    f[4] = b" 7"
+                elif kind == 5:
+                    f[2] = b"tid|1003"
+            out.append(b"\t".join(f))
+        return b"\n".join(out) + b"\n"
+    cases += [mutated(k) for k in range(6)] + [sam.rstrip(b"\n")]
+    cases.append(full * 3)              # > 4 MB: read by several threads (pieces cut at line ends, joined in order)
     d = pydsb.Desamba(hostsim=True)
     d.load_index(tiny["idx"])
     for flag in (0, 1):
