@@ -942,6 +942,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
     w.ix = &ix;
     dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
     w.warp_ctr = &s_job_ctr[threadIdx.x >> 5];
+    __syncwarp();
     for (;;) {
         uint32_t slot = 0;
         if (lane == 0) slot = atomicAdd(&ctrl->next_read, 1u);
