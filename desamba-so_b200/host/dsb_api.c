@@ -79,11 +79,15 @@ void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint
     dsb_out_opt o = {DSB_OUT_SAM_FULL, 5};          /* reference src/cly_mt.c:970-976 */
     dsb_strbuf out = {NULL, 0, 0};
     /* SAM_FULL repeats SEQ and QUAL of every read: about the size of the input plus the record fields */
-    if (input_n == (uint64_t)-1)
-        dsb_strbuf_reserve(&out, 1);
-    else {                                          /* exactly this much (dsb_strbuf_reserve would add half again) */
-        out.m = (size_t)(input_n + input_n / 16 + 4096);
-        out.s = (char *)dsb_xmalloc(out.m);
+    {
+        /* a path that names a plain file is mapped, so its size is known as well */
+        const uint64_t bytes = (input_n == (uint64_t)-1) ? dsb_fq_remaining_bytes(f) : input_n;
+        if (bytes == UINT64_MAX)
+            dsb_strbuf_reserve(&out, 1);
+        else {                                      /* exactly this much (dsb_strbuf_reserve would add half again) */
+            out.m = (size_t)(bytes + bytes / 16 + 4096);
+            out.s = (char *)dsb_xmalloc(out.m);
+        }
     }
 #ifdef MADV_HUGEPAGE
     if (out.m >= ((size_t)4 << 20)) {
