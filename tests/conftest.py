@@ -107,3 +107,16 @@ def fastq_slices(path, n_slices):
     n_rec = len(recs) // 4
     per = (n_rec + n_slices - 1) // n_slices
     return [b"\n".join(recs[4 * i:4 * min(i + per, n_rec)]) + b"\n" for i in range(0, n_rec, per)]
+
+
+def ref_cli(args):
+    """stdout of the UNMODIFIED reference binary (oracle/_ref/deSAMBA, the checker): `classify -t 1 <args>`."""
+    r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "deSAMBA"), "classify", "-t", "1"] + args, stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    return r.stdout
+
+
+# the classify command line's options and formats (reference src/cly_mt.c:431-499), as argument lists without index / reads
+CLI_VARIANTS = [["-f", "DES"], ["-f", "DES_FULL"], ["-f", "SAM_FULL"], ["-f", "SAM", "-r", "1"], ["-f", "DES", "-r", "0"],
+                ["-f", "SAM", "-s", "200"], ["-f", "SAM", "-l", "400"], ["-f", "SAM", "-l", "60", "-s", "20", "-r", "9"]]

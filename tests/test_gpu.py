@@ -246,3 +246,21 @@ def test_cfg1_demo_standin_against_reference(have_ref_binary):
     sam = d.read_classify(meta["reads"], thread_id=0, thread_num=1)
     text, snap = d.meta_analysis(sam, thread_id=0, flag=1, max_snapshot_len=65536)
     assert text and snap
+
+
+def test_cli_options_and_formats_equal_reference(mixed, have_ref_binary, tmp_path):
+    """Every output format and the -r / -s / -l options of `deSAMBA classify`, and -o FILE with two input files (the buffer
+    history carries from one file into the next): byte-identical to the reference binary run on the box."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import CLI_VARIANTS, ref_cli
+    for opts in CLI_VARIANTS:
+        want = ref_cli(opts + [mixed["idx"] + "/", mixed["reads"]])
+        r = subprocess.run([CLI, "classify", "-g", "1"] + opts + [mixed["idx"], mixed["reads"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert r.returncode == 0, r.stderr.decode()[-1500:]
+        assert r.stdout == want, opts
+    out = str(tmp_path / "o.sam")
+    r = subprocess.run([CLI, "classify", "-g", "1", "-o", out, mixed["idx"], mixed["reads"], mixed["reads"]], stdout=subprocess.PIPE,
+                       stderr=subprocess.PIPE)
+    assert r.returncode == 0 and r.stdout == b""
+    assert open(out, "rb").read() == ref_cli([mixed["idx"] + "/", mixed["reads"], mixed["reads"]])

@@ -343,3 +343,20 @@ def test_reblocked_fm_rank_equals_reference_occ_for_every_symbol(tiny):
     ix.close()
     assert (c_out == co).all() and (got == res).all()
     assert (co == 4).any()
+
+
+def test_cli_options_and_formats_equal_reference_hostsim(mixed, have_ref_binary, tmp_path):
+    """Every output format and the -r / -s / -l options of `deSAMBA classify` (reference src/cly_mt.c:431-499), and -o FILE:
+    byte-identical to the reference binary run here on the same input (host side + host simulator of the kernels)."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import CLI_VARIANTS, ref_cli
+    for opts in CLI_VARIANTS:
+        want = ref_cli(opts + [mixed["idx"] + "/", mixed["reads"]])
+        r = subprocess.run([SIM, "classify"] + opts + [mixed["idx"], mixed["reads"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert r.returncode == 0, r.stderr.decode()[-1500:]
+        assert r.stdout == want, opts
+    out = str(tmp_path / "o.sam")
+    r = subprocess.run([SIM, "classify", "-o", out, mixed["idx"], mixed["reads"], mixed["reads"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0 and r.stdout == b""
+    assert open(out, "rb").read() == ref_cli([mixed["idx"] + "/", mixed["reads"], mixed["reads"]])      # two files: the history carries over
