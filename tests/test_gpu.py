@@ -264,3 +264,14 @@ def test_cli_options_and_formats_equal_reference(mixed, have_ref_binary, tmp_pat
                        stderr=subprocess.PIPE)
     assert r.returncode == 0 and r.stdout == b""
     assert open(out, "rb").read() == ref_cli([mixed["idx"] + "/", mixed["reads"], mixed["reads"]])
+
+
+def test_concurrent_callers_with_distinct_thread_ids(tiny):
+    """Three caller threads with their own thread_ids on one resident index (reference contract: src/cly_mt.c:1279-1307):
+    each gets what a lone caller gets."""
+    from test_host import _concurrent_calls
+    res = _concurrent_calls("cuda", tiny)
+    want = sam_records(open(os.path.join(GOLD, "tiny.sam"), "rb").read())
+    for tid, (first, second) in res.items():
+        assert sam_records(first) == want, tid
+    assert len({second for _first, second in res.values()}) == 1

@@ -360,3 +360,32 @@ def test_cli_options_and_formats_equal_reference_hostsim(mixed, have_ref_binary,
     r = subprocess.run([SIM, "classify", "-o", out, mixed["idx"], mixed["reads"], mixed["reads"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert r.returncode == 0 and r.stdout == b""
     assert open(out, "rb").read() == ref_cli([mixed["idx"] + "/", mixed["reads"], mixed["reads"]])      # two files: the history carries over
+
+
+def _concurrent_calls(lib_kind, tiny, mixed_reads=None):
+    """two caller threads, distinct thread_ids, the same resident index (reference contract: src/cly_mt.c:1279-1307)"""
+    import threading
+    import pydsb
+    d = pydsb.Desamba(hostsim=(lib_kind == "hostsim"))
+    d.load_index(tiny["idx"])
+    text = open(tiny["reads"], "rb").read()
+    res = {}
+
+    def work(tid):
+        res[tid] = [d.read_classify(text, thread_id=tid, thread_num=1) for _ in range(2)]
+    th = [threading.Thread(target=work, args=(t,)) for t in (11, 12, 13)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    return res
+
+
+def test_concurrent_callers_with_distinct_thread_ids(tiny):
+    """Each thread_id owns its session (slots, history): three concurrent callers get what a lone caller gets -- the first
+    call equals the golden output, the second call (same reads again, history of the first) is the same for all three."""
+    res = _concurrent_calls("hostsim", tiny)
+    want = sam_records(open(os.path.join(GOLD, "tiny.sam"), "rb").read())
+    for tid, (first, second) in res.items():
+        assert sam_records(first) == want, tid
+    assert len({second for _first, second in res.values()}) == 1
