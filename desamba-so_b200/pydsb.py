@@ -237,8 +237,11 @@ class _SyntheticIndex(DeviceIndex):
             self.cuda.dsb_index_free(self.handle)
             self.handle = C.c_void_p()
 
+    def ek_bytes(self):
+        return self._ek_bytes
 
-def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3):
+
+def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3, ek_table=None):
     """A device index whose FM part is a random BWT of n_sym symbols in the reference's 168-byte block layout
     (counts are consistent inside a block, which is all a rank query reads).  Only dsb_fm_rank_batch is
     meaningful on it: it exists to measure rank-query throughput on a table far larger than L2."""
@@ -258,8 +261,10 @@ def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3):
     h.hash_index = keep["lut"].ctypes.data
     h.sa_taxon = keep["sa"].ctypes.data
     h.sa_n = 8
+    if ek_table is not None:                 # exist-k-mer tables of another size class (both tables = this array)
+        keep["ek"] = ek_table
     h.e_kmer0 = h.e_kmer1 = keep["ek"].ctypes.data
-    h.e_kmer_size = 0x8000000
+    h.e_kmer_size = len(keep["ek"])
     h.unitig = h.ref_pos = h.ref_seq_offset = h.ref_seq_len = keep["small"].ctypes.data
     h.n_unitig = h.n_ref_pos = h.n_ref = 8
     h.ref_bin = keep["small"].ctypes.data
@@ -270,4 +275,7 @@ def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3):
     rc = cuda.dsb_index_upload(C.byref(h), dev, C.byref(handle))
     if rc != 0:
         raise RuntimeError("dsb_index_upload: " + cuda.dsb_last_error().decode())
-    return _SyntheticIndex(handle, cuda, keep)
+    ix = _SyntheticIndex(handle, cuda, keep)
+    ix.host = C.CDLL(lib_path("libdesamba.so", hostsim))
+    ix._ek_bytes = len(keep["ek"])
+    return ix

@@ -275,3 +275,32 @@ def test_concurrent_callers_with_distinct_thread_ids(tiny):
     for tid, (first, second) in res.items():
         assert sam_records(first) == want, tid
     assert len({second for _first, second in res.values()}) == 1
+
+
+@pytest.mark.parametrize("table_bytes,k,bits", [(0x10000000, 17, 31), (0x40000000, 18, 33), (0x100000000, 19, 35)])
+def test_exist_kernel_on_larger_table_classes(api, built, table_bytes, k, bits):
+    """The exist-k-mer tables of larger indexes (reference src/idx.c:966-982: 256 MiB -> k 17 / 31-bit mask, 1 GiB -> k 18 /
+    33 bits, 4 GiB -> k 19 / 35 bits, i.e. bit offsets beyond 2^32): k_exist against the oracle's probe on a synthetic
+    table (random 64 MiB tile repeated; the real tables of such indexes cannot be built on the box)."""
+    import ctypes
+    orc = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "liboracle_port.so"))
+    orc.orc_exist_bits.restype = ctypes.c_int64
+    orc.orc_exist_bits.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
+                                   ctypes.c_void_p]
+    rng = np.random.default_rng(table_bytes & 0xffff)
+    tile = rng.integers(0, 256, size=1 << 26, dtype=np.uint8)
+    tile &= rng.integers(0, 256, size=1 << 26, dtype=np.uint8)          # a quarter of the bits set
+    table = np.tile(tile, table_bytes >> 26)
+    for j in range(0, table_bytes, 1 << 26):                             # make the tiles differ
+        table[j + (j >> 26) % 4096] ^= 0xff
+    ix = api.synthetic_fm_index(1 << 16, ek_table=table)
+    assert ix.ek_len() == k
+    codes = rng.integers(0, 4, size=300000, dtype=np.uint8)
+    codes[1000:1040] = 2                                                 # a low-complexity stretch
+    got, _ms = ix.exist(codes)
+    want = np.zeros(len(codes) - k + 1, dtype=np.uint8)
+    n = orc.orc_exist_bits(codes.ctypes.data, len(codes), k, table.ctypes.data, table.ctypes.data, (1 << bits) - 1, want.ctypes.data)
+    ix.close()
+    assert n == len(want)
+    assert (got == want).all()
+    assert 0.005 < want.mean() < 0.5
