@@ -304,3 +304,27 @@ def test_exist_kernel_on_larger_table_classes(api, built, table_bytes, k, bits):
     assert n == len(want)
     assert (got == want).all()
     assert 0.005 < want.mean() < 0.5
+
+
+def test_fm_rank_on_rows_beyond_2_to_32(api, built):
+    """A 4 Gbp index has more than 2^32 BWT rows: k_fm_reblock + k_fm_rank on a synthetic 2^33-symbol BWT (the reference's
+    168-byte block layout, random symbols) against the oracle's occ on the same blocks, rows drawn from the whole range."""
+    import ctypes
+    orc = ctypes.CDLL(os.path.join(ROOT, "oracle", "_ref", "liboracle_port.so"))
+    orc.orc_occ.restype = ctypes.c_uint64
+    orc.orc_occ.argtypes = [ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint8)]
+    n_sym = 1 << 33
+    ix = api.synthetic_fm_index(n_sym, seed=11)
+    rng = np.random.default_rng(12)
+    rows = np.concatenate([rng.integers(0, n_sym - 64, size=20000, dtype=np.uint64),
+                           rng.integers((1 << 32) - 300, (1 << 32) + 300, size=2000, dtype=np.uint64)])
+    c = rng.integers(0, 4, size=len(rows), dtype=np.uint8)
+    c[::7] = 0xff                                                        # "the symbol at this row"
+    got, c_out, _ms = ix.fm_rank(rows, c)
+    blocks = ix.keep["blocks"]
+    for i in range(len(rows)):
+        cc = ctypes.c_uint8(int(c[i]))
+        want = orc.orc_occ(blocks.ctypes.data, n_sym + 5, int(rows[i]), ctypes.byref(cc))
+        assert cc.value == int(c_out[i]) and want == int(got[i]), (i, int(rows[i]))
+    ix.close()
+    assert (rows > (1 << 32)).sum() > 5000
