@@ -797,7 +797,7 @@ static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_des
 }
 
 #ifndef DSB_MIN_BLOCKS
-#define DSB_MIN_BLOCKS 8          // 64 registers -> 32 resident warps per SM: the classifier is latency bound (96 -> 80 registers: 16.9 -> 14.6 ms; after the split 80 -> 64: classify stage 10.49 -> 10.28 ms, same box)
+#define DSB_MIN_BLOCKS 6          // 80 registers -> 24 resident warps per SM.  Same-box A/Bs (profiles/): as ONE 10 000-read launch 64 registers / 32 warps is 1.7 % faster (classify stage 10.08 vs 10.26 ms), but behind read_classify(), where three to five smaller batches overlap and a batch is about one read per warp, the faster 80-register code wins: 18.6-18.9 -> 17.8-18.2 ms per 50 Mbase call, 65.4-66.0 -> 61.9-62.2 ms per 198 Mbase call (56 registers / 7 blocks in between, 96 / 5 blocks slower in both)
 #endif
 
 // warp per read: the exist-k-mer islands of both strands, then the read's top islands as jobs of the batch-wide list
@@ -925,7 +925,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_SEED_MIN_BLOCKS) k_s
 
 // persistent: every warp pulls the next read of the (longest-first) order until none is left
 #ifndef DSB_MIN_BLOCKS
-#define DSB_MIN_BLOCKS 8          // 64 registers -> 32 resident warps per SM: the classifier is latency bound (96 -> 80 registers: 16.9 -> 14.6 ms; after the split 80 -> 64: classify stage 10.49 -> 10.28 ms, same box)
+#define DSB_MIN_BLOCKS 6          // 80 registers -> 24 resident warps per SM.  Same-box A/Bs (profiles/): as ONE 10 000-read launch 64 registers / 32 warps is 1.7 % faster (classify stage 10.08 vs 10.26 ms), but behind read_classify(), where three to five smaller batches overlap and a batch is about one read per warp, the faster 80-register code wins: 18.6-18.9 -> 17.8-18.2 ms per 50 Mbase call, 65.4-66.0 -> 61.9-62.2 ms per 198 Mbase call (56 registers / 7 blocks in between, 96 / 5 blocks slower in both)
 #endif
 __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classify(
     const __grid_constant__ DsbIndexView ix, const dsb_read_desc *__restrict__ desc, const uint32_t *__restrict__ order,
