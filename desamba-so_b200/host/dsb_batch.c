@@ -123,9 +123,10 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     e->batch_small = env_u64("DSB_BATCH_SMALL", (uint64_t)16 << 20);
     if (e->batch_small > e->batch_bases) e->batch_small = e->batch_bases;
     e->batch_reads = (uint32_t)env_u64("DSB_BATCH_READS", 65536);
-    /* short calls ramp up 4, 8, 16 Mbases (the device starts 1 ms earlier: 19.7 -> 19.3 ms on a 50 Mbase call, two rounds of
-     * tools/e2e_sweep.py); long inputs start with full batches */
-    e->batch_first = env_u64("DSB_BATCH_FIRST", (uint64_t)4 << 20);
+    /* short calls start with a half-size batch (8, 16, 16, ... Mbases): the device starts ~1 ms earlier.  Same-box sweeps
+     * (tools/e2e_sweep.py, 50 Mbase call): first batch 16 Mbases 17.8-18.5 ms, 8 Mbases 17.0-17.4, 4 Mbases ~17.8, 2 Mbases
+     * 18.1-18.5; long inputs start with full batches */
+    e->batch_first = env_u64("DSB_BATCH_FIRST", (uint64_t)8 << 20);
     if (e->batch_first > e->batch_bases || e->batch_first == 0) e->batch_first = e->batch_bases;
     e->batch_taper = (int)env_u64("DSB_BATCH_TAPER", 0);
     long ncpu = sysconf(_SC_NPROCESSORS_ONLN);
@@ -644,9 +645,8 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         /* the history borrows sequence pointers from the staging of earlier batches: before any
          * staging is overwritten it must own what it still needs */
         dsb_history_end_batch(s->hist);
-        /* Optional batch-size schedule (both off by default: a batch of any size costs the device one read's latency,
-         * 4-5 ms, so small batches lose more than their earlier start wins; profiles/): DSB_BATCH_FIRST starts small
-         * and doubles; DSB_BATCH_TAPER=1 halves towards the end when the amount of input left is known. */
+        /* Batch-size schedule of a short call: DSB_BATCH_FIRST (default: half a batch) doubles up to the call's batch
+         * size; DSB_BATCH_TAPER=1 (off: no gain measured) halves towards the end when the amount of input left is known. */
         uint64_t limit = (call_batch == s->e->batch_small) ? (s->e->batch_first << (b < 16 ? b : 16)) : call_batch;
         if (limit > call_batch || limit == 0) limit = call_batch;
         {
