@@ -435,7 +435,8 @@ def run_ours(args):
         "dtype": "u8/int64", "data": "synthetic",
         "config": {"workload": WORKLOAD_TEXT + " per GPU (tools/dataset.py)",
                    "n_reads_per_gpu": batch.n_reads, "n_bases_per_gpu": batch.n_bases, "parallelism": "reads sharded, index replicated, no collective",
-                   "l2": "inputs (50 MB ASCII + 200 MB derived) and index (0.9 GB) exceed the 126 MB L2; no flush needed",
+                   "l2": "inputs (%d MB ASCII + %d MB derived per step) and the index (>= 0.9 GB) exceed the 126 MB L2; no flush needed" %
+                         (batch.n_bases // 1000000, 4 * batch.n_bases // 1000000),
                    "wall_ms_per_step": 1e3 * wall / args.steps},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.h2d_bytes, "d2h_bytes_per_step": d2h,
                 "api": "read_classify() of libdesamba.so: FASTQ text -> SAM_FULL text (%d bytes)" % n_sam,
