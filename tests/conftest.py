@@ -120,3 +120,32 @@ def ref_cli(args):
 # the classify command line's options and formats (reference src/cly_mt.c:431-499), as argument lists without index / reads
 CLI_VARIANTS = [["-f", "DES"], ["-f", "DES_FULL"], ["-f", "SAM_FULL"], ["-f", "SAM", "-r", "1"], ["-f", "DES", "-r", "0"],
                 ["-f", "SAM", "-s", "200"], ["-f", "SAM", "-l", "400"], ["-f", "SAM", "-l", "60", "-s", "20", "-r", "9"]]
+
+
+def odd_base_reads(src_fastq, dst_fastq, seed=5):
+    """Reads with N runs, lower case, IUPAC / junk characters (all encode as 'C') and lengths around the 40-base
+    minimum (src/cly.c:3084), derived from an existing FASTQ."""
+    import random
+    rng = random.Random(seed)
+    lines = open(src_fastq).read().split("\n")
+    out = []
+    for i in range(0, len(lines) - 1, 4):
+        name, seq, plus, qual = lines[i:i + 4]
+        k = (i // 4) % 8
+        if k == 0:
+            s = list(seq)
+            for _ in range(3):
+                p = rng.randrange(0, max(1, len(s) - 30))
+                for j in range(p, min(len(s), p + rng.randrange(1, 30))):
+                    s[j] = "N"
+            seq = "".join(s)
+        elif k == 1:
+            seq = seq.lower()
+        elif k == 2:
+            seq = "".join(c if rng.random() > 0.02 else rng.choice("RYKMSWnx-") for c in seq)
+        elif k == 3:
+            seq = seq[:rng.choice([1, 10, 39, 40, 41, 60])]
+        elif k == 4:
+            seq = "".join(c.lower() if rng.random() < 0.5 else c for c in seq)
+        out += [name, seq, plus, qual[:len(seq)]]
+    open(dst_fastq, "w").write("\n".join(out) + "\n")

@@ -328,3 +328,14 @@ def test_fm_rank_on_rows_beyond_2_to_32(api, built):
         assert cc.value == int(c_out[i]) and want == int(got[i]), (i, int(rows[i]))
     ix.close()
     assert (rows > (1 << 32)).sum() > 5000
+
+
+def test_non_acgt_lower_case_and_short_reads_equal_reference(mixed, have_ref_binary, tmp_path):
+    """N runs, lower case, IUPAC codes, junk characters and reads of 1 .. 60 bases: byte-identical to the reference binary."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import odd_base_reads, ref_cli
+    fq = str(tmp_path / "odd.fq")
+    odd_base_reads(mixed["reads"], fq)
+    for fmt in ("SAM", "SAM_FULL"):
+        assert run_cli(mixed["idx"], fq, fmt=fmt) == ref_cli(["-f", fmt, mixed["idx"] + "/", fq])

@@ -389,3 +389,14 @@ def test_concurrent_callers_with_distinct_thread_ids(tiny):
     for tid, (first, second) in res.items():
         assert sam_records(first) == want, tid
     assert len({second for _first, second in res.values()}) == 1
+
+
+def test_non_acgt_lower_case_and_short_reads_equal_reference_hostsim(mixed, have_ref_binary, tmp_path):
+    """N runs, lower case, IUPAC codes, junk characters and reads of 1 .. 60 bases: byte-identical to the reference binary."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import odd_base_reads, ref_cli
+    fq = str(tmp_path / "odd.fq")
+    odd_base_reads(mixed["reads"], fq)
+    for fmt in ("SAM", "SAM_FULL"):
+        assert run_sim(mixed["idx"], [fq], fmt=fmt) == ref_cli(["-f", fmt, mixed["idx"] + "/", fq])
