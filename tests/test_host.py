@@ -400,3 +400,35 @@ def test_non_acgt_lower_case_and_short_reads_equal_reference_hostsim(mixed, have
     odd_base_reads(mixed["reads"], fq)
     for fmt in ("SAM", "SAM_FULL"):
         assert run_sim(mixed["idx"], [fq], fmt=fmt) == ref_cli(["-f", fmt, mixed["idx"] + "/", fq])
+
+
+def test_text_shapes_of_the_api_input_equal_reference_library(mixed, have_ref_binary):
+    """read_classify() on in-memory text of several shapes -- plain, with the trailing NUL callers pass (main_test_2.c:73),
+    without a final newline, CRLF line ends, multi-line FASTQ with comments, blank lines -- equals the reference library's
+    answer byte for byte.  FASTA is the one documented deviation: the reference gives every record slot its own kseq_t
+    (src/cly_mt.c:29-43), forgets the '>' it has already consumed and loses every second FASTA record; here all records
+    come out, and the ones the reference does return are identical."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdesamba.so")):
+        pytest.skip("reference library absent")
+    import pydsb
+    from conftest import ref_resident_session
+    lines = open(mixed["reads"], "rb").read().split(b"\n")
+    recs = [lines[i:i + 4] for i in range(0, len(lines) - 1, 4)][:60]
+    plain = b"".join(b"\n".join(r) + b"\n" for r in recs)
+
+    def wrap(s, n):
+        return b"\n".join(s[k:k + n] for k in range(0, len(s), n))
+    multi = b"".join(r[0] + b" extra words\n" + wrap(r[1], 61) + b"\n+\n" + wrap(r[3], 61) + b"\n" for r in recs)
+    fasta = b"".join(b">" + r[0][1:] + b"\n" + wrap(r[1], 70) + b"\n" for r in recs)
+    cases = [plain, plain + b"\0", plain.rstrip(b"\n"), plain.replace(b"\n", b"\r\n"), multi, plain.replace(b"\n@", b"\n\n@", 5)]
+    for text in cases:
+        want = ref_resident_session(mixed["idx"], [text], 1, 65536)[0][0]
+        d = pydsb.Desamba(hostsim=True)
+        d.load_index(mixed["idx"])
+        assert d.read_classify(text, thread_id=7) == want
+    want = sam_records(ref_resident_session(mixed["idx"], [fasta], 1, 65536)[0][0])
+    d = pydsb.Desamba(hostsim=True)
+    d.load_index(mixed["idx"])
+    got = sam_records(d.read_classify(fasta, thread_id=7))
+    assert len(got) == 60 and len(want) == 30
+    assert all(got[k] == v for k, v in want.items())
