@@ -32,6 +32,10 @@ struct dsb_fq {
     /* records found ahead of time by dsb_fq_prescan (memory mode) */
     dsb_rec_view *pre;
     size_t pre_n, pre_i;
+    /* the reference's read batches (read_reads, src/cly_mt.c:22-43: 5000 records or 10 Mbases), only as far as they decide
+     * what happens at a record kseq rejects: see dsb_fq_next_view */
+    uint64_t rb_count, rb_bases;
+    int rb_empty;
     /* pending record when the caller's buffer was too small */
     int have_pending;
     dsb_strbuf p_name, p_seq, p_qual;
@@ -294,16 +298,41 @@ static int fq_try_fast(dsb_fq *f, dsb_rec_view *v)
     return 1;
 }
 
+/* What the reference does at a record kseq_read rejects (-2: quality string of another length, or none): read_reads ends
+ * its batch there (`if (rst < 0) break;`, src/cly_mt.c:36-37), the records read so far are classified, and the next batch
+ * carries on BEHIND the rejected record.  If the batch was still empty (the rejected record is the first of a reference
+ * batch: the first record overall, the one after 5000 records or 10 Mbases, or the one right after another rejected
+ * record), step 0 of the pipeline reports "no reads" and THAT pipeline worker ends (src/cly_mt.c:367,
+ * src/lib/kthread.c:136-141); the other workers keep reading, so the run only ends with the third empty batch
+ * (PIPELINE_T_NUM = 3, src/cly_mt.c:461).  So: a rejected record is dropped and reading continues, until the third one
+ * that opens a batch. */
+#define REF_PIPELINE_WORKERS 3
+#define REF_BATCH_RECORDS 5000u
+#define REF_BATCH_BASES 10000000u
+static void ref_batch_note(dsb_fq *f, uint64_t seq_l)
+{
+    if (f->rb_count >= REF_BATCH_RECORDS || f->rb_bases >= REF_BATCH_BASES) f->rb_count = f->rb_bases = 0;
+    f->rb_count++;
+    f->rb_bases += seq_l;
+}
+
 int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v)
 {
     if (f->have_pending) {              /* a record fetched by dsb_fq_next() that did not fit its buffer */
         f->have_pending = 0;
     } else {
-        if (f->pre_i < f->pre_n) { *v = f->pre[f->pre_i++]; return (int64_t)v->seq_l; }
-        if (f->mem && fq_try_fast(f, v)) return (int64_t)v->seq_l;
-        f->p_ret = fq_read_record(f);
+        if (f->pre_i < f->pre_n) { *v = f->pre[f->pre_i++]; ref_batch_note(f, v->seq_l); return (int64_t)v->seq_l; }
+        if (f->mem && fq_try_fast(f, v)) { ref_batch_note(f, v->seq_l); return (int64_t)v->seq_l; }
+        for (;;) {
+            f->p_ret = fq_read_record(f);
+            if (f->p_ret != -2) break;
+            if (f->rb_count >= REF_BATCH_RECORDS || f->rb_bases >= REF_BATCH_BASES) f->rb_count = f->rb_bases = 0;
+            if (f->rb_count == 0 && ++f->rb_empty >= REF_PIPELINE_WORKERS) return -2;   /* the last pipeline worker ends */
+            f->rb_count = f->rb_bases = 0;              /* the batch ends; the next one starts behind the rejected record */
+        }
         if (f->p_ret < 0) return f->p_ret;
     }
+    ref_batch_note(f, f->p_seq.l);
     v->name = f->p_name.s; v->name_l = f->p_name.l;
     v->seq = f->p_seq.s; v->seq_l = f->p_seq.l;
     v->qual = f->p_is_fastq ? f->p_qual.s : NULL;

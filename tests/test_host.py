@@ -432,3 +432,33 @@ def test_text_shapes_of_the_api_input_equal_reference_library(mixed, have_ref_bi
     got = sam_records(d.read_classify(fasta, thread_id=7))
     assert len(got) == 60 and len(want) == 30
     assert all(got[k] == v for k, v in want.items())
+
+
+def test_rejected_fastq_records_follow_the_reference_pipeline(mixed, have_ref_binary):
+    """A record kseq rejects (quality string of another length) ends the reference's read batch; reading carries on behind
+    it, and only the third rejected record that OPENS a batch ends the run (one pipeline worker ends per empty batch,
+    src/cly_mt.c:29-43,367,461, src/lib/kthread.c:136-141).  Same output as the reference library for rejected records in
+    the middle, adjacent ones, at the start, and enough of them to end the run early."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdesamba.so")):
+        pytest.skip("reference library absent")
+    import pydsb
+    from conftest import ref_resident_session
+    lines = open(mixed["reads"], "rb").read().split(b"\n")
+    recs = [lines[i:i + 4] for i in range(0, len(lines) - 1, 4)][:30]
+
+    def text(bad, cut=()):
+        out = []
+        for i, r in enumerate(recs):
+            q = r[3] + b"II" if i in bad else (r[3][:40] if i in cut else r[3])
+            out.append(b"\n".join([r[0], r[1], r[2], q]) + b"\n")
+        return b"".join(out)
+    cases = [text({10}), text({10, 11}), text({0}), text({0, 1}), text({0, 1, 2}), text({10, 11, 12}), text({10, 11, 12, 13}),
+             text({0, 5, 6, 20, 21}), text((), cut={7}), text(()) + b"@x\nACGTACGT\n+\n"]
+    n_lines = []
+    for t in cases:
+        want = ref_resident_session(mixed["idx"], [t], 1, 65536)[0][0]
+        d = pydsb.Desamba(hostsim=True)
+        d.load_index(mixed["idx"])
+        assert d.read_classify(t, thread_id=7) == want
+        n_lines.append(want.count(b"\n"))
+    assert n_lines[4] == 0 and n_lines[6] < n_lines[5] < n_lines[0]      # the early ends really happened
