@@ -26,6 +26,7 @@ typedef struct api_index {
     pthread_mutex_t mu;
     int n_sessions, m_sessions;
     int *session_tid;
+    int *session_thread_num;        /* thread_num of the thread_id's last read_classify call */
     dsb_session **sessions;
 } api_index;
 
@@ -44,20 +45,31 @@ void load_index(void **idx, const char *dirPath)
     *idx = a;
 }
 
-static dsb_session *session_for(api_index *a, int thread_id)
+static dsb_session *session_for(api_index *a, int thread_id, int thread_num)
 {
     dsb_session *s = NULL;
     pthread_mutex_lock(&a->mu);
     for (int i = 0; i < a->n_sessions; i++)
-        if (a->session_tid[i] == thread_id) { s = a->sessions[i]; break; }
+        if (a->session_tid[i] == thread_id) {
+            s = a->sessions[i];
+            /* a different thread_num makes the reference throw the thread_id's buffers away and start afresh
+             * (src/cly_mt.c:1286-1295): the buffer history of earlier calls ends here */
+            if (thread_num != -1 && a->session_thread_num[i] != thread_num) {
+                dsb_session_reset_history(s);
+                a->session_thread_num[i] = thread_num;
+            }
+            break;
+        }
     if (!s) {
         if (a->n_sessions == a->m_sessions) {
             a->m_sessions = a->m_sessions ? a->m_sessions * 2 : 8;
             a->session_tid = (int *)dsb_xrealloc(a->session_tid, (size_t)a->m_sessions * sizeof(int));
+            a->session_thread_num = (int *)dsb_xrealloc(a->session_thread_num, (size_t)a->m_sessions * sizeof(int));
             a->sessions = (dsb_session **)dsb_xrealloc(a->sessions, (size_t)a->m_sessions * sizeof(dsb_session *));
         }
         s = dsb_session_create(a->engine);
         a->session_tid[a->n_sessions] = thread_id;
+        a->session_thread_num[a->n_sessions] = thread_num;
         a->sessions[a->n_sessions++] = s;
     }
     pthread_mutex_unlock(&a->mu);
@@ -74,7 +86,7 @@ void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint
     }
     api_index *a = (api_index *)idx;
     if (!a || a->magic != API_MAGIC) dsb_fatal("read_classify: bad index handle");
-    dsb_session *s = session_for(a, thread_id);
+    dsb_session *s = session_for(a, thread_id, thread_num);
     dsb_fq *f = (input_n == (uint64_t)-1) ? dsb_fq_open_path(input) : dsb_fq_open_mem(input, input_n);
     dsb_out_opt o = {DSB_OUT_SAM_FULL, 5};          /* reference src/cly_mt.c:970-976 */
     dsb_strbuf out = {NULL, 0, 0};

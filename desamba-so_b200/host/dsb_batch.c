@@ -242,6 +242,14 @@ dsb_session *dsb_session_create(dsb_engine *e)
     return s;
 }
 
+/* the reference rebuilds a thread_id's buffers when the caller changes thread_num (src/cly_mt.c:1286-1295): what earlier
+ * reads left in the worker buffer is gone, max_read_l starts again */
+void dsb_session_reset_history(dsb_session *s)
+{
+    dsb_history_free(s->hist);
+    s->hist = dsb_history_new();
+}
+
 void dsb_session_destroy(dsb_session *s)
 {
     if (!s) return;

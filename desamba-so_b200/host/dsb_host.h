@@ -117,6 +117,7 @@ int dsb_engine_n_gpu(const dsb_engine *e);
 typedef struct dsb_session dsb_session;   /* = one reference "worker buffer set" (a thread_id) */
 dsb_session *dsb_session_create(dsb_engine *e);
 void dsb_session_destroy(dsb_session *s);
+void dsb_session_reset_history(dsb_session *s);
 typedef void (*dsb_sink_fn)(void *ctx, const char *text, size_t n);
 typedef struct dsb_run_stats {
     uint64_t n_reads, n_bases, n_batches;

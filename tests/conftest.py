@@ -149,3 +149,28 @@ def odd_base_reads(src_fastq, dst_fastq, seed=5):
             seq = "".join(c.lower() if rng.random() < 0.5 else c for c in seq)
         out += [name, seq, plus, qual[:len(seq)]]
     open(dst_fastq, "w").write("\n".join(out) + "\n")
+
+
+def ref_call_sequence(idx_dir, calls):
+    """read_classify() of the UNMODIFIED reference library for a list of (fastq text, thread_id, thread_num) calls on one
+    load_index, in a child process; returns the SAM_FULL text of every call."""
+    code = r'''
+import ctypes as C, sys, pickle
+lib = C.CDLL(sys.argv[1]); idx = C.c_void_p(); lib.load_index(C.byref(idx), sys.argv[2].encode())
+lib.read_classify.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.c_int, C.c_int]
+res = []
+for fq, tid, tn in pickle.load(open(sys.argv[3], "rb")):
+    o, n = C.c_void_p(), C.c_uint64(0)
+    lib.read_classify(idx, fq, len(fq), C.byref(o), C.byref(n), tid, tn)
+    res.append(C.string_at(o.value, n.value))
+pickle.dump(res, open(sys.argv[4], "wb"))
+'''
+    import pickle
+    import sys
+    import tempfile
+    d = tempfile.mkdtemp()
+    pickle.dump(calls, open(os.path.join(d, "in.pkl"), "wb"))
+    r = subprocess.run([sys.executable, "-c", code, os.path.join(ROOT, "oracle", "_ref", "libdesamba.so"), idx_dir + "/",
+                        os.path.join(d, "in.pkl"), os.path.join(d, "out.pkl")], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    assert r.returncode == 0, r.stderr.decode()[-1500:]
+    return pickle.load(open(os.path.join(d, "out.pkl"), "rb"))

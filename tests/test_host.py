@@ -462,3 +462,22 @@ def test_rejected_fastq_records_follow_the_reference_pipeline(mixed, have_ref_bi
         assert d.read_classify(t, thread_id=7) == want
         n_lines.append(want.count(b"\n"))
     assert n_lines[4] == 0 and n_lines[6] < n_lines[5] < n_lines[0]      # the early ends really happened
+
+
+def test_thread_num_change_restarts_the_buffer_history(mixed, have_ref_binary):
+    """The reference throws a thread_id's buffers away when the caller changes thread_num (src/cly_mt.c:1286-1295), so the
+    buffer history of earlier calls ends there.  A call sequence that switches 1 -> 3 -> 1 on one thread_id: every
+    thread_num == 1 call (the reproducible ones) equals the reference library's answer, the one after the switch included."""
+    if not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libdesamba.so")):
+        pytest.skip("reference library absent")
+    import pydsb
+    from conftest import fastq_slices, ref_call_sequence
+    sl = fastq_slices(mixed["reads"], 5)
+    calls = [(sl[0], 7, 1), (sl[1], 7, 1), (sl[2], 7, 3), (sl[3], 7, 1), (sl[4], 7, 1), (sl[1], 7, 1)]
+    want = ref_call_sequence(mixed["idx"], calls)
+    d = pydsb.Desamba(hostsim=True)
+    d.load_index(mixed["idx"])
+    for i, (fq, tid, tn) in enumerate(calls):
+        got = d.read_classify(fq, thread_id=tid, thread_num=tn)
+        if tn == 1:
+            assert got == want[i], i
