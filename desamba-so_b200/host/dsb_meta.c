@@ -375,8 +375,10 @@ static void *parse_worker(void *arg)
             j->n_slow++;
             if (parse_record(line, &r) != 0) { j->bad = 1; return NULL; }
         }
-        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158) && j->human.l < j->snap_cap) {
-            /* only the first max_snapshot_len bases of the whole text are ever returned */
+        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158) &&
+            (j->human.l < j->snap_cap || j->human.l == 0)) {
+            /* only the first max_snapshot_len bases of the whole text are ever returned (but "some human bases" must stay
+             * distinguishable from "none": with max_snapshot_len 0 the reference returns an empty block, not NULL) */
             dsb_strbuf_reserve(&j->human, r.read_length);
             memcpy(j->human.s + j->human.l, r.seq, r.read_length);
             j->human.l += r.read_length;

@@ -199,7 +199,7 @@ def test_meta_analysis_equals_reference(tiny, mixed, have_ref_binary):
     d = pydsb.Desamba(hostsim=True)
     d.load_index(tiny["idx"])
     for flag in (0, 1):
-        for snap in (65536, 1000):
+        for snap in (65536, 1000, 0):          # 0: some human bases -> an empty block, not NULL
             want = _ref_meta(tiny["idx"], cases, flag, snap)
             for s, (w_text, w_snap) in zip(cases, want):
                 got_text, got_snap = d.meta_analysis(s, thread_id=0, flag=flag, max_snapshot_len=snap)
