@@ -1,7 +1,8 @@
-/* dsb_main.c -- `deSAMBA classify` command line, flag-compatible with the reference
- * (reference src/main.c:35-53 dispatcher, src/cly_mt.c:431-562 classify_main / usage).
- * Only `classify` is implemented here: index building, kmersort and the analysis tools are
- * outside the hot path and remain the reference binary's job.
+/* dsb_main.c -- `deSAMBA classify` and `deSAMBA index` command lines, flag-compatible with the reference
+ * (reference src/main.c:35-53 dispatcher, src/cly_mt.c:431-562 classify_main / usage, src/idx.c:1239-1282
+ * build_index_main).  `index` runs on the GPU and needs no Jellyfish / kmersort step: the 31-mer set is derived from the
+ * FASTA itself; a kmer.srt given in the reference's argument position is checked against it.
+ * The analysis tools are outside the hot path and remain the reference binary's job.
  */
 #include "dsb_host.h"
 #include <getopt.h>
@@ -93,11 +94,50 @@ static int classify_main(int argc, char *argv[])
     return 0;
 }
 
+static int index_usage(void)
+{
+    fprintf(stderr, "\nProgram:   deSAMBA (B200 build)\n");
+    fprintf(stderr, "  Usage:     deSAMBA  index  [Options] [SortedKmer] <Reference> <IndexDir>\n");
+    fprintf(stderr, "  Basic:     \n");
+    fprintf(stderr, "    [SortedKmer]  FILE   optional: \"kmer.srt\" of the reference's kmersort; checked against the FASTA's own 31-mers\n");
+    fprintf(stderr, "    <Reference>   FILE   one fasta REF file (plain or gzip), multiple files need to be combined\n");
+    fprintf(stderr, "    <IndexDir>    FOLDER the directory to store deSAMBA index\n");
+    fprintf(stderr, "  Options:\n    -h            help\n    -g INT        GPU to build on [0]\n\n");
+    return 0;
+}
+
+/* reference src/idx.c:1255-1282: `index [SortedKmer] [Reference] [IndexDir]` */
+static int index_main(int argc, char *argv[])
+{
+    int c, dev = 0;
+    while ((c = getopt(argc, argv, "k:hg:")) >= 0) {
+        if (c == 'h') return index_usage();
+        else if (c == 'g') dev = atoi(optarg);
+    }
+    if (optind + 2 > argc) {
+        fprintf(stderr, "Warning: [Reference] or [IndexDir] missed.\n");
+        return index_usage();
+    }
+    const char *kmer = NULL;
+    if (optind + 3 <= argc) kmer = argv[optind++];
+    const char *ref = argv[optind++], *dir = argv[optind++];
+    dsb_build_stats st;
+    if (dsb_index_build(ref, kmer, dir, dev, &st) != 0) dsb_fatal("index: %s", dsb_build_last_error());
+    fprintf(stderr, "index built in %.2fs: %llu references, %llu bases, %llu distinct 31-mers, %llu unitigs, %llu BWT rows, "
+            "exist k = %d (2 x %llu MiB); %d kernel launches, %.2f GB peak on the device\n", st.seconds,
+            (unsigned long long)st.n_ref, (unsigned long long)st.n_bases, (unsigned long long)st.n_kmer,
+            (unsigned long long)st.n_unitig, (unsigned long long)st.n_rows, st.exist_k,
+            (unsigned long long)(st.exist_table_bytes >> 20), st.kernel_launches, st.peak_device_bytes / 1e9);
+    for (int i = 0; i < st.n_phases; i++) fprintf(stderr, "  %-34s %8.3f s\n", st.phase_name[i], st.phase_s[i]);
+    return 0;
+}
+
 static int usage(void)
 {
     fprintf(stderr, "\nProgram: deSAMBA (B200 build)\n\n  Usage  : deSAMBA <command> \n  Command: \n");
     fprintf(stderr, "		classify:	classify meta-genomic reads (runs on the GPUs)\n");
-    fprintf(stderr, "		index | kmersort | analysis: not part of the B200 hot path; use the reference binary\n\n");
+    fprintf(stderr, "		index:		build the index from a FASTA (runs on the GPU; no kmersort step needed)\n");
+    fprintf(stderr, "		analysis:	not part of the B200 hot path; use the reference binary\n\n");
     return 1;
 }
 
@@ -105,5 +145,6 @@ int main(int argc, char *argv[])
 {
     if (argc <= 1) return usage();
     if (strcmp(argv[1], "classify") == 0) return classify_main(argc - 1, argv + 1);
+    if (strcmp(argv[1], "index") == 0) return index_main(argc - 1, argv + 1);
     return usage();
 }

@@ -153,6 +153,33 @@ int  dsb_random_access_probe(int dev, uint64_t table_bytes, uint32_t chunk_bytes
  * k-mer start of codes[0..n), same rule as k_exist.  Host pointers. */
 int  dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist, int repeat, float *ms);
 
+/* ---- index build --------------------------------------------------------------- */
+
+#define DSB_BUILD_MAX_PHASES 32
+typedef struct dsb_build_stats {
+    uint64_t n_ref, n_bases;         /* reference sequences, bases */
+    uint64_t n_kmer;                 /* distinct 31-mers (what kmer.srt holds, reference src/idx_sort.c:196-200) */
+    uint64_t n_unitig;               /* unitigs, without the sentinel */
+    uint64_t n_rows;                 /* BWT rows = bases of unitig text incl. terminators */
+    uint64_t n_ref_pos;              /* REF_POS entries */
+    uint64_t exist_table_bytes;      /* bytes of each of the two exist-k-mer tables */
+    int32_t  exist_k;
+    int32_t  kernel_launches;
+    uint64_t peak_device_bytes;
+    double   seconds;
+    int32_t  n_phases;
+    char     phase_name[DSB_BUILD_MAX_PHASES][40];
+    double   phase_s[DSB_BUILD_MAX_PHASES];
+} dsb_build_stats;
+
+/* `deSAMBA index` on device `dev`: reference FASTA (plain or gzip) -> the ten deSAMBA.* files in out_dir, byte for byte
+ * what the reference builder writes (reference src/idx.c:1255-1282 build_index_main and everything below it; the
+ * unspecified bytes -- heap garbage after each reference name in .ref_i -- are zero).  kmer_srt may be NULL: the 31-mer
+ * set is derived from the FASTA on the device; when given, it must be that same set (reference src/idx_sort.c:196-200).
+ * Returns 0, or -1 with dsb_build_last_error(). */
+int dsb_index_build(const char *ref_fasta, const char *kmer_srt, const char *out_dir, int dev, dsb_build_stats *stats);
+const char *dsb_build_last_error(void);
+
 const char *dsb_last_error(void);
 int  dsb_kernel_launch_count(void);   /* kernels launched by this library so far */
 
