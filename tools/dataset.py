@@ -46,9 +46,25 @@ CONFIGS = {
 }
 
 
-# BASELINE.json configs[3] (read-length / error sweep) at test scale, on the cfg2 genomes: ~3 Mbp per cell
-for _L in (1000, 10000, 50000):
-    for _e in (5, 20):
+# BASELINE.json configs[2] at the size this box builds in seconds with OUR index builder (`deSAMBA index` on the
+# GPU, byte-identical to the reference builder on tiny / cfg2): 1 Gbp = 200 families x 5 strains x 1 Mbp
+# (BWT ~0.95 G rows, exist tables 2 x 256 MiB, k = 17) and 100 000 ONT-like 10 kb reads (1 Gbase) per read set;
+# the reference's own `-t 1` answer (the golden) is computed for the first `golden_reads` reads.
+CONFIGS["cfg3"] = dict(families=200, strains=5, length=1000000, snp=0.01, ref_seed=44, human_first=False,
+                       n_reads=100000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5,
+                       builder="gpu", sim="c", golden_reads=20000)
+# configs[2] at its full index size: 4 Gbp = 800 x 5 x 1 Mbp (BWT ~3.8 G rows, exist tables 2 x 1 GiB, k = 18)
+CONFIGS["cfg3x"] = dict(families=800, strains=5, length=1000000, snp=0.01, ref_seed=44, human_first=False,
+                        n_reads=100000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5,
+                        builder="gpu", sim="c", golden_reads=10000)
+# small twin of cfg3 for CPU-side checks of the tooling (reference builder, C simulator)
+CONFIGS["cfg3t"] = dict(families=4, strains=3, length=80000, snp=0.01, ref_seed=7, human_first=False,
+                        n_reads=300, read_len=4000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5,
+                        sim="c", golden_reads=200)
+
+# BASELINE.json configs[3] (read-length / error sweep) at test scale, on the cfg2 genomes: ~3 Mbp per cell, all 24 cells
+for _L in (1000, 2000, 5000, 10000, 20000, 50000):
+    for _e in (5, 10, 15, 20):
         CONFIGS["sw_L%d_e%d" % (_L, _e)] = dict(families=10, strains=5, length=1000000, snp=0.01, ref_seed=42, human_first=False,
                                                 n_reads=max(40, 3000000 // _L), read_len=_L, err=_e / 100.0,
                                                 read_seed=100 + _L // 1000 + _e, junk=0.05, mix="3,3,4", jitter=0.3)
@@ -71,27 +87,81 @@ def run(cmd, **kw):
     return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, **kw)
 
 
+OUR_BIN = os.path.join(ROOT, "desamba-so_b200", "bin", "deSAMBA")
+
+
+class _Lock:
+    """Cross-process lock on a data directory (the ranks of one bench run share /tmp/dsb_data)."""
+
+    def __init__(self, path):
+        self.path = path
+
+    def __enter__(self):
+        import fcntl
+        os.makedirs(os.path.dirname(self.path), exist_ok=True)
+        self.fh = open(self.path, "w")
+        fcntl.flock(self.fh, fcntl.LOCK_EX)
+
+    def __exit__(self, *a):
+        import fcntl
+        fcntl.flock(self.fh, fcntl.LOCK_UN)
+        self.fh.close()
+
+
 def build_index(p, log=sys.stderr):
-    """Reference FASTA + index directory shared by every read set on the same genomes."""
+    """Reference FASTA + index directory shared by every read set on the same genomes.
+
+    builder "ref" (default): the UNMODIFIED reference binary (`deSAMBA index` of oracle/_ref) from a kmer.srt written
+    here; builder "gpu": this repository's own `deSAMBA index` (GPU; byte-identical to the reference builder where both
+    run, tests/test_gpu.py::test_index_builder_equals_reference) -- the only one that finishes a >= 1 Gbp index in
+    minutes.  DSB_INDEX_BUILDER=hostsim (local experiments without a GPU) runs the builder's host twin instead."""
     d = os.path.join(data_root(), ref_key(p))
     idx = os.path.join(d, "idx")
-    if os.path.exists(os.path.join(d, "index.ok")):
-        return d, idx
-    if not os.path.exists(REF_BIN):
-        raise RuntimeError("oracle/_ref/deSAMBA is missing: run `make -C oracle ref` where /root/reference exists")
-    os.makedirs(idx, exist_ok=True)
-    t0 = time.time()
-    g = synth.make_genomes(p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"])
-    synth.write_fasta(os.path.join(d, "ref.fa"), g, p["human_first"])
-    synth.write_kmer_srt(os.path.join(d, "kmer.srt"), g)
-    synth.write_taxonomy(idx, g, p["strains"], p["human_first"])
-    r = run([REF_BIN, "index", "kmer.srt", "ref.fa", "idx"], cwd=d)
-    if r.returncode != 0 or not os.path.exists(os.path.join(idx, "deSAMBA.bwt")):
-        raise RuntimeError("reference index build failed:\n" + r.stderr.decode()[-2000:])
-    os.remove(os.path.join(d, "kmer.srt"))
-    open(os.path.join(d, "index.ok"), "w").write("ok\n")
-    print("[dataset] index %s built in %.1fs" % (ref_key(p), time.time() - t0), file=log)
+    with _Lock(os.path.join(data_root(), ref_key(p) + ".lock")):
+        if os.path.exists(os.path.join(d, "index.ok")):
+            return d, idx
+        os.makedirs(idx, exist_ok=True)
+        t0 = time.time()
+        g = synth.make_genomes(p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"])
+        synth.write_fasta(os.path.join(d, "ref.fa"), g, p["human_first"])
+        synth.write_taxonomy(idx, g, p["strains"], p["human_first"])
+        t1 = time.time()
+        builder = p.get("builder", "ref")
+        if builder == "gpu":
+            del g
+            exe = OUR_BIN
+            if os.environ.get("DSB_INDEX_BUILDER") == "hostsim":
+                exe = os.path.join(ROOT, "tests", "hostsim", "deSAMBA_hostsim")
+            r = run([exe, "index", "ref.fa", "idx"], cwd=d)
+            if r.returncode != 0 or not os.path.exists(os.path.join(idx, "deSAMBA.bwt")):
+                raise RuntimeError("index build failed:\n" + r.stderr.decode()[-2000:])
+            open(os.path.join(d, "build.log"), "wb").write(r.stderr)
+        else:
+            if not os.path.exists(REF_BIN):
+                raise RuntimeError("oracle/_ref/deSAMBA is missing: run `make -C oracle ref` where /root/reference exists")
+            synth.write_kmer_srt(os.path.join(d, "kmer.srt"), g)
+            r = run([REF_BIN, "index", "kmer.srt", "ref.fa", "idx"], cwd=d)
+            if r.returncode != 0 or not os.path.exists(os.path.join(idx, "deSAMBA.bwt")):
+                raise RuntimeError("reference index build failed:\n" + r.stderr.decode()[-2000:])
+            os.remove(os.path.join(d, "kmer.srt"))
+        open(os.path.join(d, "index.ok"), "w").write("ok\n")
+        print("[dataset] index %s: genomes + FASTA %.1fs, %s builder %.1fs" % (ref_key(p), t1 - t0, builder, time.time() - t1),
+              file=log)
     return d, idx
+
+
+def readsim_exe():
+    """tools/readsim.c compiled on first use (gcc is on both machines)."""
+    exe = os.path.join(data_root(), "readsim")
+    src = os.path.join(HERE, "readsim.c")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+        os.makedirs(data_root(), exist_ok=True)
+        tmp = exe + ".%d" % os.getpid()
+        r = run(["gcc", "-O2", "-fopenmp", "-o", tmp, src])
+        if r.returncode != 0:
+            raise RuntimeError("readsim build failed:\n" + r.stderr.decode())
+        os.replace(tmp, exe)
+    return exe
 
 
 def read_fastq_records(path):
@@ -147,6 +217,8 @@ def build(name, log=sys.stderr, golden=True):
             return meta
     os.makedirs(d, exist_ok=True)
     t0 = time.time()
+    if p.get("sim") == "c":
+        return _build_large(name, p, rd, idx, d, golden, log)
     g = synth.make_genomes(p["families"], p["strains"], p["length"], p["snp"], p["ref_seed"])
     w = [float(x) for x in p["mix"].split(",")]
     raw = os.path.join(d, "raw.fq")
@@ -189,6 +261,48 @@ def build(name, log=sys.stderr, golden=True):
     return meta
 
 
+def _build_large(name, p, rd, idx, d, golden, log):
+    """Read sets of the C simulator: `reads` = the whole set (bench), `parity_reads` = its first golden_reads reads (what
+    the reference is run on: golden, twins, and the reference arm of bench.py).  Reads the reference crashes on are
+    dropped from the parity subset only."""
+    t0 = time.time()
+    exe = readsim_exe()
+    fq = os.path.join(d, "reads.fq")
+    args = [str(p["read_len"]), str(p["err"]), str(p["read_seed"]), str(p["junk"]), p["mix"], str(p["jitter"]), "r"]
+    r = run([exe, os.path.join(rd, "ref.fa"), fq, str(p["n_reads"])] + args)
+    if r.returncode != 0:
+        raise RuntimeError("readsim failed: " + r.stderr.decode())
+    n_bases = int(r.stdout.decode().split("bases=")[1])
+    meta = dict(name=name, dir=d, idx=idx, reads=fq, golden=None, n_reads=p["n_reads"], n_bases=n_bases, dropped=0)
+    if golden:
+        ng = min(p.get("golden_reads", p["n_reads"]), p["n_reads"])
+        raw = os.path.join(d, "parity_raw.fq")
+        r = run([exe, os.path.join(rd, "ref.fa"), raw, str(ng)] + args)   # per-read seeding: the first ng reads of the set
+        if r.returncode != 0:
+            raise RuntimeError("readsim failed: " + r.stderr.decode())
+        recs = read_fastq_records(raw)
+        pfq, sam = os.path.join(d, "parity.fq"), os.path.join(d, "golden.sam")
+        dropped = []
+        for _ in range(4):
+            keep = [x for i, x in enumerate(recs) if i not in set(dropped)]
+            with open(pfq, "wb") as fh:
+                fh.write(b"".join(keep))
+            if ref_classify(idx, pfq, sam) == 0:
+                break
+            print("[dataset] %s: reference crashed, bisecting" % name, file=log)
+            live = [i for i in range(len(recs)) if i not in set(dropped)]
+            dropped += [live[j] for j in find_crashers(idx, [recs[i] for i in live], os.path.join(d, "bisect.fq"))]
+        else:
+            raise RuntimeError("reference keeps crashing on " + name)
+        os.remove(raw)
+        meta.update(parity_reads=pfq, golden=sam, n_parity_reads=len(recs) - len(dropped),
+                    n_parity_bases=sum(len(x.split(b"\n")[1]) for i, x in enumerate(recs) if i not in set(dropped)),
+                    dropped=len(dropped), golden_md5=hashlib.md5(open(sam, "rb").read()).hexdigest())
+    json.dump(meta, open(os.path.join(d, "meta.json"), "w"))
+    print("[dataset] %s: %d reads, %d bases, %.1fs" % (name, meta["n_reads"], n_bases, time.time() - t0), file=log)
+    return meta
+
+
 TWINS = ("deSAMBA_zinit", "deSAMBA_pinit", "deSAMBA_o1")
 
 
@@ -203,31 +317,78 @@ def _records_by_read(path):
 def undefined_reads(meta, log=sys.stderr):
     """Names of the reads whose REFERENCE answer is not defined by the reference's source: any instrumented
     build of the unmodified sources (oracle/Makefile `twins`: zero- / pattern-initialised automatic variables,
-    -O1 frame layout) classifies them differently from the stock -O3 binary at -t 1.  Cached per data set."""
+    -O1 frame layout) classifies them differently from the stock -O3 binary at -t 1.  Cached per data set.
+
+    A twin that crashes gives no verdict on the reads it did not reach (they are NOT counted as undefined); the read it
+    stopped at is undefined (a build of the same sources crashing on it is undefined behaviour by definition).  The
+    per-twin counts and crashes are kept in <dir>/undefined.json; the twins' own answers stay in <dir>/<twin>.sam so
+    that tests can require our answer on an undefined read to be ONE of the reference builds' answers."""
     path = os.path.join(meta["dir"], "undefined.txt")
-    if os.path.exists(path):
+    if os.path.exists(path) and os.path.exists(os.path.join(meta["dir"], "undefined.json")):
         return set(open(path).read().split())
+    reads = meta.get("parity_reads") or meta["reads"]
     stock = _records_by_read(meta["golden"])
+    order = []
+    for line in open(meta["golden"], "rb"):
+        k = line.split(b"\t", 1)[0]
+        if not order or order[-1] != k:
+            order.append(k)
     bad = set()
+    info = {"n_reads": len(order), "twins": {}}
+    procs = []
+    t0 = time.time()
     for tw in TWINS:
         b = os.path.join(ROOT, "oracle", "_ref", tw)
         if not os.path.exists(b):
             raise RuntimeError("%s is missing: run `make -C oracle twins` where /root/reference exists" % b)
         out = os.path.join(meta["dir"], tw + ".sam")
-        t0 = time.time()
-        with open(out, "wb") as fo:
-            r = subprocess.run([b, "classify", "-t", "1", "-f", "SAM", meta["idx"] + "/", meta["reads"]], stdout=fo,
-                               stderr=subprocess.PIPE)
-        if r.returncode != 0:
-            print("[dataset] twin %s crashed on %s (rc %d): every read it did not reach counts as undefined" %
-                  (tw, meta["name"], r.returncode), file=log)
+        fo = open(out, "wb")
+        procs.append((tw, out, fo, subprocess.Popen([b, "classify", "-t", "1", "-f", "SAM", meta["idx"] + "/", reads],
+                                                    stdout=fo, stderr=subprocess.DEVNULL)))
+    for tw, out, fo, pr in procs:
+        rc = pr.wait()
+        fo.close()
         other = _records_by_read(out)
-        d = {k.decode() for k in stock if other.get(k) != stock[k]}
-        print("[dataset] %s vs stock on %s: %d reads differ, %.1fs" % (tw, meta["name"], len(d), time.time() - t0), file=log)
+        reached = [k for k in order if k in other]
+        d = {k.decode() for k in reached if other[k] != stock[k]}
+        ti = {"rc": rc, "reached": len(reached), "differ": len(d)}
+        if rc != 0 or len(reached) < len(order):
+            nxt = next((k for k in order if k not in other), None)
+            if nxt is not None:
+                d.add(nxt.decode())
+                ti["stopped_at"] = nxt.decode()
+            print("[dataset] twin %s stopped on %s after %d of %d reads (rc %d): no verdict on the rest" %
+                  (tw, meta["name"], len(reached), len(order), rc), file=log)
+        info["twins"][tw] = ti
+        print("[dataset] %s vs stock on %s: %d reads differ" % (tw, meta["name"], len(d)), file=log)
         bad |= d
+    info["undefined"] = len(bad)
+    info["seconds"] = round(time.time() - t0, 1)
+    json.dump(info, open(os.path.join(meta["dir"], "undefined.json"), "w"), indent=1)
     with open(path, "w") as fh:
         fh.write("\n".join(sorted(bad)) + "\n")
     return bad
+
+
+def build_many(names, golden=True, workers=None, log=sys.stderr):
+    """Build several data sets (and their undefined-read lists) with a process pool: the reference's `-t 1` runs are
+    serial and there are many small sets (the 24 sweep cells)."""
+    import concurrent.futures as cf
+    metas = {}
+    for n in names:                       # indexes first, one at a time (shared by the cells)
+        build_index(dict(CONFIGS[n.split("@")[0]]), log)
+    with cf.ProcessPoolExecutor(max_workers=workers or max(1, (os.cpu_count() or 4) // 2)) as ex:
+        futs = {ex.submit(_build_one, n, golden): n for n in names}
+        for f in cf.as_completed(futs):
+            metas[futs[f]] = f.result()
+    return metas
+
+
+def _build_one(name, golden):
+    m = build(name, log=open(os.devnull, "w"), golden=golden)
+    if golden:
+        undefined_reads(m, log=open(os.devnull, "w"))
+    return m
 
 
 if __name__ == "__main__":
