@@ -1622,7 +1622,7 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
     const int key_len = dsb_read_hash_key_len((uint32_t)q_len);
     const uint32_t key_mask = (1u << key_len) - 1u;
     const uint32_t n_pos = (uint32_t)(q_len - DSB_KMER9 + 1);
-    if (w->L >= (1u << 24)) { w->overflow = 2; return key_len; }     // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes)
+    if (w->L >= (1u << 24)) { w->overflow = 16; return key_len; }     // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes)
     for (int c_dir = 2; c_dir >= 1; c_dir--) {
         if ((c_dir & both_dir) == 0) continue;
         const int strand = (c_dir == 2) ? 0 : 1;

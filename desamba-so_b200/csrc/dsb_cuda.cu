@@ -46,7 +46,7 @@ static int fail(const char *what, cudaError_t e)
 struct DsbCtrl {
     uint32_t next_read;      // work queue head of k_classify
     uint32_t n_hits;         // hit arena allocator
-    uint32_t overflow;       // bit0 arena too small, bit1 reference would abort, bit2 hit arena too small, bit3 anchor pool / job list too small
+    uint32_t overflow;       // bit0 arena too small, bit1 reference would abort, bit2 hit arena too small, bit3 anchor pool / job list too small, bit4 a read of >= 2^24 bases
     uint32_t next_island_read;   // work queue head of k_islands
     uint32_t n_jobs;         // job list allocator (k_islands), then the job count k_seed works through
     uint32_t next_job;       // work queue head of k_seed
@@ -786,8 +786,10 @@ static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_des
                 else
                     for (uint32_t k = 0; k < cnt; k++) pool[off + k] = w->anchors[k];
             }
-            jobs[jb].a_off = off;
-            jobs[jb].count = cnt;
+            // pool full: the batch is re-run with a larger pool; until then nobody may follow a_off past the pool's end
+            const bool lost = (w->overflow & 8u) != 0;
+            jobs[jb].a_off = lost ? 0u : off;
+            jobs[jb].count = lost ? 0u : cnt;
             jobs[jb].skip = skip_next;
             have = false;
         }
@@ -894,6 +896,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_SEED_MIN_BLOCKS) k_s
 {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (ctrl->overflow & 8u) return;            // k_islands ran out of job slots: n_jobs counts jobs that were never written
     const uint32_t n_jobs = ctrl->n_jobs;
     DsbWork w;
     memset(&w, 0, sizeof w);
@@ -937,6 +940,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
     __shared__ uint32_t s_job_ctr[DSB_CLASSIFY_THREADS / 32];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (rinfo && (ctrl->overflow & 8u)) return; // job list or anchor pool overflowed upstream: the host regrows and re-runs the batch
     DsbWork w;
     memset(&w, 0, sizeof w);
     w.ix = &ix;
@@ -1455,6 +1459,8 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
             TRY(cudaMalloc((void **)&s->d_rinfo, (size_t)max_reads * sizeof(DsbReadSeeds)));
             TRY(cudaMalloc((void **)&s->d_jobs, (size_t)s->cap_jobs * sizeof(DsbSeedJob)));
             s->cap_pool = (uint32_t)(max_bases / 8) + 64u * max_reads + 1024u;
+            // tests: start with arenas that are far too small, so that the regrow-and-rerun path runs (tests/test_gpu.py)
+            if (getenv("DSB_TEST_TINY_ARENAS")) { s->cap_jobs = 64; s->cap_pool = 256; }
             TRY(cudaMalloc((void **)&s->d_pool, (size_t)s->cap_pool * sizeof(DsbAnchor)));
         }
     }
@@ -1574,6 +1580,11 @@ int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **
             g_err = "a chain gap of >= 2000 reference bases reached sdp_middle: the reference aborts here (src/cly.c:2468)";
             return -2;
         }
+        if (of & 16u) {
+            s->in_flight = false;
+            g_err = "a read of 2^24 bases or more reached the device: the read's 9-mer table holds 24-bit positions";
+            return -3;
+        }
         if (attempt >= 8) { s->in_flight = false; g_err = "scratch arenas still too small after 8 regrows"; return -1; }
         // grow whatever overflowed and run the batch again (inputs are still on the device)
         if (of & 1u) {
@@ -1587,7 +1598,11 @@ int dsb_slot_wait(dsb_slot *s, const dsb_read_result **results, const dsb_hit **
         if (of & 8u) {                                 // anchor pool (or job list) of the split pipeline
             cudaFree(s->d_pool); cudaFree(s->d_jobs);
             s->d_pool = nullptr; s->d_jobs = nullptr;
+            // both allocators keep counting past their capacity, so they say how much this batch needs (the pool's count is
+            // only complete when k_seed ran, i.e. when the job list fitted)
             s->cap_pool *= 2; s->cap_jobs *= 2;
+            if (s->h_ctrl->n_jobs > s->cap_jobs) s->cap_jobs = s->h_ctrl->n_jobs + 64u;
+            if (s->h_ctrl->n_pool > s->cap_pool) s->cap_pool = s->h_ctrl->n_pool + s->h_ctrl->n_pool / 4u + 1024u;
             CU(cudaMalloc((void **)&s->d_pool, (size_t)s->cap_pool * sizeof(DsbAnchor)));
             CU(cudaMalloc((void **)&s->d_jobs, (size_t)s->cap_jobs * sizeof(DsbSeedJob)));
         }

@@ -313,7 +313,9 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
             if (r < 0) { *eof = 1; break; }
         }
         const uint64_t L = v.seq_l;
-        if (L > 0x7fffffff) dsb_fatal("read too long");
+        /* the read's 9-mer table on the device holds 24-bit positions; the reference's own table stops at 1 Mi nodes per
+         * strand, i.e. reads of about 0.9 Mbases (src/cly_mt.c:537-538, src/cly.c:2179-2182) */
+        if (L >= (1u << 24)) dsb_fatal("a read of %llu bases: reads of 2^24 bases or more are not supported", (unsigned long long)L);
         if (n > 0 && bases + L > limit_bases && L <= e->batch_bases) {   /* this batch is meant to be a small one */
             s->carry = v;
             s->have_carry = 1;

@@ -136,6 +136,15 @@ def test_batch_size_and_rerun_do_not_change_results(mixed):
     assert run_cli(mixed["idx"], mixed["reads"], env={"DSB_BLOCKS_PER_SM": "1"}) == want
 
 
+def test_job_list_and_anchor_pool_regrow_and_rerun(mixed):
+    """The split pipeline's batch-wide job list and anchor pool start far too small (DSB_TEST_TINY_ARENAS: 64 jobs, 256
+    anchors): k_islands / k_seed flag the overflow, k_seed / k_classify stand down, the host doubles both until the batch
+    fits and re-runs it; the bytes are the golden's."""
+    want = open(os.path.join(GOLD, "mixed.sam"), "rb").read()
+    assert run_cli(mixed["idx"], mixed["reads"], env={"DSB_TEST_TINY_ARENAS": "1"}) == want
+    assert run_cli(mixed["idx"], mixed["reads"], env={"DSB_TEST_TINY_ARENAS": "1", "DSB_BATCH_READS": "50"}) == want
+
+
 @pytest.mark.parametrize("name", ["tiny", "mixed"])
 def test_single_kernel_form_equals_split_pipeline(name, request):
     """DSB_SPLIT=0 (everything in k_classify) and the default k_islands -> k_seed -> k_classify give the same bytes."""
