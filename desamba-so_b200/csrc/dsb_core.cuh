@@ -232,6 +232,7 @@ struct DsbWork {
     uint8_t *ref_mid;             // 2000+64  : sdp_middle window  (persistent per warp)
     uint8_t *ref_ext;             // 1000+64+64 : right / left window
     uint32_t fast_classify;
+    uint32_t had_chain;           // the read reached delete_small_score_rst with >= 1 chain (src/cly.c:2884-2885)
     uint32_t overflow;            // set when an arena was too small -> batch is re-run bigger
     // fast seeding: islands are independent work items, one lane each (dsb_fast_seeding)
     uint32_t solo;                // 1 while this lane runs an island on its own (no warp-collective code)
@@ -2372,6 +2373,9 @@ DSB_HDN void dsb_get_score(DsbWork *w)
 // ------------------------------------------------------------------------------------------
 DSB_HDN void dsb_delete_small_score_rst(DsbWork *w)
 {
+    // only a read that arrives here WITH chains raises the worker's max_read_l (src/cly.c:2884-2885 return, :2953 update):
+    // the host needs that bit to evaluate `max_read_l < 510` for the reads that follow (dsb_history.c)
+    w->had_chain = w->n_chain != 0;
     if (w->n_chain == 0) return;
     if (w->n_chain > 200) {
         uint32_t rst_num = 200;
@@ -2569,6 +2573,7 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     w->n_anchor = 0;
     w->n_chain = 0;
     w->fast_classify = 1;
+    w->had_chain = 0;
     if (w->L < 40) return;                                                  // MIN_READ_LEN
     DSB_PHASE_BEGIN();
     dsb_islands(w, 0);
@@ -2592,6 +2597,7 @@ __device__ __noinline__ void dsb_classify_seeded(DsbWork *w, const DsbReadSeeds 
     w->n_anchor = 0;
     w->n_chain = 0;
     w->fast_classify = 1;
+    w->had_chain = 0;
     if (w->L < 40) return;
     w->total_score[0] = rs->total_score[0];
     w->total_score[1] = rs->total_score[1];

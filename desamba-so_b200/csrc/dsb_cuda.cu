@@ -993,7 +993,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
         }
         if (lane == 0) {
             dsb_read_result rr;
-            rr.hit_off = hit_off; rr.n_hit = w.n_chain; rr.fast_classify = w.fast_classify; rr.n_anchor = w.n_anchor;
+            rr.hit_off = hit_off; rr.n_hit = w.n_chain; rr.fast_classify = (w.fast_classify ? DSB_RES_FAST : 0u) | (w.had_chain ? DSB_RES_HAD_CHAIN : 0u); rr.n_anchor = w.n_anchor;
 #if defined(DSB_READ_CYCLES)
             // profiling build (tools/read_times.py): when this read started and how long it took, in microseconds
             unsigned long long t_end;

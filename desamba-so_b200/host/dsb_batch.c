@@ -22,7 +22,10 @@
 #define MAX_FMT_THREADS 32
 
 uint32_t dsb_history_max(const dsb_history *h);
-void dsb_history_note_max(dsb_history *h, uint32_t len);
+int dsb_history_class(const dsb_history *h, uint32_t len);
+void dsb_history_note_pending(dsb_history *h, uint32_t len);
+void dsb_history_note_result(dsb_history *h, uint32_t len, int had_chain);
+void dsb_history_all_drained(dsb_history *h);
 
 struct dsb_engine {
     dsb_loaded_index *ix;
@@ -80,6 +83,9 @@ struct dsb_session {
     /* a record that did not fit the previous batch */
     int have_carry;
     dsb_rec_view carry;
+    /* the carried read's filter class hangs on batches still on the device: drain them before the next record loop */
+    int need_drain;
+    uint64_t n_class_stalls;
 };
 
 static uint64_t env_u64(const char *name, uint64_t dflt)
@@ -328,6 +334,15 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
             s->have_carry = 1;
             break;
         }
+        /* 2G / 3G filter class (src/cly.c:2953-2981): known now, or only once the reads before this one are back */
+        const int cls = L >= 40 ? dsb_history_class(s->hist, (uint32_t)L) : 0;
+        if (cls == 2) {
+            s->carry = v;
+            s->have_carry = 1;
+            s->need_drain = 1;
+            s->n_class_stalls++;
+            break;
+        }
         /* a stable view's bases stay where they are until the copy helpers move the whole batch at once; the
          * history model only needs to READ them, from wherever they live */
         const char *src = v.seq;
@@ -335,8 +350,9 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
         else { memcpy(seq + bases, v.seq, L); s->copy_src[k][n] = NULL; src = seq + bases; }
         desc[n].seq_off = bases;
         desc[n].len = (uint32_t)L;
-        desc[n].flags = dsb_history_next(s->hist, src, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES));
-        if (L >= 40) dsb_history_note_max(s->hist, (uint32_t)L);
+        desc[n].flags = dsb_history_next(s->hist, src, (uint32_t)L, edge + (size_t)n * (DSB_HEAD_BYTES + DSB_TAIL_BYTES)) |
+                        (cls == 1 ? DSB_READ_2G : 0u);
+        dsb_history_note_pending(s->hist, (uint32_t)L);
         m->name_off[n] = m->names.l;
         dsb_strbuf_reserve(&m->names, v.name_l + 1);
         memcpy(m->names.s + m->names.l, v.name, v.name_l);
@@ -463,6 +479,9 @@ static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn 
     dsb_read_desc *desc;
     uint8_t *edge;
     dsb_slot_staging(s->slots[k], &seq, &desc, &edge);
+    /* the reference worker's max_read_l, in read order: batches are drained in submission order */
+    for (uint32_t i = 0; i < m->n_reads; i++)
+        if (desc[i].len >= 510) dsb_history_note_result(s->hist, desc[i].len, (j.res[i].fast_classify & DSB_RES_HAD_CHAIN) != 0);
     j.s = s; j.m = m; j.o = o; j.seq = seq; j.desc = desc;
     /* contiguous read ranges of about equal size in bases, one per formatter thread, sunk in order */
     const int parts = s->pool.n + 1;
@@ -652,6 +671,14 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         pthread_mutex_lock(&r.mu);
         while (b >= r.drained + (uint64_t)s->n_slots) pthread_cond_wait(&r.cv, &r.mu);
         pthread_mutex_unlock(&r.mu);
+        if (s->need_drain) {
+            /* the next read's filter class depends on results that are still on a device: wait for every batch */
+            pthread_mutex_lock(&r.mu);
+            while (r.drained < b) pthread_cond_wait(&r.cv, &r.mu);
+            pthread_mutex_unlock(&r.mu);
+            dsb_history_all_drained(s->hist);
+            s->need_drain = 0;
+        }
         /* the history borrows sequence pointers from the staging of earlier batches: before any
          * staging is overwritten it must own what it still needs */
         dsb_history_end_batch(s->hist);
@@ -669,7 +696,10 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         double t0 = dsb_now();
         uint32_t n = fill_slot(s, k, f, want_qual, &eof, limit);
         stats->t_parse += dsb_now() - t0;
-        if (n == 0) break;
+        if (n == 0) {
+            if (s->have_carry && s->need_drain) { b--; continue; }     /* nothing but a read whose filter class must wait */
+            break;
+        }
         stats->n_reads += n;
         stats->n_bases += s->meta[k].n_bases;
         stats->n_batches++;
@@ -688,6 +718,7 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     pthread_join(th_submit, NULL);
     pthread_join(th, NULL);
     dsb_history_end_batch(s->hist);
+    dsb_history_all_drained(s->hist);
     pthread_mutex_destroy(&r.mu);
     pthread_cond_destroy(&r.cv);
     stats->t_total = dsb_now() - t_start;

@@ -13,7 +13,12 @@
  *       BUFF_REALLOC src/lib/utils.h:117-122) are the neighbouring heap chunk: 0xFF = no match.
  *   head[64 + q], q in [-64, -1]: the 8 bytes before the buffer are glibc's chunk size field
  *       (little endian, low bits = flags); anything further is unknown: 0xFF = no match.
- *   flags bit0: `buff->max_read_l < 510` after this read (src/cly.c:2953-2955).
+ *   flags bit0: `buff->max_read_l < 510` after this read (src/cly.c:2953-2955).  max_read_l is raised only by reads
+ *       that reach delete_small_score_rst WITH a chain (src/cly.c:2884-2885 returns before :2953), which the host
+ *       learns when a batch comes back (DSB_RES_HAD_CHAIN).  So for a read shorter than 510 bases there are three
+ *       cases (dsb_history_class): an earlier read of >= 510 bases is KNOWN to have had a chain -> long-read filters;
+ *       no earlier read of >= 510 bases can still turn out to have had one -> 2G filter; otherwise the answer hangs on
+ *       batches still on the device: the batcher closes the batch before that read and waits for them.
  */
 #include "dsb_host.h"
 #include <stdlib.h>
@@ -29,7 +34,8 @@ struct dsb_history {
     hist_entry *st;    /* skyline: lengths strictly decrease from bottom (oldest) to top (newest) */
     int n, m;
     uint64_t m_bin_read;   /* current allocation size of bin_read */
-    uint32_t max_read_l;
+    uint32_t max_known;    /* the reference's max_read_l over the reads whose results are back */
+    uint32_t max_pending;  /* longest read handed to a device whose DSB_RES_HAD_CHAIN bit is not known yet */
     int n_borrowed;
 };
 
@@ -75,7 +81,7 @@ uint32_t dsb_history_next(dsb_history *h, const char *seq, uint32_t len, uint8_t
     if (len < 40) {
         /* classify_seq returns before getIsland (src/cly.c:3084): the buffer is untouched */
         memset(edge, 0xFF, DSB_HEAD_BYTES + DSB_TAIL_BYTES);
-        return (h->max_read_l < 510) ? DSB_READ_2G : 0;
+        return 0;
     }
     /* BUFF_REALLOC(bin_read, m, 2L) */
     if ((uint64_t)2 * len > h->m_bin_read) h->m_bin_read = (uint64_t)2 * len + 20;
@@ -116,19 +122,34 @@ uint32_t dsb_history_next(dsb_history *h, const char *seq, uint32_t len, uint8_t
     h->st[h->n].owned = NULL;
     h->st[h->n].len = len;
     h->n++;
-    /* max_read_l: see dsb_batch.c for the exact rule (only reads that reach the filter update it) */
-    uint32_t flags = 0;
-    uint32_t mx = h->max_read_l > len ? h->max_read_l : len;
-    if (mx < 510) flags |= DSB_READ_2G;
-    return flags;
+    return 0;
 }
 
-void dsb_history_note_max(dsb_history *h, uint32_t len)
+/* Which filter class a read of `len` bases gets (src/cly.c:2953-2981): 0 = max_read_l >= 510 for certain,
+ * 1 = max_read_l < 510 for certain ("2G"), 2 = depends on reads whose results are not back yet. */
+int dsb_history_class(const dsb_history *h, uint32_t len)
 {
-    if (len > h->max_read_l) h->max_read_l = len;
+    if (len >= 510 || __atomic_load_n(&h->max_known, __ATOMIC_ACQUIRE) >= 510) return 0;
+    if (h->max_pending < 510) return 1;
+    return 2;
 }
 
-uint32_t dsb_history_max(const dsb_history *h) { return h->max_read_l; }
+/* a read goes to a device (producer thread) */
+void dsb_history_note_pending(dsb_history *h, uint32_t len)
+{
+    if (len >= 40 && len > h->max_pending) h->max_pending = len;
+}
+
+/* a read's result is back (drain thread, in read order) */
+void dsb_history_note_result(dsb_history *h, uint32_t len, int had_chain)
+{
+    if (had_chain && len > __atomic_load_n(&h->max_known, __ATOMIC_RELAXED)) __atomic_store_n(&h->max_known, len, __ATOMIC_RELEASE);
+}
+
+/* every batch handed out so far has been drained (producer thread, after waiting for the drain thread) */
+void dsb_history_all_drained(dsb_history *h) { h->max_pending = 0; }
+
+uint32_t dsb_history_max(const dsb_history *h) { return h->max_known; }
 
 void dsb_history_end_batch(dsb_history *h)
 {

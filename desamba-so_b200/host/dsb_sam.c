@@ -108,7 +108,7 @@ static void format_des(dsb_strbuf *out, const dsb_loaded_index *ix, const dsb_ou
                        uint32_t read_l, const dsb_read_result *r, const dsb_hit *h, int full)
 {
     dsb_strbuf_printf(out, "%s\t%s\t%s\t%ld\tn_rst:[%ld]\tn_anc:[%ld]\t\n", name, r->n_hit ? "CLASSIFY" : "UNCLASSIFY",
-                      r->fast_classify ? "FAST" : "SLOW", (long)read_l, (long)r->n_hit, (long)r->n_anchor);
+                      (r->fast_classify & DSB_RES_FAST) ? "FAST" : "SLOW", (long)read_l, (long)r->n_hit, (long)r->n_anchor);
     int rst_cnt = 0;
     for (uint32_t i = 0; i < r->n_hit; i++)
         if (h[i].pri_index == 0) print_hit(out, ix, h + i, rst_cnt++);

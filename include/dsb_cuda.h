@@ -69,7 +69,9 @@ uint64_t dsb_index_device_bytes(const dsb_index *ix);
 typedef struct dsb_read_desc {
     uint64_t seq_off;
     uint32_t len;
-    uint32_t flags;         /* bit0: worker's running max read length < 510 ("2G reads" filter, src/cly.c:2953-2963) */
+    uint32_t flags;         /* bit0: the reference worker's max_read_l, after this read, is < 510 ("2G reads" filter,
+                             * src/cly.c:2953-2963): a running maximum over the EARLIER READS THAT HAD A CHAIN and this one;
+                             * evaluated on the host in read order from the DSB_RES_HAD_CHAIN bits of the reads before */
 } dsb_read_desc;
 #define DSB_READ_2G 1u
 
@@ -92,9 +94,14 @@ typedef struct dsb_hit {
 typedef struct dsb_read_result {
     uint32_t hit_off;       /* first hit of this read in the batch's hit array */
     uint32_t n_hit;
-    uint32_t fast_classify; /* cly_r.fast_classify (src/cly.h:97) */
+    uint32_t fast_classify; /* bit 0 (DSB_RES_FAST): cly_r.fast_classify (src/cly.h:97); bit 1 (DSB_RES_HAD_CHAIN): the read
+                             * entered delete_small_score_rst with >= 1 chain, i.e. it raised the reference worker's
+                             * max_read_l (src/cly.c:2884-2885,2953) */
     uint32_t n_anchor;      /* cly_r.anchor_v.n */
 } dsb_read_result;
+
+#define DSB_RES_FAST      1u
+#define DSB_RES_HAD_CHAIN 2u
 
 /* Work counters, summed over the batch: the algorithmic units of SURVEY.md 8(d). */
 typedef struct dsb_counters {

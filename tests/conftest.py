@@ -174,3 +174,36 @@ pickle.dump(res, open(sys.argv[4], "wb"))
                         os.path.join(d, "in.pkl"), os.path.join(d, "out.pkl")], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
     assert r.returncode == 0, r.stderr.decode()[-1500:]
     return pickle.load(open(os.path.join(d, "out.pkl"), "rb"))
+
+
+def max_read_l_stream(src_fastq, dst_fastq, junk_first=True, seed=17):
+    """A read stream for the reference's max_read_l rule (src/cly.c:2884-2885,2953-2981): three long reads that cannot have
+    a chain (random bases; with junk_first=False, three long REAL reads instead), then 60 reads cut down to 100..509 bases,
+    one long real read, then 40 more short reads.  Until the first long read WITH a chain has been classified the short reads
+    take the "2G" filter; afterwards the long-read filters."""
+    import random
+    rng = random.Random(seed)
+    lines = open(src_fastq).read().split("\n")
+    recs = [lines[i:i + 4] for i in range(0, len(lines) - 1, 4)]
+    real = [r for r in recs if "junk" not in r[0]]
+    longs = [r for r in real if len(r[1]) >= 1500]
+    out = []
+    for i in range(3):
+        if junk_first:
+            s = "".join(rng.choice("ACGT") for _ in range(3000))
+            out += ["@lead%d_junk" % i, s, "+", "I" * len(s)]
+        else:
+            out += ["@lead%d" % i] + longs[i][1:]
+
+    def short(r, k):
+        n = rng.choice([100, 150, 250, 309, 310, 400, 509])
+        n = min(n, len(r[1]))
+        st = rng.randrange(0, len(r[1]) - n + 1)
+        return ["@s%d_%s" % (k, r[0][1:]), r[1][st:st + n], "+", r[3][st:st + n]]
+    pool = [r for r in real if len(r[1]) >= 520]
+    for k in range(60):
+        out += short(pool[k % len(pool)], k)
+    out += ["@mid_long"] + longs[5][1:]
+    for k in range(60, 100):
+        out += short(pool[k % len(pool)], k)
+    open(dst_fastq, "w").write("\n".join(out) + "\n")

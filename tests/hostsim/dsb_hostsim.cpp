@@ -206,7 +206,7 @@ static int run_batch(dsb_slot *s, uint32_t cap_anchor, uint32_t cap_sms)
         dsb_read_result &r = s->results[i];
         r.hit_off = (uint32_t)s->hits.size();
         r.n_hit = w.n_chain;
-        r.fast_classify = w.fast_classify;
+        r.fast_classify = (w.fast_classify ? DSB_RES_FAST : 0u) | (w.had_chain ? DSB_RES_HAD_CHAIN : 0u);
         r.n_anchor = w.n_anchor;
         for (uint32_t c = 0; c < w.n_chain; c++) {
             const DsbChain &ch = w.chains[c];

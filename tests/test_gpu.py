@@ -136,6 +136,19 @@ def test_batch_size_and_rerun_do_not_change_results(mixed):
     assert run_cli(mixed["idx"], mixed["reads"], env={"DSB_BLOCKS_PER_SM": "1"}) == want
 
 
+def test_max_read_l_counts_only_reads_that_had_a_chain(mixed, have_ref_binary, tmp_path):
+    """GPU form of tests/test_host.py's test of the same name (reference src/cly.c:2884-2885,2953-2981)."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import max_read_l_stream, ref_cli
+    for junk_first in (True, False):
+        fq = str(tmp_path / ("m%d.fq" % junk_first))
+        max_read_l_stream(mixed["reads"], fq, junk_first=junk_first)
+        want = ref_cli([mixed["idx"] + "/", fq])
+        for env in ({}, {"DSB_BATCH_READS": "7"}, {"DSB_BATCH_READS": "1"}):
+            assert run_cli(mixed["idx"], fq, env=env) == want, (junk_first, env)
+
+
 def test_job_list_and_anchor_pool_regrow_and_rerun(mixed):
     """The split pipeline's batch-wide job list and anchor pool start far too small (DSB_TEST_TINY_ARENAS: 64 jobs, 256
     anchors): k_islands / k_seed flag the overflow, k_seed / k_classify stand down, the host doubles both until the batch

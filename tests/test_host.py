@@ -481,3 +481,24 @@ def test_thread_num_change_restarts_the_buffer_history(mixed, have_ref_binary):
         got = d.read_classify(fq, thread_id=tid, thread_num=tn)
         if tn == 1:
             assert got == want[i], i
+
+
+def test_max_read_l_counts_only_reads_that_had_a_chain(mixed, have_ref_binary, tmp_path):
+    """The reference worker's max_read_l is raised only by reads that reach the filter WITH a chain (src/cly.c:2884-2885
+    returns first, :2953 updates): after long reads without any hit, short reads still take the 2G filter.  A stream
+    that opens with three 3 kb junk reads, then 100..509-base reads, a long real read, more short reads -- byte-identical
+    to the reference binary, at several batch sizes (the class of a short read may hang on a batch still in flight)."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    from conftest import max_read_l_stream, ref_cli
+    fq, fq2 = str(tmp_path / "a.fq"), str(tmp_path / "b.fq")
+    max_read_l_stream(mixed["reads"], fq, junk_first=True)
+    max_read_l_stream(mixed["reads"], fq2, junk_first=False)
+    want = ref_cli([mixed["idx"] + "/", fq])
+    other = ref_cli([mixed["idx"] + "/", fq2])
+    # teeth: in the reference itself the short reads' records depend on whether the leading long reads had chains
+    tail = lambda t: [l for l in t.split(b"\n") if l.startswith(b"s")]
+    assert tail(want) != tail(other)
+    for env in ({}, {"DSB_BATCH_READS": "7"}, {"DSB_BATCH_READS": "1"}, {"DSB_BATCH_READS": "64", "DSB_HOSTSIM_GPUS": "2"}):
+        assert run_sim(mixed["idx"], [fq], env=env) == want, env
+        assert run_sim(mixed["idx"], [fq2], env=env) == other, env
