@@ -1751,4 +1751,67 @@ int dsb_exist_batch(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *ex
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Exist-k-mer probes in bulk WITHOUT any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).  The device-side working buffers of dsb_exist_batch -- the 2-bit codes the kernel reads and the exist bytes
+// it writes -- live in ONE file-scope device array of DSB_EXIST_STATIC_MAX codes + as many exist bytes (8 MiB + padding,
+// held by every GPU that loads this library until the process exits).  In host code `g_exist_static` is only a stand-in
+// for the symbol, never a device address: the address is fetched once per device, with that device current, by
+// cudaGetSymbolAddress and handed to the kernel.  All calls share the array and it keeps the last call's contents: the
+// part a call uses is cleared first, and two calls that overlap on one GPU race (callers serialise them; within a
+// process a host mutex does).
+// ------------------------------------------------------------------------------------------
+#define DSB_EXIST_STATIC_PAD 256
+static __device__ __align__(256) uint8_t g_exist_static[2 * (DSB_EXIST_STATIC_MAX + DSB_EXIST_STATIC_PAD)];
+
+// same work as k_exist_flat, on the static scratch: codes at scratch[0 ..), exist bytes at scratch[half ..)
+__global__ void __launch_bounds__(256) k_exist_flat_static(const __grid_constant__ DsbIndexView ix, uint8_t *__restrict__ scratch,
+                                                           uint64_t n_kmer)
+{
+    const uint8_t *codes = scratch;
+    uint8_t *exist = scratch + (DSB_EXIST_STATIC_MAX + DSB_EXIST_STATIC_PAD);
+    uint32_t p0 = 0, p1 = 0;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_kmer; i += (uint64_t)gridDim.x * blockDim.x)
+        exist[i] = dsb_exist_kmer(&ix, codes + i, &p0, &p1);
+}
+
+#define DSB_MAX_DEVICES 64
+static std::mutex g_exist_static_mu;
+static uint8_t *g_exist_static_ptr[DSB_MAX_DEVICES];      // device address of g_exist_static on each GPU (set up on first use)
+
+int dsb_exist_batch_static(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist)
+{
+    if (!ix || !codes || !exist) { g_err = "dsb_exist_batch_static: null argument"; return -1; }
+    const uint64_t k = (uint64_t)ix->v.ek_len;
+    if (n < k) { g_err = "dsb_exist_batch_static: string shorter than k"; return -1; }
+    if (n > (uint64_t)DSB_EXIST_STATIC_MAX) {
+        g_err = "dsb_exist_batch_static: " + std::to_string(n) + " codes exceed the static scratch of " +
+                std::to_string((uint64_t)DSB_EXIST_STATIC_MAX) + " (DSB_EXIST_STATIC_MAX); split the string or use dsb_exist_batch";
+        return -1;
+    }
+    if (ix->dev < 0 || ix->dev >= DSB_MAX_DEVICES) { g_err = "dsb_exist_batch_static: device ordinal out of range"; return -1; }
+    std::lock_guard<std::mutex> lock(g_exist_static_mu);
+    CU(cudaSetDevice(ix->dev));
+    uint8_t *scratch = g_exist_static_ptr[ix->dev];
+    if (!scratch) {                                     // once per device, with that device current
+        void *p = nullptr;
+        CU(cudaGetSymbolAddress(&p, g_exist_static));
+        if (!p) { g_err = "dsb_exist_batch_static: cudaGetSymbolAddress returned no address"; return -1; }
+        scratch = g_exist_static_ptr[ix->dev] = (uint8_t *)p;
+    }
+    const uint64_t nk = n - k + 1;
+    const uint64_t half = DSB_EXIST_STATIC_MAX + DSB_EXIST_STATIC_PAD;
+    // the array keeps the last call's contents: clear what this call reads beyond its codes (the k-mer of the last start
+    // reads up to 16 bytes) and the exist bytes it is about to produce
+    CU(cudaMemset(scratch + n, 0, DSB_EXIST_STATIC_PAD));
+    CU(cudaMemset(scratch + half, 0, nk));
+    CU(cudaMemcpy(scratch, codes, n, cudaMemcpyHostToDevice));
+    k_exist_flat_static<<<ix->sm_count * 8, 256>>>(ix->v, scratch, nk);
+    CU(cudaGetLastError());
+    g_launches++;
+    CU(cudaMemcpy(exist, scratch + half, nk, cudaMemcpyDeviceToHost));     // synchronises with the kernel (default stream)
+    return 0;
+}
+
 }  // extern "C"

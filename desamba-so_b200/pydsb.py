@@ -17,7 +17,7 @@ API_SYMBOLS = ["load_index", "read_classify", "meta_analysis"]
 CUDA_SYMBOLS = ["dsb_gpu_count", "dsb_index_upload", "dsb_index_clone", "dsb_index_free", "dsb_index_device_bytes", "dsb_slot_create",
                 "dsb_slot_free", "dsb_slot_staging", "dsb_slot_submit", "dsb_slot_wait", "dsb_slot_timing",
                 "dsb_slot_rerun_device", "dsb_last_error", "dsb_kernel_launch_count", "dsb_fm_rank_batch",
-                "dsb_exist_batch"]
+                "dsb_exist_batch", "dsb_exist_batch_static", "dsb_index_build", "dsb_build_last_error"]
 HOST_SYMBOLS = ["dsb_index_load", "dsb_index_release_bulk", "dsb_index_destroy", "dsb_engine_create",
                 "dsb_engine_destroy", "dsb_session_create", "dsb_session_destroy", "dsb_session_run",
                 "dsb_fq_open_path", "dsb_fq_open_mem", "dsb_fq_close", "dsb_history_new", "dsb_history_next",
@@ -179,6 +179,18 @@ class DeviceIndex:
         if rc != 0:
             raise RuntimeError("dsb_exist_batch: " + self.cuda.dsb_last_error().decode())
         return out, ms.value
+
+    def exist_static(self, codes):
+        """dsb_exist_batch_static: the same probes through the entry point that allocates nothing."""
+        np = self.np
+        codes = np.ascontiguousarray(codes, dtype=np.uint8)
+        k = self.ek_len()
+        out = np.full(max(0, len(codes) - k + 1), 0xEE, dtype=np.uint8)
+        rc = self.cuda.dsb_exist_batch_static(self.handle, codes.ctypes.data_as(C.c_void_p), C.c_uint64(len(codes)),
+                                              out.ctypes.data_as(C.c_void_p))
+        if rc != 0:
+            raise RuntimeError("dsb_exist_batch_static: " + self.cuda.dsb_last_error().decode())
+        return out
 
     def ek_len(self):
         self.host.dsb_ekmer_len.argtypes = [C.c_uint64]

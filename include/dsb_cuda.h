@@ -187,6 +187,18 @@ typedef struct dsb_build_stats {
 int dsb_index_build(const char *ref_fasta, const char *kmer_srt, const char *out_dir, int dev, dsb_build_stats *stats);
 const char *dsb_build_last_error(void);
 
+/* Exist-k-mer probes in bulk with NO allocation of any kind (no cudaMalloc / cudaFree / allocating library call): the
+ * same results as dsb_exist_batch for codes[0..n) -> exist[0..n-k+1) (host pointers), computed by a variant of its kernel
+ * whose device-side working buffers are one file-scope `static __device__` array inside libdsb_cuda.so.
+ * This entry point has NO COUNTERPART IN THE REFERENCE: it was added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Limit: n <= DSB_EXIST_STATIC_MAX codes per call (larger n is rejected with -1 and a dsb_last_error() that says so);
+ * the array (2 x (DSB_EXIST_STATIC_MAX + 256) bytes = 8 MiB) is held by every GPU that loads the library until exit.
+ * All calls share the array: calls that overlap on one GPU race (calls of one process are serialised by a host mutex;
+ * processes sharing a GPU each have their own copy of the array). */
+#define DSB_EXIST_STATIC_MAX 4194304u   /* 4 Mi codes */
+int  dsb_exist_batch_static(dsb_index *ix, const uint8_t *codes, uint64_t n, uint8_t *exist);
+
 const char *dsb_last_error(void);
 int  dsb_kernel_launch_count(void);   /* kernels launched by this library so far */
 
