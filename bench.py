@@ -1,19 +1,27 @@
 #!/usr/bin/env python3
-"""bench.py -- Mbp/s classified on the BASELINE.json workload (configs[1]: 50 Mbp synthetic multi-genome
-index, 10 000 simulated 5 kb reads at 10 % error), 1..8 B200, index replicated, reads sharded.
+"""bench.py -- Mbp/s classified on the BASELINE.json headline workload (configs[2]: RefSeq-scale unitig index, simulated
+10 kb ONT-like reads, read-sharded over 1/2/4/8 B200 with the index replicated).  Default = `cfg3`: a 1 Gbp reference
+(200 families x 5 strains x 1 Mbp: BWT 0.95 G rows, FM blocks 0.95 GB, prefix table 512 MiB, exist tables 2 x 256 MiB /
+k = 17 -- everything far larger than the 126 MB L2), built on the box by this repository's own `deSAMBA index`, and
+100 000 reads (~1 Gbase) PER GPU.  DSB_WORKLOAD=cfg3x is the same at 4 Gbp (configs[2]'s own size), cfg2 is configs[1].
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
 One "step" = one pass of the classify hot path over the rank's batch of reads.
-  value        whole-job Mbp/s with the batch already resident in HBM (kernels only, CUDA events on the
-               library's stream, max over ranks)
+  value        whole-job Mbp/s with the batch already resident in HBM (the path's kernels + D2H of the results; CUDA events
+               on the library's stream, max over ranks); `h2d_kernels_d2h` is the same with the H2D of the staged batch
+               inside the events (SURVEY 8d's definition)
   e2e          same metric through read_classify() of libdesamba.so: FASTQ text in host memory in, SAM text
                out (parse, pinned H2D, kernels, D2H, SAM formatting all inside the timed region)
   roofline     dominant kernel (k_classify): algorithmic bytes (counted by the kernels) / its
                CUDA-event time vs the measured HBM peak; `fm_search` = bulk FM rank probe on a BWT larger
                than L2 vs the same peak (the random-access roofline the north star names)
-  cpu_baseline the UNMODIFIED reference (oracle/_ref/deSAMBA classify -t <cores>) on the same reads, same box
-`--impl reference` times that reference binary alone (rank 0 only).
+  cpu_baseline the UNMODIFIED reference (oracle/_ref/deSAMBA classify -t <cores>) on a bounded sample of the same reads
+               (the first REF_SAMPLE_READS reads), same index, same box
+  e2e_inproc   (N > 1, rank 0, outside the timed region) ONE process driving all N GPUs through read_classify() on N x
+               the per-GPU reads -- the north star's own multi-GPU design -- and `inproc_parity`: md5 of a read set
+               classified with 1 and with N devices in one process
+`--impl reference` times that reference binary alone (rank 0 only) on the same bounded sample.
 The oracle is only the checker / the CPU baseline here; nothing under oracle/ is on the measured GPU path.
 """
 import argparse
@@ -30,13 +38,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "desamba-so_b200"))
 sys.path.insert(0, os.path.join(ROOT, "tools"))
 
-# The bench workload is BASELINE.json configs[1] (cfg2).  DSB_WORKLOAD=cfg3s measures configs[2] at the scale the
-# reference's index builder allows on the box (tools/dataset.py); that line is evidence for profiles/, not the headline.
-WORKLOAD = os.environ.get("DSB_WORKLOAD", "cfg2")
+WORKLOAD = os.environ.get("DSB_WORKLOAD", "cfg3")
 WORKLOAD_TEXT = {
-    "cfg2": "cfg2: 50 Mbp 10x5x1Mbp index, 10000 x 5 kb reads @10% error",
-    "cfg3s": "cfg3s (configs[2] scaled): 200 Mbp 40x5x1Mbp index, 20000 x 10 kb ONT-like reads @10% error",
-}.get(WORKLOAD, WORKLOAD)
+    "cfg2": "cfg2 = BASELINE configs[1]: 50 Mbp 10x5x1Mbp index, 10000 x 5 kb reads @10% error per GPU",
+    "cfg3": "cfg3 = BASELINE configs[2] at 1 Gbp: 200x5x1Mbp reference, BWT 0.95 G rows, exist tables 2x256 MiB (k=17), index "
+            "built by this repo's `deSAMBA index`; 100000 ONT-like 10 kb reads (~1 Gbase, 10% error 30/30/40 sub/ins/del, "
+            "+-50% length) per GPU",
+    "cfg3x": "cfg3x = BASELINE configs[2] at 4 Gbp: 800x5x1Mbp reference, BWT 3.8 G rows (> 2^32 with the reference's "
+             "block bytes), exist tables 2x1 GiB (k=18), index built by this repo's `deSAMBA index`; 100000 ONT-like 10 kb "
+             "reads (~1 Gbase) per GPU",
+}.get(WORKLOAD, WORKLOAD) + " (tools/dataset.py)"
+REF_SAMPLE_READS = int(os.environ.get("DSB_REF_SAMPLE_READS", "20000"))     # bounded sample of the reference arm
 METRIC = "Mbp/s classified"
 UNIT = "Mbp/s"
 
@@ -154,18 +166,42 @@ def sum_over_ranks(dist, v):
 # ------------------------------------------------------------------------------------------------
 # reference arm / CPU baseline: the unmodified reference binary on the box's host cores
 # ------------------------------------------------------------------------------------------------
+def reference_sample(meta):
+    """The bounded sample the reference is timed on: the first REF_SAMPLE_READS reads of the workload's read set
+    -> (path, n_reads, n_bases)."""
+    path = os.path.join(meta["dir"], "ref_sample_%d.fq" % REF_SAMPLE_READS)
+    n = min(REF_SAMPLE_READS, meta["n_reads"])
+    if n == meta["n_reads"]:
+        return meta["reads"], meta["n_reads"], meta["n_bases"]
+    info = path + ".json"
+    if not (os.path.exists(path) and os.path.exists(info)):
+        bases = 0
+        with open(meta["reads"], "rb") as fi, open(path + ".tmp", "wb") as fo:
+            for i in range(4 * n):
+                line = fi.readline()
+                if i % 4 == 1:
+                    bases += len(line) - 1
+                fo.write(line)
+        os.replace(path + ".tmp", path)
+        json.dump({"n_reads": n, "n_bases": bases}, open(info, "w"))
+    d = json.load(open(info))
+    return path, d["n_reads"], d["n_bases"]
+
+
 def reference_run(meta, threads):
-    """One `deSAMBA classify -t threads` pass; returns (seconds of classify excluding index load, bases)."""
+    """One `deSAMBA classify -t threads` pass over the bounded sample; returns (seconds of classify excluding index
+    load -- the reference's own 'sequences processed in' line --, bases, reads)."""
     ref_bin = os.path.join(ROOT, "oracle", "_ref", "deSAMBA")
     if not os.path.exists(ref_bin):
         raise RuntimeError("oracle/_ref/deSAMBA missing (built by __graft_entry__.build() where /root/reference exists)")
-    r = subprocess.run([ref_bin, "classify", "-t", str(threads), "-f", "SAM", meta["idx"] + "/", meta["reads"]],
+    fq, n_reads, n_bases = reference_sample(meta)
+    r = subprocess.run([ref_bin, "classify", "-t", str(threads), "-f", "SAM", meta["idx"] + "/", fq],
                        stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
     err = r.stderr.decode(errors="replace")
     m = re.search(r"sequences processed in ([0-9.]+)s", err)
     if r.returncode != 0 or not m:
         raise RuntimeError("reference classify failed: " + err[-500:])
-    return float(m.group(1)), meta["n_bases"]
+    return float(m.group(1)), n_bases, n_reads
 
 
 def cpu_model():
@@ -182,23 +218,26 @@ def run_reference_arm(args):
     import dataset
     if RANK != 0:
         return
-    meta = dataset.build(WORKLOAD, log=sys.stderr)
+    meta = dataset.build(WORKLOAD, log=sys.stderr, golden=False)
     cores = os.cpu_count() or 1
     for _ in range(args.warmup):
         reference_run(meta, cores)
     t = 0.0
+    n_bases = n_reads = 0
     for _ in range(args.steps):
-        s, _b = reference_run(meta, cores)
+        s, n_bases, n_reads = reference_run(meta, cores)
         t += s
-    v = meta["n_bases"] * args.steps / t / 1e6
+    v = n_bases * args.steps / t / 1e6
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8/int64", "data": "synthetic",
-        "config": {"workload": WORKLOAD_TEXT + " (tools/dataset.py)",
-                   "n_reads": meta["n_reads"], "n_bases": meta["n_bases"], "timing": "reference's own 'sequences processed in' line, index load excluded"},
+        "config": {"workload": WORKLOAD_TEXT,
+                   "sample_reads_per_step": n_reads, "sample_bases_per_step": n_bases,
+                   "timing": "reference's own 'sequences processed in' line, index load excluded"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference",
-                         "sample": "all %d reads, deSAMBA classify -t %d, %s" % (meta["n_reads"], cores, cpu_model())},
+                         "sample": "the first %d reads of the workload (%d bases) per step, deSAMBA classify -t %d, %s" %
+                                   (n_reads, n_bases, cores, cpu_model())},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -247,8 +286,11 @@ class DeviceBatch:
         host.dsb_history_new.restype = C.c_void_p
         host.dsb_history_next.restype = C.c_uint32
         host.dsb_history_next.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]
-        host.dsb_history_note_max.argtypes = [C.c_void_p, C.c_uint32]
         host.dsb_history_free.argtypes = [C.c_void_p]
+        # the 2G / 3G filter class of a read shorter than 510 bases depends on earlier results (dsb_history.c); the bench
+        # workloads have none, so every read is in the long-read class and one launch can hold the whole set
+        if int(lens.min()) < 510:
+            raise RuntimeError("bench workload holds reads shorter than 510 bases")
         h = host.dsb_history_new()
         desc = (pydsb.ReadDesc * self.n_reads).from_address(p_desc.value)
         edge_stride = 128
@@ -257,8 +299,6 @@ class DeviceBatch:
             desc[i].seq_off = o
             desc[i].len = L
             desc[i].flags = host.dsb_history_next(h, p_seq.value + o, L, p_edge.value + i * edge_stride)
-            if L >= 40:
-                host.dsb_history_note_max(h, L)
         host.dsb_history_free(h)
         self.h2d_bytes = self.n_bases + self.n_reads * (16 + edge_stride + 4)
         self.counters = None
@@ -300,9 +340,37 @@ class DeviceBatch:
 
 
 def algorithmic_bytes(c, n_bases):
-    """DESIGN.md 'algorithmic bytes': what one pass of k_classify must fetch at minimum."""
+    """DESIGN.md 'algorithmic bytes': what one pass of the classify stage must fetch at minimum."""
     return (c["occ_queries"] * 64 + c["lut_lookups"] * 16 + c["sa_lookups"] * 8 + c["unitig_reads"] * 8 +
             c["refpos_reads"] * 8 + c["ref_window_bytes"] + 4 * n_bases)
+
+
+def random_access_peak(dev):
+    """The random-access ceiling of this GPU, measured in this run: plain gathers of 32 / 64 / 128-byte pieces from an
+    8 GiB table (k_random_gather, no arithmetic) -> GB/s per piece size."""
+    import pydsb
+    cuda = pydsb.load_cuda_layer()
+    ra = {}
+    for chunk in (32, 64, 128):
+        t = C.c_float(0)
+        rc = cuda.dsb_random_access_probe(dev, C.c_uint64(8 << 30), C.c_uint32(chunk), C.c_uint64(1 << 26), 3, C.byref(t))
+        if rc != 0:
+            raise RuntimeError("dsb_random_access_probe: " + cuda.dsb_last_error().decode())
+        ra["%dB" % chunk] = (1 << 26) * chunk / (t.value * 1e-3) / 1e9
+    return ra
+
+
+def fm_search_product(counters, k_seed_ms, ra, index_bytes):
+    """The north star's FM-search figure for the PRODUCT kernel: rank queries issued by k_seed (one 64-byte FM block
+    each; the kernel counts them) / k_seed's CUDA-event time, against the random-64 B ceiling measured in this run.
+    k_seed also does the LUT, SA, unitig and reference-window reads and the Landau-Vishkin extensions in that time, so
+    this is a lower bound on its rank-query rate."""
+    q = counters.get("seed_occ_queries") or counters["occ_queries"]
+    gbs = q * 64 / (k_seed_ms * 1e-3) / 1e9
+    return {"kernel": "k_seed", "occ_queries": q, "counted_by": "seed_occ_queries" if counters.get("seed_occ_queries") else
+            "occ_queries (k_seed + the slow-seeding path of k_classify)", "bytes_per_query": 64, "ms": k_seed_ms,
+            "achieved": gbs, "unit": "GB/s", "random_64B_peak": ra["64B"], "frac_of_random_64B": gbs / ra["64B"],
+            "index_device_bytes": index_bytes}
 
 
 def fm_probe(ix_dir_unused, dev, hbm_peak):
@@ -318,16 +386,8 @@ def fm_probe(ix_dir_unused, dev, hbm_peak):
     _o, _c, ms = ix.fm_rank(rows, c, repeat=5)
     ix.close()
     gbs = n * 64 / (ms * 1e-3) / 1e9
-    # the ceiling: plain random gathers of 32 / 64 / 128-byte pieces from an 8 GiB table (no arithmetic)
-    cuda = pydsb.load_cuda_layer()
-    ra = {}
-    for chunk in (32, 64, 128):
-        t = C.c_float(0)
-        rc = cuda.dsb_random_access_probe(dev, C.c_uint64(8 << 30), C.c_uint32(chunk), C.c_uint64(1 << 26), 3, C.byref(t))
-        if rc != 0:
-            raise RuntimeError("dsb_random_access_probe: " + cuda.dsb_last_error().decode())
-        ra["%dB" % chunk] = (1 << 26) * chunk / (t.value * 1e-3) / 1e9
-    return {"kernel": "k_fm_rank", "queries": n, "ms": ms, "bytes_per_query": 64, "achieved": gbs, "peak": hbm_peak,
+    ra = random_access_peak(dev)
+    return {"kernel": "k_fm_rank (synthetic micro-kernel: validates the 64-byte FM block, NOT the product's FM search)", "queries": n, "ms": ms, "bytes_per_query": 64, "achieved": gbs, "peak": hbm_peak,
             "unit": "GB/s", "frac": gbs / hbm_peak, "table_bytes": (n_sym // 64) * 64,
             "random_access_peak": ra, "frac_of_random_64B": gbs / ra["64B"],
             "note": "one 64 B block (2 sectors) per rank query, random rows, table 16x larger than L2; "
@@ -356,7 +416,7 @@ def e2e_leg(meta, dev, steps, warmup, sampler=None):
     text = open(meta["reads"], "rb").read()
     n_sam = 0
     for _ in range(max(1, warmup)):
-        n_sam = len(d.read_classify(text, thread_id=0, thread_num=1))
+        _t, n_sam = d.read_classify_timed(text, thread_id=0, thread_num=1)
     dt = 0.0
     if sampler is not None:
         sampler.active = True
@@ -389,7 +449,10 @@ def run_ours(args):
         meta = dataset.build(name, golden=False)
     t_load = time.perf_counter()
     batch = DeviceBatch(meta["idx"], meta["reads"], LOCAL_RANK)
-    log("index + batch resident in %.1fs, %d reads %d bases" % (time.perf_counter() - t_load, batch.n_reads, batch.n_bases))
+    batch.cuda.dsb_index_device_bytes.restype = C.c_uint64
+    index_bytes = int(batch.cuda.dsb_index_device_bytes(batch.ix.handle))
+    log("index (%.2f GB on the device) + batch resident in %.1fs, %d reads %d bases" %
+        (index_bytes / 1e9, time.perf_counter() - t_load, batch.n_reads, batch.n_bases))
     first = batch.submit()                      # H2D + first pass (also sizes the scratch arenas)
     log("first pass: total %.1f ms (exist %.2f, classify %.1f)" % first)
     for _ in range(args.warmup):
@@ -400,12 +463,15 @@ def run_ours(args):
     sampler.active = True
     launches0 = batch.cuda.dsb_kernel_launch_count()
     ms_total = ms_exist = ms_classify = 0.0
+    stage = {"k_islands": 0.0, "k_seed": 0.0, "k_classify": 0.0}
     t0 = time.perf_counter()
     for _ in range(args.steps):
         a, b, c = batch.rerun()
         ms_total += a
         ms_exist += b
         ms_classify += c
+        for k in stage:
+            stage[k] += batch.stage_ms[k]
     wall = time.perf_counter() - t0
     sampler.active = False
     barrier(dist)
@@ -415,7 +481,18 @@ def run_ours(args):
     value = bases_all * args.steps / t_dev / 1e6
     counters = batch.counters
     d2h = batch.d2h_bytes()
+    # SURVEY 8(d)'s own definition: first H2D of the staged batch -> last D2H of the results, per step
+    n_sub = max(3, min(args.steps, 5))
+    ms_sub = 0.0
+    sampler.active = True
+    for _ in range(n_sub):
+        ms_sub += batch.submit()[0]
+    sampler.active = False
+    t_sub = max_over_ranks(dist, ms_sub * 1e-3 / n_sub)
     # end to end through the public API (every rank runs it; max over ranks)
+    n_reads, n_bases = batch.n_reads, batch.n_bases
+    h2d_bytes, split = batch.h2d_bytes, batch.split
+    batch.close()                               # the e2e leg brings its own index replica and slots
     e2e_s, n_sam = e2e_leg(meta, LOCAL_RANK, args.steps, args.warmup, sampler)
     barrier(dist)
     sampler.stop_flag = True
@@ -423,50 +500,122 @@ def run_ours(args):
     e2e_t = max_over_ranks(dist, e2e_s)
     e2e_value = bases_all / e2e_t / 1e6
     if RANK != 0:
-        batch.close()
+        barrier(dist)                           # rank 0 runs the single-process multi-GPU leg meanwhile
         return
-    alg = algorithmic_bytes(counters, batch.n_bases)
+    alg = algorithmic_bytes(counters, n_bases)
     k_ms = ms_classify / args.steps
+    stage = {k: v / args.steps for k, v in stage.items()}
     achieved = alg / (k_ms * 1e-3) / 1e9
-    traffic, traffic_src = ncu_traffic(batch.n_reads, batch.n_bases)
+    traffic, traffic_src = ncu_traffic(n_reads, n_bases)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": WORLD, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8/int64", "data": "synthetic",
-        "config": {"workload": WORKLOAD_TEXT + " per GPU (tools/dataset.py)",
-                   "n_reads_per_gpu": batch.n_reads, "n_bases_per_gpu": batch.n_bases, "parallelism": "reads sharded, index replicated, no collective",
-                   "l2": "inputs (%d MB ASCII + %d MB derived per step) and the index (>= 0.9 GB) exceed the 126 MB L2; no flush needed" %
-                         (batch.n_bases // 1000000, 4 * batch.n_bases // 1000000),
+        "config": {"workload": WORKLOAD_TEXT,
+                   "n_reads_per_gpu": n_reads, "n_bases_per_gpu": n_bases, "index_device_bytes": index_bytes,
+                   "parallelism": "reads sharded, index replicated, no collective",
+                   "value_scope": "inputs resident in HBM: k_encode, k_exist, k_islands, k_seed, k_classify + D2H of the results",
+                   "l2": "inputs (%d MB ASCII + %d MB derived per step) and the index (%.1f GB) exceed the 126 MB L2; no flush needed" %
+                         (n_bases // 1000000, 4 * n_bases // 1000000, index_bytes / 1e9),
                    "wall_ms_per_step": 1e3 * wall / args.steps},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": batch.h2d_bytes, "d2h_bytes_per_step": d2h,
+        "h2d_kernels_d2h": {"value": bases_all / t_sub / 1e6, "unit": UNIT, "ms_per_step": 1e3 * t_sub, "steps": n_sub,
+                            "scope": "SURVEY 8(d): pinned staging -> H2D -> kernels -> D2H of the results, CUDA events on the slot's stream"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h,
                 "api": "read_classify() of libdesamba.so: FASTQ text -> SAM_FULL text (%d bytes)" % n_sam,
                 "ms_per_step": 1e3 * e2e_t},
         "gpu_launches": launches,
         "kernel_ms": {"exist": ms_exist / args.steps, "classify": k_ms, "total": ms_total / args.steps,
-                      "classify_stages_last_step": batch.stage_ms if batch.split else None},
-        "roofline": {"bound": "hbm", "kernel": "classify stage = k_islands + k_seed + k_classify (the path's work counters span the three launches)" if batch.split else "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                      "classify_stages": stage if split else None},
+        "roofline": {"bound": "hbm", "kernel": "classify stage = k_islands + k_seed + k_classify (the path's work counters span the three launches)" if split else "k_classify", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes": alg, "peak_source": peak_src},
         "counters": counters,
         "clocks": sampler.result(),
     }
-    batch.close()
     if not args.no_fm_probe:
         try:
+            ra = random_access_peak(LOCAL_RANK)
+            line["roofline"]["random_access_peak"] = ra
+            line["roofline"]["frac_of_random_64B"] = achieved / ra["64B"]
+            if split:
+                line["fm_search_product"] = fm_search_product(counters, stage["k_seed"], ra, index_bytes)
             line["fm_search"] = fm_probe(None, LOCAL_RANK, hbm_peak)
-        except Exception as e:                                   # the probe is auxiliary: report, do not hide
+        except Exception as e:                                   # the probes are auxiliary: report, do not hide
             line["fm_search"] = {"error": str(e)}
     if not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         try:
-            gm = dataset.build(WORKLOAD, golden=True)
-            s, b = reference_run(gm, cores)
+            s, b, nr = reference_run(meta, cores)
             line["cpu_baseline"] = {"value": b / s / 1e6, "unit": UNIT, "cores": cores, "kind": "reference",
-                                    "sample": "all %d reads of the workload, oracle/_ref/deSAMBA classify -t %d, %.2fs, %s" %
-                                              (gm["n_reads"], cores, s, cpu_model())}
+                                    "sample": "the first %d reads of the workload (%d bases), oracle/_ref/deSAMBA classify -t %d, %.2fs, %s" %
+                                              (nr, b, cores, s, cpu_model())}
         except Exception as e:
             line["cpu_baseline"] = {"error": str(e)}
+    if WORLD > 1 and not args.no_inproc:
+        try:
+            line.update(inproc_leg(meta, WORLD, e2e_value / WORLD))
+        except Exception as e:
+            line["e2e_inproc"] = {"error": str(e)}
+    barrier(dist)
     emit(line)
+
+
+INPROC_CHILD = r'''
+import hashlib, json, os, sys, time
+sys.path.insert(0, os.path.join(sys.argv[1], "desamba-so_b200"))
+import pydsb
+idx, reads, sample, n_gpu, steps = sys.argv[2], sys.argv[3], sys.argv[4], int(sys.argv[5]), int(sys.argv[6])
+out = {}
+text = open(sample, "rb").read()
+md5 = {}
+for g in (1, n_gpu):
+    os.environ["DSB_GPUS"] = str(g)
+    os.environ["DSB_GPU_FIRST"] = "0"
+    d = pydsb.Desamba()
+    t0 = time.perf_counter()
+    d.load_index(idx)
+    out["load_index_s_%d_gpu" % g] = time.perf_counter() - t0
+    md5[g] = hashlib.md5(d.read_classify(text, thread_id=0, thread_num=1)).hexdigest()
+    if g == n_gpu:
+        one = open(reads, "rb").read()
+        n_bases = sum(len(l) for l in one.split(b"\n")[1::4])
+        big = one * n_gpu
+        del one
+        d.read_classify_timed(big, thread_id=1, thread_num=1)
+        dt = 0.0
+        for _ in range(steps):
+            t, n = d.read_classify_timed(big, thread_id=1, thread_num=1)
+            dt += t
+        out["ms_per_step"] = 1e3 * dt / steps
+        out["value"] = n_bases * n_gpu / (dt / steps) / 1e6
+        out["bases_per_step"] = n_bases * n_gpu
+        out["sam_bytes"] = n
+out["md5"] = {str(k): v for k, v in md5.items()}
+print("INPROC " + json.dumps(out))
+'''
+
+
+def inproc_leg(meta, n_gpu, e2e_per_gpu):
+    """One process, DSB_GPUS=N (SURVEY 8e / the north star's design: one host process shards the reads of a call over
+    the box's GPUs, index replicated by peer copy, results merged in read order on the host).  Run by rank 0 in a child
+    process while the other ranks wait at a barrier; not part of the timed region of `value` / `e2e`."""
+    sample, _nr, _nb = reference_sample(meta)
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
+        env.pop(k, None)
+    r = subprocess.run([sys.executable, "-c", INPROC_CHILD, ROOT, meta["idx"], meta["reads"], sample, str(n_gpu), "3"],
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
+    m = re.search(r"^INPROC (.*)$", r.stdout.decode(errors="replace"), re.M)
+    if r.returncode != 0 or not m:
+        raise RuntimeError("in-process leg failed: " + r.stderr.decode(errors="replace")[-600:])
+    o = json.loads(m.group(1))
+    return {"e2e_inproc": {"value": o["value"], "unit": UNIT, "n_gpus": n_gpu, "ms_per_step": o["ms_per_step"],
+                           "bases_per_step": o["bases_per_step"], "steps": 3,
+                           "vs_one_gpu_e2e": o["value"] / e2e_per_gpu if e2e_per_gpu else None,
+                           "load_index_s": {"1_gpu": o["load_index_s_1_gpu"], "%d_gpus" % n_gpu: o["load_index_s_%d_gpu" % n_gpu]},
+                           "api": "ONE process, read_classify() with DSB_GPUS=%d on %d x the per-GPU reads" % (n_gpu, n_gpu)},
+            "inproc_parity": o["md5"]["1"] == o["md5"][str(n_gpu)],
+            "inproc_md5": o["md5"]}
 
 
 def main():
@@ -477,6 +626,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-fm-probe", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-inproc", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

@@ -56,6 +56,8 @@ def parity_against_reference(name, max_undefined, env=None):
         with open(os.path.join(od, "parity_summary.jsonl"), "a") as fh:
             fh.write(json.dumps(line) + "\n")
     assert bad <= undefined, (name, sorted(bad - undefined)[:5])
+    # on a reference-undefined read our answer must still be the answer of ONE of the four builds of the reference
+    assert in_family == len(undefined), (name, in_family, len(undefined))
     assert len(undefined) <= max_undefined * len(want), (name, len(undefined))
     for t, v in info["twins"].items():                    # a twin that stopped early must still have judged most of the set
         assert v["reached"] >= 0.9 * len(want), (name, t, v)
