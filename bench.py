@@ -370,6 +370,8 @@ def fm_search_product(counters, k_seed_ms, ra, index_bytes):
     return {"kernel": "k_seed", "occ_queries": q, "counted_by": "seed_occ_queries" if counters.get("seed_occ_queries") else
             "occ_queries (k_seed + the slow-seeding path of k_classify)", "bytes_per_query": 64, "ms": k_seed_ms,
             "achieved": gbs, "unit": "GB/s", "random_64B_peak": ra["64B"], "frac_of_random_64B": gbs / ra["64B"],
+            "alg_bytes_all": counters.get("seed_alg_bytes"),
+            "achieved_all_bytes": (counters.get("seed_alg_bytes") or 0) / (k_seed_ms * 1e-3) / 1e9,
             "index_device_bytes": index_bytes}
 
 

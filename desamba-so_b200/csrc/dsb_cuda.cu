@@ -919,6 +919,9 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_SEED_MIN_BLOCKS) k_s
     DSB_FOLD_ADD(unitig_reads, w.st.unitig); DSB_FOLD_ADD(refpos_reads, w.st.refpos);
     DSB_FOLD_ADD(ref_window_bytes, w.st.ref_bytes); DSB_FOLD_ADD(mem_searches, w.st.mem_search);
     DSB_FOLD_ADD(map_seeds, w.st.map_seed);
+    DSB_FOLD_ADD(seed_occ_queries, w.st.occ);
+    DSB_FOLD_ADD(seed_alg_bytes, (unsigned long long)w.st.occ * 64ull + (unsigned long long)w.st.lut * 16ull +
+                                 ((unsigned long long)w.st.sa + w.st.unitig + w.st.refpos) * 8ull + w.st.ref_bytes);
 #undef DSB_FOLD_ADD
     if (lane == 0) atomicAdd((unsigned long long *)&cn->phase_cycles[1], cyc);
 #if defined(DSB_SEED_DIAG)

@@ -28,7 +28,7 @@ class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "exist_probes0", "exist_probes1", "occ_queries", "lut_lookups", "sa_lookups", "unitig_reads", "refpos_reads",
         "ref_window_bytes", "mem_searches", "map_seeds", "sdp_windows", "anchors", "slow_reads")] + [
-        ("phase_cycles", C.c_uint64 * 8)]
+        ("phase_cycles", C.c_uint64 * 8), ("seed_occ_queries", C.c_uint64), ("seed_alg_bytes", C.c_uint64)]
 
     def as_dict(self):
         d = {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "phase_cycles"}
@@ -56,32 +56,53 @@ class RunStats(C.Structure):
                 ("gpu_ms_total", C.c_double), ("gpu_ms_exist", C.c_double), ("gpu_ms_classify", C.c_double)]
 
 
-def lib_path(name, hostsim=False):
-    if hostsim:
-        return os.path.join(os.path.dirname(HERE), "tests", "hostsim", name.replace(".so", "_hostsim.so"))
+def lib_path(name):
     return os.path.join(LIB_DIR, name)
 
 
-def load_cuda_layer(hostsim=False):
-    p = lib_path("libdsb_cuda.so", hostsim) if not hostsim else os.path.join(os.path.dirname(HERE), "tests", "hostsim",
-                                                                          "libdsb_hostsim.so")
-    if not os.path.exists(p):
-        raise RuntimeError("%s is not built (run __graft_entry__.build())" % p)
-    lib = C.CDLL(p)
+def _load(path):
+    if not os.path.exists(path):
+        raise RuntimeError("%s is not built (run __graft_entry__.build())" % path)
+    return C.CDLL(path)
+
+
+def load_cuda_layer(path=None):
+    """libdsb_cuda.so, the sm_100a kernels behind include/dsb_cuda.h.  There is no other implementation in this package
+    (the tests' host simulator binds its own libraries from tests/hostsim/pydsb_hostsim.py)."""
+    lib = _load(path or lib_path("libdsb_cuda.so"))
     lib.dsb_last_error.restype = C.c_char_p
     lib.dsb_index_device_bytes.restype = C.c_uint64
+    lib.dsb_build_last_error.restype = C.c_char_p
     return lib
+
+
+def build_index(ref_fasta, out_dir, kmer_srt=None, dev=0, _cuda_lib=None):
+    """`deSAMBA index` through the C-ABI (dsb_index_build): returns the stats as a dict."""
+    class Stats(C.Structure):
+        _fields_ = [("n_ref", C.c_uint64), ("n_bases", C.c_uint64), ("n_kmer", C.c_uint64), ("n_unitig", C.c_uint64),
+                    ("n_rows", C.c_uint64), ("n_ref_pos", C.c_uint64), ("exist_table_bytes", C.c_uint64),
+                    ("exist_k", C.c_int32), ("kernel_launches", C.c_int32), ("peak_device_bytes", C.c_uint64),
+                    ("seconds", C.c_double), ("n_phases", C.c_int32), ("phase_name", (C.c_char * 40) * 32),
+                    ("phase_s", C.c_double * 32)]
+    cuda = load_cuda_layer(_cuda_lib)
+    st = Stats()
+    rc = cuda.dsb_index_build(ref_fasta.encode(), kmer_srt.encode() if kmer_srt else None, out_dir.encode(), dev, C.byref(st))
+    if rc != 0:
+        raise RuntimeError("dsb_index_build: " + cuda.dsb_build_last_error().decode())
+    d = {n: getattr(st, n) for n, _ in Stats._fields_[:11]}
+    d["phases"] = {st.phase_name[i].value.decode(): st.phase_s[i] for i in range(st.n_phases)}
+    return d
 
 
 class Desamba:
     """The three-symbol API, exactly as a C caller would use it (reference main_test.c:29-57)."""
 
-    def __init__(self, hostsim=False):
-        load_cuda_layer(hostsim)
-        p = lib_path("libdesamba.so", hostsim)
-        if not os.path.exists(p):
-            raise RuntimeError("%s is not built (run __graft_entry__.build())" % p)
-        self.lib = C.CDLL(p)
+    API_LIB = None          # overridden only by tests/hostsim/pydsb_hostsim.py
+    CUDA_LIB = None
+
+    def __init__(self):
+        load_cuda_layer(self.CUDA_LIB)
+        self.lib = _load(self.API_LIB or lib_path("libdesamba.so"))
         self.libc = C.CDLL(None)
         self.libc.free.argtypes = [C.c_void_p]
         self.lib.load_index.argtypes = [C.POINTER(C.c_void_p), C.c_char_p]
@@ -136,11 +157,14 @@ class Desamba:
 class DeviceIndex:
     """Index loaded by the C host loader and made resident through the CUDA C-ABI (or the host simulator)."""
 
-    def __init__(self, index_dir, dev=0, hostsim=False):
+    API_LIB = None
+    CUDA_LIB = None
+
+    def __init__(self, index_dir, dev=0):
         import numpy as np
         self.np = np
-        self.cuda = load_cuda_layer(hostsim)
-        self.host = C.CDLL(lib_path("libdesamba.so", hostsim))
+        self.cuda = load_cuda_layer(self.CUDA_LIB)
+        self.host = _load(self.API_LIB or lib_path("libdesamba.so"))
         self.buf = C.create_string_buffer(1 << 16)          # dsb_loaded_index (its first member is dsb_host_index)
         self.host.dsb_index_load(self.buf, index_dir.encode(), 170, 64)
         self.handle = C.c_void_p()
@@ -253,12 +277,12 @@ class _SyntheticIndex(DeviceIndex):
         return self._ek_bytes
 
 
-def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3, ek_table=None):
+def synthetic_fm_index(n_sym, dev=0, seed=3, ek_table=None, _libs=(None, None)):
     """A device index whose FM part is a random BWT of n_sym symbols in the reference's 168-byte block layout
     (counts are consistent inside a block, which is all a rank query reads).  Only dsb_fm_rank_batch is
     meaningful on it: it exists to measure rank-query throughput on a table far larger than L2."""
     import numpy as np
-    cuda = load_cuda_layer(hostsim)
+    cuda = load_cuda_layer(_libs[1])
     rng = np.random.default_rng(seed)
     nb = n_sym // 256
     blocks = np.zeros((nb, 168), dtype=np.uint8)
@@ -288,6 +312,6 @@ def synthetic_fm_index(n_sym, dev=0, hostsim=False, seed=3, ek_table=None):
     if rc != 0:
         raise RuntimeError("dsb_index_upload: " + cuda.dsb_last_error().decode())
     ix = _SyntheticIndex(handle, cuda, keep)
-    ix.host = C.CDLL(lib_path("libdesamba.so", hostsim))
+    ix.host = _load(_libs[0] or lib_path("libdesamba.so"))
     ix._ek_bytes = len(keep["ek"])
     return ix

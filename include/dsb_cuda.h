@@ -116,6 +116,9 @@ typedef struct dsb_counters {
      * 0 islands, 1 fast seeding, 2 chaining, 3 slow seeding, 4 read 9-mer table, 5 chain scoring,
      * 6 filters + primary, 7 result write-back */
     uint64_t phase_cycles[8];
+    /* k_seed's own share of the counts above (the FM-search kernel of the split pipeline): its rank queries, and its
+     * algorithmic bytes = 64 x rank queries + 16 x LUT pairs + 8 x (SA + unitig + REF_POS reads) + reference-window bytes */
+    uint64_t seed_occ_queries, seed_alg_bytes;
 } dsb_counters;
 
 typedef struct dsb_slot dsb_slot;  /* one CUDA stream + pinned staging + device scratch */

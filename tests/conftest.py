@@ -9,6 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "desamba-so_b200")
 sys.path.insert(0, PKG)
 sys.path.insert(0, os.path.join(ROOT, "tools"))
+sys.path.insert(0, os.path.join(ROOT, "tests", "hostsim"))
 GOLD = os.path.join(ROOT, "tests", "golden")
 
 

@@ -9,6 +9,8 @@ import subprocess
 
 import pytest
 
+import pydsb_hostsim
+
 from conftest import GOLD, PKG, ROOT, sam_records
 
 SIM = os.path.join(ROOT, "tests", "hostsim", "deSAMBA_hostsim")
@@ -98,7 +100,7 @@ def test_gzip_and_fasta_inputs(tiny, tmp_path):
 def test_api_read_classify_through_hostsim_library(tiny):
     """read_classify(): text input, path input, empty input, history carried across calls per thread_id."""
     import pydsb
-    d = pydsb.Desamba(hostsim=True)
+    d = pydsb_hostsim.Desamba()
     d.load_index(tiny["idx"])
     text = open(tiny["reads"], "rb").read()
     recs = text.split(b"\n")
@@ -196,7 +198,7 @@ def test_meta_analysis_equals_reference(tiny, mixed, have_ref_binary):
         return b"\n".join(out) + b"\n"
     cases += [mutated(k) for k in range(6)] + [sam.rstrip(b"\n")]
     cases.append(full * 3)              # > 4 MB: read by several threads (pieces cut at line ends, joined in order)
-    d = pydsb.Desamba(hostsim=True)
+    d = pydsb_hostsim.Desamba()
     d.load_index(tiny["idx"])
     for flag in (0, 1):
         for snap in (65536, 1000, 0):          # 0: some human bases -> an empty block, not NULL
@@ -280,7 +282,7 @@ def test_resident_index_call_sequence_through_hostsim(mixed, have_ref_binary):
     slices = fastq_slices(mixed["reads"], 5)
     slices = slices + slices[:2]
     want = ref_resident_session(mixed["idx"], slices, 1, 65536)
-    d = pydsb.Desamba(hostsim=True)
+    d = pydsb_hostsim.Desamba()
     d.load_index(mixed["idx"])
     for i, (fq, (w_sam, w_meta, w_snap)) in enumerate(zip(slices, want)):
         sam = d.read_classify(fq, thread_id=7, thread_num=1)
@@ -299,7 +301,7 @@ def test_api_splice_formatter_equals_cli_formatter(mixed, tmp_path):
     fa_path = str(tmp_path / "reads.fa")
     open(fa_path, "wb").write(fa)
     for data, path in ((fq, mixed["reads"]), (fa, fa_path)):
-        d = pydsb.Desamba(hostsim=True)
+        d = pydsb_hostsim.Desamba()
         d.load_index(mixed["idx"])
         assert d.read_classify(data, thread_id=3) == run_sim(mixed["idx"], [path], fmt="SAM_FULL")
 
@@ -338,7 +340,7 @@ def test_reblocked_fm_rank_equals_reference_occ_for_every_symbol(tiny):
     ci = np.frombuffer(raw, dtype=np.uint8, count=n, offset=o); o += n
     co = np.frombuffer(raw, dtype=np.uint8, count=n, offset=o); o += n
     res = np.frombuffer(raw, dtype=np.uint64, count=n, offset=o)
-    ix = pydsb.DeviceIndex(tiny["idx"], hostsim=True)
+    ix = pydsb_hostsim.DeviceIndex(tiny["idx"])
     got, c_out, _ms = ix.fm_rank(r, ci)
     ix.close()
     assert (c_out == co).all() and (got == res).all()
@@ -366,7 +368,7 @@ def _concurrent_calls(lib_kind, tiny, mixed_reads=None):
     """two caller threads, distinct thread_ids, the same resident index (reference contract: src/cly_mt.c:1279-1307)"""
     import threading
     import pydsb
-    d = pydsb.Desamba(hostsim=(lib_kind == "hostsim"))
+    d = (pydsb_hostsim.Desamba() if lib_kind == "hostsim" else pydsb.Desamba())
     d.load_index(tiny["idx"])
     text = open(tiny["reads"], "rb").read()
     res = {}
@@ -423,11 +425,11 @@ def test_text_shapes_of_the_api_input_equal_reference_library(mixed, have_ref_bi
     cases = [plain, plain + b"\0", plain.rstrip(b"\n"), plain.replace(b"\n", b"\r\n"), multi, plain.replace(b"\n@", b"\n\n@", 5)]
     for text in cases:
         want = ref_resident_session(mixed["idx"], [text], 1, 65536)[0][0]
-        d = pydsb.Desamba(hostsim=True)
+        d = pydsb_hostsim.Desamba()
         d.load_index(mixed["idx"])
         assert d.read_classify(text, thread_id=7) == want
     want = sam_records(ref_resident_session(mixed["idx"], [fasta], 1, 65536)[0][0])
-    d = pydsb.Desamba(hostsim=True)
+    d = pydsb_hostsim.Desamba()
     d.load_index(mixed["idx"])
     got = sam_records(d.read_classify(fasta, thread_id=7))
     assert len(got) == 60 and len(want) == 30
@@ -457,7 +459,7 @@ def test_rejected_fastq_records_follow_the_reference_pipeline(mixed, have_ref_bi
     n_lines = []
     for t in cases:
         want = ref_resident_session(mixed["idx"], [t], 1, 65536)[0][0]
-        d = pydsb.Desamba(hostsim=True)
+        d = pydsb_hostsim.Desamba()
         d.load_index(mixed["idx"])
         assert d.read_classify(t, thread_id=7) == want
         n_lines.append(want.count(b"\n"))
@@ -475,7 +477,7 @@ def test_thread_num_change_restarts_the_buffer_history(mixed, have_ref_binary):
     sl = fastq_slices(mixed["reads"], 5)
     calls = [(sl[0], 7, 1), (sl[1], 7, 1), (sl[2], 7, 3), (sl[3], 7, 1), (sl[4], 7, 1), (sl[1], 7, 1)]
     want = ref_call_sequence(mixed["idx"], calls)
-    d = pydsb.Desamba(hostsim=True)
+    d = pydsb_hostsim.Desamba()
     d.load_index(mixed["idx"])
     for i, (fq, tid, tn) in enumerate(calls):
         got = d.read_classify(fq, thread_id=tid, thread_num=tn)
