@@ -1591,19 +1591,72 @@ DSB_HD int dsb_read_hash_key_len(uint32_t L)
     return key_len;
 }
 
-// Bucket heads of the read's 9-mer table hold position + 1.  Reads shorter than 65 535 bases keep them in 16 bits (half
-// the heads' random-access footprint: classify stage 10.34 -> 10.07 ms in a same-box A/B, output identical); longer reads
-// use 32 bits in the same arena.  -DDSB_NO_HEAD16 keeps 32 bits throughout.  (Prefetching the heads one to three chunks
-// ahead while the table is built changed nothing: 10.32-10.41 ms.)
-#if !defined(DSB_NO_HEAD16) && defined(DSB_DEVICE_CODE)
-#define DSB_HEAD_GET(head, narrow, k) ((narrow) ? (uint32_t)((const uint16_t *)(head))[k] : (head)[k])
-#define DSB_HEAD_SET(head, narrow, k, v) do { if (narrow) ((uint16_t *)(head))[k] = (uint16_t)(v); else (head)[k] = (v); } while (0)
-#define DSB_HEAD_NARROW(L) ((L) < 65535u)
-#else
-#define DSB_HEAD_GET(head, narrow, k) ((head)[k])
-#define DSB_HEAD_SET(head, narrow, k, v) do { (head)[k] = (v); } while (0)
-#define DSB_HEAD_NARROW(L) false
+// The read's 9-mer table is BLOCKED BY READ POSITION: segment g holds the positions [g << DSB_SEG_BITS, (g + 1) << DSB_SEG_BITS)
+// in its own 2^DSB_SEG_BITS buckets (key = low bits of the 9-mer, the tag in the entry = the remaining bits, so a tag match is
+// an exact 9-mer match).  The reference's table (src/cly.c:2168-2219) is one hash over the whole read; its results depend only
+// on, per window 9-mer, the matching read positions inside [q_bg, q_ed] in ASCENDING order (chains are appended at the tail,
+// :2206-2215) -- the bucket width is free.  A scoring window only asks for positions within ~2000 bases of the chain's end
+// (sdp_right / sdp_left / sdp_middle), i.e. 2-3 segments: its loads stay inside ~6 KB per segment (heads 2 B, entries 4 B)
+// instead of being spread over the whole 70 KB table of a 10 kb read, which every resident warp evicted from L1 / L2 between
+// two uses (round 1: 5.7 GB of DRAM traffic per step for 0.27 GB of algorithmic bytes).  Same-box A/B on the 1 Gbp / 10 kb
+// workload (profiles/ab_r02.txt): k_classify 171.6 -> 165.3 ms with 2048-position segments (1024: 166.5, 4096: 167.5), output
+// identical.  Tried on top and dropped, all slower in the same runs: first entry's tag + a has-next bit inlined in 32-bit
+// heads (one load instead of head -> entry for most look-ups: 190 ms, the heads double and the cursor grows), 4 / 8
+// segments built in an interleaved fashion (181 / 188 ms: register arrays under the kernel's 80-register cap), word-wide
+// exact-run extension of the hits (166.8 ms).
+//   head16[g * SEG + key] = (position inside the segment) + 1, 0 = empty bucket
+//   ent[p]                = (next position in the bucket + 1) << 8 | tag       (positions ascending along a chain)
+#ifndef DSB_SEG_BITS
+#define DSB_SEG_BITS 11
 #endif
+#define DSB_SEG (1u << DSB_SEG_BITS)
+#define DSB_SEG_MASK (DSB_SEG - 1u)
+#if DSB_SEG_BITS < 10 || DSB_SEG_BITS > 15
+#error "DSB_SEG_BITS: the tag (18 - DSB_SEG_BITS bits) must fit 8 bits and a local position + 1 must fit 16 bits"
+#endif
+
+// cursor over the hits of one window 9-mer: ascending read positions p with 9-mer(p) == kmer and q_bg <= p <= q_ed
+struct DsbTabCur { uint32_t node, seg, seg_hi, key, tag; };
+
+// advance from the candidate c->node (0 = bucket exhausted) to the next entry that matches; returns position + 1 or 0
+DSB_HD uint32_t dsb_tab_settle(const uint16_t *head, const uint32_t *ent, DsbTabCur *c, uint32_t q_bg, uint32_t q_ed)
+{
+    uint32_t node = c->node;
+    for (;;) {
+        while (node != 0) {
+            const uint32_t qp = node - 1;
+            if (qp > q_ed) { node = 0; c->seg = c->seg_hi; break; }      // chains ascend: nothing further can be in range
+            const uint32_t e = ent[qp];
+            if ((e & 0xffu) == c->tag && qp >= q_bg) { c->node = node; return node; }
+            node = e >> 8;
+        }
+        if (c->seg >= c->seg_hi) { c->node = 0; return 0; }
+        c->seg++;
+        const uint32_t h = head[(c->seg << DSB_SEG_BITS) + c->key];
+        node = h ? (c->seg << DSB_SEG_BITS) + h : 0u;
+    }
+}
+
+// first hit of `kmer` in [q_bg, q_ed]; n_pos = number of positions the table holds
+DSB_HD uint32_t dsb_tab_first(const uint16_t *head, const uint32_t *ent, DsbTabCur *c, uint32_t kmer, uint32_t q_bg, uint32_t q_ed,
+                              uint32_t n_pos)
+{
+    c->key = kmer & DSB_SEG_MASK;
+    c->tag = kmer >> DSB_SEG_BITS;
+    c->node = 0;
+    if (q_bg > q_ed || q_bg >= n_pos) { c->seg = c->seg_hi = 0; return 0; }     // a wrapped q_bg matches nothing
+    c->seg = q_bg >> DSB_SEG_BITS;
+    c->seg_hi = (q_ed < n_pos ? q_ed : n_pos - 1) >> DSB_SEG_BITS;
+    const uint32_t h = head[(c->seg << DSB_SEG_BITS) + c->key];
+    c->node = h ? (c->seg << DSB_SEG_BITS) + h : 0u;
+    return dsb_tab_settle(head, ent, c, q_bg, q_ed);
+}
+
+DSB_HD uint32_t dsb_tab_next(const uint16_t *head, const uint32_t *ent, DsbTabCur *c, uint32_t q_bg, uint32_t q_ed)
+{
+    c->node = ent[c->node - 1] >> 8;
+    return dsb_tab_settle(head, ent, c, q_bg, q_ed);
+}
 
 DSB_HD uint32_t dsb_kmer9(const uint8_t *s)
 {
@@ -1620,48 +1673,52 @@ DSB_HDN int dsb_build_read_hash(DsbWork *w)
         if (both_dir == 3) break;
     }
     const int q_len = (int)w->L;
-    const int key_len = dsb_read_hash_key_len((uint32_t)q_len);
-    const uint32_t key_mask = (1u << key_len) - 1u;
+    const int key_len = DSB_SEG_BITS;
     const uint32_t n_pos = (uint32_t)(q_len - DSB_KMER9 + 1);
-    if (w->L >= (1u << 24)) { w->overflow = 16; return key_len; }     // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes)
+    const uint32_t n_head = ((n_pos + DSB_SEG_MASK) >> DSB_SEG_BITS) << DSB_SEG_BITS;
+    if (w->L >= (1u << 24)) { w->overflow = 16; return key_len; }    // entries hold 24-bit positions (the reference's own table stops at 1 Mi nodes); its own flag: the host rejects such reads before they get here
     for (int c_dir = 2; c_dir >= 1; c_dir--) {
         if ((c_dir & both_dir) == 0) continue;
         const int strand = (c_dir == 2) ? 0 : 1;
         const uint8_t *q = w->bin + (strand ? w->L : 0);
-        uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
+        uint16_t *head = (uint16_t *)w->h_head[strand];
+        uint32_t *ent = w->h_ent[strand];
 #if defined(DSB_DEVICE_CODE)
         const uint32_t lane = threadIdx.x & 31;
-        const bool narrow = DSB_HEAD_NARROW(w->L);
-        if (narrow) { for (uint32_t i = lane; i <= (key_mask >> 1); i += 32) head[i] = 0; }
-        else for (uint32_t i = lane; i <= key_mask; i += 32) head[i] = 0;
+        for (uint32_t i = lane; i < (n_head >> 1); i += 32) ((uint32_t *)head)[i] = 0;
         __syncwarp();
         // Buckets must list positions in ascending order (the reference appends to the tail).  32
-        // positions per step, from the highest chunk down: inside a chunk, lanes with the same key
-        // (match_any) link to the next higher lane of their group; the group's highest lane links to
-        // the bucket head left by the chunks above, its lowest lane becomes the new head.
+        // positions per step, from the highest chunk down (a chunk never straddles a segment): inside a chunk,
+        // lanes with the same key (match_any) link to the next higher lane of their group; the group's highest
+        // lane links to the bucket head left by the chunks above, its lowest lane becomes the new head.
         for (int32_t cs = (int32_t)((n_pos - 1) & ~31u); cs >= 0; cs -= 32) {
             const uint32_t p = (uint32_t)cs + lane;
             const bool valid = p < n_pos;
             const uint32_t km = valid ? dsb_kmer9(q + p) : 0u;
-            const uint32_t key = valid ? (km & key_mask) : (0x80000000u | lane);
+            const uint32_t seg_base = (uint32_t)cs & ~DSB_SEG_MASK;
+            const uint32_t key = valid ? (km & DSB_SEG_MASK) : (0x80000000u | lane);
             const uint32_t peers = __match_any_sync(0xffffffffu, key);
             const uint32_t higher = peers & ~((2u << lane) - 1u);
             uint32_t nx = 0;
-            if (valid) nx = higher ? ((uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u) : DSB_HEAD_GET(head, narrow, key);
+            if (valid) {
+                if (higher) nx = (uint32_t)cs + (uint32_t)__ffs((int)higher) - 1u + 1u;
+                else { const uint32_t h = head[seg_base + key]; nx = h ? seg_base + h : 0u; }
+            }
             __syncwarp();
             if (valid) {
-                ent[p] = (nx << 8) | (km >> key_len);
-                if ((peers & ((1u << lane) - 1u)) == 0) DSB_HEAD_SET(head, narrow, key, p + 1);
+                ent[p] = (nx << 8) | (km >> DSB_SEG_BITS);
+                if ((peers & ((1u << lane) - 1u)) == 0) head[seg_base + key] = (uint16_t)((p & DSB_SEG_MASK) + 1u);
             }
             __syncwarp();
         }
 #else
-        for (uint32_t i = 0; i <= key_mask; i++) head[i] = 0;
+        for (uint32_t i = 0; i < n_head; i++) head[i] = 0;
         for (uint32_t p = n_pos; p-- > 0;) {
             const uint32_t km = dsb_kmer9(q + p);
-            const uint32_t key = km & key_mask;
-            ent[p] = (head[key] << 8) | (km >> key_len);
-            head[key] = p + 1;
+            const uint32_t seg_base = p & ~DSB_SEG_MASK, key = km & DSB_SEG_MASK;
+            const uint32_t h = head[seg_base + key];
+            ent[p] = ((h ? seg_base + h : 0u) << 8) | (km >> DSB_SEG_BITS);
+            head[seg_base + key] = (uint16_t)((p & DSB_SEG_MASK) + 1u);
         }
 #endif
     }
@@ -1752,11 +1809,11 @@ DSB_HD bool dsb_extend_hit(const uint8_t *q_str, const uint8_t *t_str, uint32_t 
 DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8_t *q_str, const uint8_t *t_str,
                            uint32_t t_len, int key_len, int strand, uint32_t t_st, bool is_forward)
 {
-    const uint32_t key_mask = (1u << key_len) - 1u;
+    (void)key_len;
     const uint32_t t_kmer_num = t_len - DSB_KMER9 + 1;
-    const uint32_t *head = w->h_head[strand], *ent = w->h_ent[strand];
-    const bool narrow = DSB_HEAD_NARROW(w->L);
-    (void)narrow;
+    const uint16_t *head = (const uint16_t *)w->h_head[strand];
+    const uint32_t *ent = w->h_ent[strand];
+    const uint32_t n_pos = w->L - DSB_KMER9 + 1;
     w->st.sdp_win++;
 #if defined(DSB_DEVICE_CODE)
     {
@@ -1770,17 +1827,9 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             const uint32_t mine = base + lane;
             const int i_l = 4 + 4 * (int)mine;
             const long off_l = is_forward ? (long)i_l : ((long)t_len - DSB_KMER9 - (long)i_l);
-            uint32_t kmer = 0, node = 0;
-            if (mine < n_i) {
-                kmer = dsb_kmer9(t_str + off_l);
-                node = DSB_HEAD_GET(head, narrow, kmer & key_mask);
-                while (node != 0) {
-                    const uint32_t qp = node - 1;
-                    const uint32_t e = ent[qp];
-                    if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
-                    node = e >> 8;
-                }
-            }
+            uint32_t node = 0;
+            DsbTabCur cur = {0, 0, 0, 0, 0};
+            if (mine < n_i) node = dsb_tab_first(head, ent, &cur, dsb_kmer9(t_str + off_l), q_bg, q_ed, n_pos);
             if (!__any_sync(0xffffffffu, node != 0)) continue;
             // Every hit is an independent computation (two exact-run extensions); only the ORDER of the
             // match-block list couples them (window position, then bucket order).  So each lane extends
@@ -1790,6 +1839,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             {
                 DsbSms *my = w->sms_stage + lane * DSB_SMS_LANE_CAP;
                 uint32_t cnt = 0, nd = node;
+                DsbTabCur c2 = cur;                           // the serial path below restarts from `cur`
                 while (nd != 0 && cnt <= DSB_SMS_LANE_CAP) {
                     const uint32_t q_pos = nd - 1;
                     uint32_t o_t = 0, o_q = 0, o_len = 0;
@@ -1798,13 +1848,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                         if (cnt < DSB_SMS_LANE_CAP) { my[cnt].t_pos = o_t; my[cnt].q_pos = o_q; my[cnt].len = o_len; }
                         cnt++;
                     }
-                    nd = ent[q_pos] >> 8;
-                    while (nd != 0) {
-                        const uint32_t qp = nd - 1;
-                        const uint32_t e = ent[qp];
-                        if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
-                        nd = e >> 8;
-                    }
+                    nd = dsb_tab_next(head, ent, &c2, q_bg, q_ed);
                 }
                 if (!__any_sync(0xffffffffu, cnt > DSB_SMS_LANE_CAP)) {
                     uint32_t pre = cnt;                       // inclusive prefix sum of the lanes' counts
@@ -1852,15 +1896,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                                 dsb_push_sms(w, (uint32_t)(c_off - back_len + (long)t_st), q_pos - (uint32_t)back_len, (uint32_t)total_len);
                         }
                     }
-                    if ((int)lane == l) {                     // the owner moves to its next hit
-                        node = ent[q_pos] >> 8;
-                        while (node != 0) {
-                            const uint32_t qp = node - 1;
-                            const uint32_t e = ent[qp];
-                            if ((e & 0xffu) == (kmer >> key_len) && qp >= q_bg && qp <= q_ed) break;
-                            node = e >> 8;
-                        }
-                    }
+                    if ((int)lane == l) node = dsb_tab_next(head, ent, &cur, q_bg, q_ed);   // the owner moves to its next hit
                     __syncwarp();
                 }
                 act &= ~(1u << l);
@@ -1872,11 +1908,11 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
     if (is_forward) {
         for (int i = 4; (uint32_t)i < t_kmer_num; i += 4) {
             const uint8_t *c_t_str = t_str + i;
-            const uint32_t kmer = dsb_kmer9(c_t_str);
-            uint32_t node = head[kmer & key_mask];
+            DsbTabCur cur;
+            uint32_t node = dsb_tab_first(head, ent, &cur, dsb_kmer9(c_t_str), q_bg, q_ed, n_pos);
             while (node != 0) {
                 const uint32_t q_pos = node - 1;
-                if ((ent[q_pos] & 0xffu) == (kmer >> key_len) && q_pos >= q_bg && q_pos <= q_ed) {
+                {
                     const int back_len = dsb_run_len(q_str + q_pos - 1, c_t_str - 1, false, 4);
                     if (back_len < 4 || i == 4) {
                         uint32_t max_search = q_ed - q_pos - 1;
@@ -1887,18 +1923,18 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                             dsb_push_sms(w, (uint32_t)(i - back_len) + t_st, q_pos - (uint32_t)back_len, (uint32_t)total_len);
                     }
                 }
-                node = ent[q_pos] >> 8;
+                node = dsb_tab_next(head, ent, &cur, q_bg, q_ed);
             }
         }
     } else {
         for (int i = 4; (uint32_t)i < t_kmer_num; i += 4) {
             const long c_off = (long)t_len - DSB_KMER9 - (long)i;       // c_t_str - t_str
             const uint8_t *c_t_str = t_str + c_off;
-            const uint32_t kmer = dsb_kmer9(c_t_str);
-            uint32_t node = head[kmer & key_mask];
+            DsbTabCur cur;
+            uint32_t node = dsb_tab_first(head, ent, &cur, dsb_kmer9(c_t_str), q_bg, q_ed, n_pos);
             while (node != 0) {
                 const uint32_t q_pos = node - 1;
-                if ((ent[q_pos] & 0xffu) == (kmer >> key_len) && q_pos >= q_bg && q_pos <= q_ed) {
+                {
                     const int forward_len = dsb_run_len(q_str + q_pos + DSB_KMER9, c_t_str + DSB_KMER9, true, 4);
                     if (forward_len < 4 || i == 4) {
                         uint32_t max_search = q_pos;
@@ -1909,7 +1945,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
                             dsb_push_sms(w, (uint32_t)(c_off - back_len + (long)t_st), q_pos - (uint32_t)back_len, (uint32_t)total_len);
                     }
                 }
-                node = ent[q_pos] >> 8;
+                node = dsb_tab_next(head, ent, &cur, q_bg, q_ed);
             }
         }
     }

@@ -1148,6 +1148,23 @@ __global__ void __launch_bounds__(256) k_fm_reblock(const uint64_t *__restrict__
     }
 }
 
+// L2 fetch granularity of the device (a hint): the path's index accesses are single 32-byte sectors (exist probes) and
+// 64-byte FM blocks at random places.  DSB_L2_FETCH=32|64|128 asks for a value (A/B runs); DSB_VERBOSE prints what the device
+// reports.  Measured on B200 (profiles/l2_fetch_r02.txt): no setting changes the time or the DRAM bytes of the probes.
+static void dsb_apply_l2_fetch_env(void)
+{
+    const char *e = getenv("DSB_L2_FETCH");
+    size_t before = 0, got = 0;
+    cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
+    cudaError_t rc = cudaSuccess;
+    if (e && atoi(e) > 0) rc = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
+    cudaDeviceGetLimit(&got, cudaLimitMaxL2FetchGranularity);
+    if (getenv("DSB_VERBOSE"))
+        fprintf(stderr, "[dsb] L2 fetch granularity: device default %zu, asked %s (%s), now %zu\n", before, e ? e : "-",
+                cudaGetErrorString(rc), got);
+    cudaGetLastError();
+}
+
 template <typename T>
 static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_zero, const T **out)
 {
@@ -1194,6 +1211,7 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
         g_err = "device is not sm_100-class; this library carries sm_100a code only";
         return -1;
     }
+    dsb_apply_l2_fetch_env();
     dsb_index *ix = new dsb_index();
     ix->dev = dev;
     ix->bytes = 0;
@@ -1692,6 +1710,7 @@ int dsb_random_access_probe(int dev, uint64_t table_bytes, uint32_t chunk_bytes,
 {
     CU(cudaSetDevice(dev));
     if (chunk_bytes != 32 && chunk_bytes != 64 && chunk_bytes != 128) { g_err = "chunk_bytes must be 32, 64 or 128"; return -1; }
+    dsb_apply_l2_fetch_env();
     cudaDeviceProp prop;
     CU(cudaGetDeviceProperties(&prop, dev));
     uint4 *table = nullptr;

@@ -40,7 +40,7 @@ struct DsbScratchDims {
     uint32_t Lmax;          // longest read of the batch
     uint32_t cap_anchor;    // anchors == chains == sort buffers capacity
     uint32_t cap_sms;
-    uint32_t head_entries;  // 2^key_len for Lmax
+    uint32_t head_entries;  // 16-bit bucket heads of the position-blocked 9-mer table: Lmax rounded up to whole segments
     uint32_t cap_jobs;      // top islands of both strands (<= L/100 + 1 each)
     uint32_t cap_stage;     // anchors one lane may stage during fast seeding
     // byte offsets inside a slice
@@ -58,7 +58,7 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     d->Lmax = Lmax;
     d->cap_anchor = cap_anchor;
     d->cap_sms = cap_sms;
-    d->head_entries = 1u << dsb_read_hash_key_len(Lmax);
+    d->head_entries = ((Lmax + DSB_SEG_MASK) >> DSB_SEG_BITS) << DSB_SEG_BITS;
     size_t o = 0;
 #define DSB_TAKE(field, nbytes) d->field = o; o = dsb_align_up(o + (nbytes), 64)
     const size_t n_seed = (size_t)(Lmax / 4) + 8;       // < L/4 islands per strand
@@ -80,8 +80,8 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     DSB_TAKE(o_lane_priv, (size_t)32 * DSB_LANE_PRIV_BYTES);
     DSB_TAKE(o_sms_stage, (size_t)32 * DSB_SDP_STAGE * sizeof(DsbSms));
     DSB_TAKE(o_sms, (size_t)cap_sms * sizeof(DsbSms));
-    DSB_TAKE(o_head0, (size_t)d->head_entries * 4);
-    DSB_TAKE(o_head1, (size_t)d->head_entries * 4);
+    DSB_TAKE(o_head0, (size_t)d->head_entries * 2 + 64);
+    DSB_TAKE(o_head1, (size_t)d->head_entries * 2 + 64);
     DSB_TAKE(o_ent0, (size_t)Lmax * 4);
     DSB_TAKE(o_ent1, (size_t)Lmax * 4);
     DSB_TAKE(o_sc_hash, (256 + 2 * 400 + 8) * sizeof(DsbScHash));

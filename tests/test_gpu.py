@@ -184,7 +184,48 @@ def test_cfg3_headline_index_against_reference(have_ref_binary):
     20 000 reads of the bench set against the unmodified reference's `classify -t 1` on the same index."""
     if not have_ref_binary:
         pytest.skip("reference binary absent")
-    parity_against_reference("cfg3", 0.05)
+    meta, out = parity_against_reference("cfg3", 0.05)
+    placed_where_simulated(meta, out, 0.9)
+
+
+def placed_where_simulated(meta, sam_text, min_share):
+    """The C simulator names a read r<i>_g<genome>_<start>_<strand>: the PRIMARY record of a classified read must name that
+    genome's reference (or a strain of the same family: strains differ by 1 % SNPs, ties between them are legitimate) at the
+    simulated position (+-10 % of the read length for indels).  A check of the INDEX's content that parity with the reference
+    cannot give, because both sides read the same index files."""
+    import re
+    ok = n = 0
+    for line in sam_text.decode().split("\n"):
+        f = line.split("\t")
+        if len(f) < 6 or (int(f[1]) & 0x900):
+            continue
+        m = re.match(r"r\d+_g(\d+)_(\d+)_([+-])$", f[0])
+        if not m or f[2] == "*":
+            continue
+        g, st = int(m.group(1)), int(m.group(2))
+        r = re.search(r"SYN_(\d+)", f[2])
+        n += 1
+        clip = re.match(r"(-?\d+)S", f[5])
+        lead = int(clip.group(1)) if clip else 0
+        if r and int(r.group(1)) // 5 == g // 5 and abs(int(f[3]) - lead * (m.group(3) == "+") - st) <= 2000:
+            ok += 1
+    assert n > 0
+    print("placed where simulated: %d of %d primary records (%.1f %%)" % (ok, n, 100.0 * ok / n))
+    assert ok >= min_share * n, (ok, n)
+
+
+def test_cfg3x_full_scale_index_against_reference(have_ref_binary):
+    """BASELINE.json configs[2] at its own index size: 4 Gbp reference (800 families x 5 strains x 1 Mbp), BWT 3.8 G rows (the
+    reference's FM array is 2.5 GB, the SA samples 3.8 GB, the exist tables 2 x 1 GiB with k = 18), built on this box by OUR
+    index builder in seconds; 5 000 ONT-like 10 kb reads against the unmodified reference's `classify -t 1` on that index, and
+    the reads must land where they were simulated from."""
+    if not have_ref_binary:
+        pytest.skip("reference binary absent")
+    import shutil
+    if shutil.disk_usage("/tmp").free < (40 << 30):
+        pytest.skip("less than 40 GB free under /tmp")
+    meta, out = parity_against_reference("cfg3x", 0.05)
+    placed_where_simulated(meta, out, 0.9)
 
 
 def test_length_error_sweep_against_reference(have_ref_binary):

@@ -17,9 +17,9 @@ d = pydsb.Desamba(); d.load_index(m["idx"])
 print("$v", hashlib.md5(d.read_classify(open(m["reads"], "rb").read(), thread_id=0, thread_num=1)).hexdigest(), flush=True)
 P
     fi
-    env $v python bench.py --steps 10 --warmup 3 --no-fm-probe --no-cpu-baseline > gpurun_out/abe_${i}_$round.json 2> gpurun_out/abe_$i.err || tail -5 gpurun_out/abe_$i.err
+    env $v python bench.py --steps 5 --warmup 3 --no-fm-probe --no-cpu-baseline > gpurun_out/abe_${i}_$round.json 2> gpurun_out/abe_$i.err || tail -5 gpurun_out/abe_$i.err
     python -c "
 import json; d=json.loads(open('gpurun_out/abe_${i}_$round.json').read().strip().splitlines()[-1])
-print('$v', $round, 'classify %.2f total %.2f e2e %.2f' % (d['kernel_ms']['classify'], d['kernel_ms']['total'], d['e2e']['ms_per_step']), d['kernel_ms'])"
+print('$v', $round, 'exist %.2f classify %.2f total %.2f e2e %.2f' % (d['kernel_ms']['exist'], d['kernel_ms']['classify'], d['kernel_ms']['total'], d['e2e']['ms_per_step']), d['kernel_ms']['classify_stages'])"
   done
 done

@@ -56,7 +56,7 @@ CONFIGS["cfg3"] = dict(families=200, strains=5, length=1000000, snp=0.01, ref_se
 # configs[2] at its full index size: 4 Gbp = 800 x 5 x 1 Mbp (BWT ~3.8 G rows, exist tables 2 x 1 GiB, k = 18)
 CONFIGS["cfg3x"] = dict(families=800, strains=5, length=1000000, snp=0.01, ref_seed=44, human_first=False,
                         n_reads=100000, read_len=10000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5,
-                        builder="gpu", sim="c", golden_reads=10000)
+                        builder="gpu", sim="c", golden_reads=5000)
 # small twin of cfg3 for CPU-side checks of the tooling (reference builder, C simulator)
 CONFIGS["cfg3t"] = dict(families=4, strains=3, length=80000, snp=0.01, ref_seed=7, human_first=False,
                         n_reads=300, read_len=4000, err=0.10, read_seed=45, junk=0.05, mix="3,3,4", jitter=0.5,

@@ -21,8 +21,12 @@ import tempfile
 def function_ranges(so_path, kernel="k_classify"):
     d = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(so_path)], cwd=d, stdout=subprocess.DEVNULL, check=True)
-    cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
-    txt = subprocess.run(["nvdisasm", "-c", os.path.join(d, cubin)], stdout=subprocess.PIPE, check=True).stdout.decode()
+    txt = ""
+    for cubin in sorted(f for f in os.listdir(d) if f.endswith(".cubin")):      # the library holds one cubin per .cu file
+        t = subprocess.run(["nvdisasm", "-c", os.path.join(d, cubin)], stdout=subprocess.PIPE, check=True).stdout.decode()
+        if re.search(r"^\.text\.\S*" + re.escape(kernel), t, re.M):
+            txt = t
+            break
     names, in_kernel, idx = [], False, 0
     for line in txt.splitlines():
         m = re.match(r"^\.text\.(\S+):", line)
@@ -37,6 +41,11 @@ def function_ranges(so_path, kernel="k_classify"):
         m = re.match(r"^\$\S+\$(_Z\w+):", line)
         if m:
             sym = m.group(1)
+            mi = re.match(r"_ZN\d+_INTERNAL_[0-9a-f]{8}_\d+_\w+?_cu_[0-9a-f]{8}(\d+)", sym)     # file-local (static) functions
+            if mi:
+                n = int(mi.group(1))
+                names.append((idx, sym[mi.end():mi.end() + n]))
+                continue
             mm = re.match(r"_ZL?(\d+)", sym)
             if not mm:
                 names.append((idx, sym))

@@ -7,6 +7,6 @@ cd "$(dirname "$0")/../desamba-so_b200"
 name=$1; shift
 mkdir -p lib_$name
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 --extended-lambda \
-    -Xcompiler -fPIC -I ../include -I csrc "$@" -shared -o lib_$name/libdsb_cuda.so csrc/dsb_cuda.cu
+    -Xcompiler -fPIC -I ../include -I csrc "$@" -shared -o lib_$name/libdsb_cuda.so csrc/dsb_cuda.cu obj/dsb_build.o -lz
 cp lib/libdesamba.so lib_$name/
 echo "built lib_$name ($*)"
