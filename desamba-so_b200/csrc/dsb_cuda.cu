@@ -1165,6 +1165,48 @@ static void dsb_apply_l2_fetch_env(void)
     cudaGetLastError();
 }
 
+// Host -> device copy of an index array through two pinned staging buffers: the memcpy out of the (mapped, pageable) source
+// into one buffer overlaps the DMA of the other.  A plain cudaMemcpy from pageable memory does the same inside the driver
+// with one small buffer and no overlap (index load of the 1 Gbp index: 2.7 s -> see profiles/).
+struct DsbStager {
+    uint8_t *buf[2] = {nullptr, nullptr};
+    cudaEvent_t ev[2] = {nullptr, nullptr};
+    cudaStream_t st = nullptr;
+    size_t cap = (size_t)32 << 20;
+    int n = 0;
+    bool ok = false;
+    DsbStager()
+    {
+        ok = cudaHostAlloc((void **)&buf[0], cap, cudaHostAllocDefault) == cudaSuccess &&
+             cudaHostAlloc((void **)&buf[1], cap, cudaHostAllocDefault) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming) == cudaSuccess &&
+             cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+    }
+    ~DsbStager()
+    {
+        if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+        for (int i = 0; i < 2; i++) { if (ev[i]) cudaEventDestroy(ev[i]); if (buf[i]) cudaFreeHost(buf[i]); }
+    }
+    cudaError_t copy(void *dst, const void *src, size_t bytes)
+    {
+        if (!ok) return cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice);
+        for (size_t off = 0; off < bytes; off += cap, n++) {
+            const int b = n & 1;
+            const size_t m = bytes - off < cap ? bytes - off : cap;
+            if (n >= 2) { cudaError_t e = cudaEventSynchronize(ev[b]); if (e != cudaSuccess) return e; }
+            memcpy(buf[b], (const uint8_t *)src + off, m);
+            cudaError_t e = cudaMemcpyAsync((uint8_t *)dst + off, buf[b], m, cudaMemcpyHostToDevice, st);
+            if (e != cudaSuccess) return e;
+            cudaEventRecord(ev[b], st);
+        }
+        return cudaSuccess;
+    }
+    cudaError_t finish() { return ok ? cudaStreamSynchronize(st) : cudaSuccess; }
+};
+static thread_local DsbStager *g_stager = nullptr;      // alive during one dsb_index_upload
+
 template <typename T>
 static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_zero, const T **out)
 {
@@ -1173,7 +1215,10 @@ static int upload(dsb_index *ix, const T *src, uint64_t count, uint64_t extra_ze
     CU(cudaMalloc(&d, bytes ? bytes : 16));
     ix->allocs.push_back(d);
     ix->alloc_bytes.push_back(bytes ? bytes : 16);
-    if (count) CU(cudaMemcpy(d, src, (size_t)count * sizeof(T), cudaMemcpyHostToDevice));
+    if (count) {
+        if (g_stager) CU(g_stager->copy(d, src, (size_t)count * sizeof(T)));
+        else CU(cudaMemcpy(d, src, (size_t)count * sizeof(T), cudaMemcpyHostToDevice));
+    }
     if (extra_zero) CU(cudaMemset((char *)d + (size_t)count * sizeof(T), 0, (size_t)extra_zero * sizeof(T)));
     ix->bytes += bytes;
     *out = (const T *)d;
@@ -1219,6 +1264,9 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     DsbIndexView &v = ix->v;
     memset(&v, 0, sizeof v);
     int rc = 0;
+    DsbStager stager;
+    g_stager = &stager;
+    struct StagerScope { ~StagerScope() { g_stager = nullptr; } } stager_scope;
     {   // FM index: the occ array goes up as it is on disk and is re-blocked into 64-symbol / 64-byte blocks by k_fm_reblock
         const uint64_t nb = h->bwt_bytes / 168;
         const uint64_t nblk = dsb_fm_blocks_needed(h->bwt_bytes);
@@ -1237,7 +1285,8 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
             CU(cudaMalloc(&d_raw, nb * 168));
             CU(cudaMalloc((void **)&d_row, 8));
             CU(cudaMemcpy(d_row, &h_row, 8, cudaMemcpyHostToDevice));
-            CU(cudaMemcpy(d_raw, h->bwt_occ, nb * 168, cudaMemcpyHostToDevice));
+            CU(stager.copy(d_raw, h->bwt_occ, nb * 168));
+            CU(stager.finish());
             k_fm_reblock<<<(unsigned)((nb * 4 + 255) / 256), 256>>>((const uint64_t *)d_raw, nb, (DsbFmBlock *)d_fm, d_row);
             g_launches++;
             cudaError_t e = cudaMemcpy(&h_row, d_row, 8, cudaMemcpyDeviceToHost);
@@ -1287,6 +1336,7 @@ int dsb_index_upload(const dsb_host_index *h, int dev, dsb_index **out)
     v.n_ref = h->n_ref;
     rc |= upload(ix, h->q_mem, 2000, 0, &v.q_mem);
     rc |= upload(ix, h->q_lv, 400, 0, &v.q_lv);
+    if (!rc && stager.finish() != cudaSuccess) { g_err = "index upload: staged copy failed"; rc = -1; }
     v.filter_min_length = h->filter_min_length;
     v.filter_min_score = h->filter_min_score;
     v.filter_min_score_lv3 = h->filter_min_score_lv3;
@@ -1468,6 +1518,40 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
         if (per_sm_seed < 1) per_sm_seed = 1;
         s->seed_blocks = per_sm_seed * ix->sm_count;
         if (s->seed_blocks * (DSB_CLASSIFY_THREADS / 32) > s->n_warps) s->n_warps = s->seed_blocks * (DSB_CLASSIFY_THREADS / 32);
+    }
+    {
+        // North-star item N1: pin part of an index array in L2 with an access-policy window on the slot's stream.
+        // DSB_L2_PERSIST=lut|ek0|fm|sa picks the array (the window covers its first accessPolicyMaxWindowSize bytes, hit ratio =
+        // persisting capacity / window).  Off by default: the path's index accesses are uniformly random over arrays 4 - 30x
+        // the L2, there is no hot subset to keep (A/B on the 1 Gbp index: profiles/ab_r02.txt).
+        const char *e = getenv("DSB_L2_PERSIST");
+        if (e && *e) {
+            cudaDeviceProp prop;
+            TRY(cudaGetDeviceProperties(&prop, ix->dev));
+            const void *base = nullptr;
+            size_t bytes = 0;
+            if (!strcmp(e, "lut")) { base = ix->v.lut; bytes = ((size_t)1 << 26) * 8; }
+            else if (!strcmp(e, "ek0")) { base = ix->v.ek0; bytes = (size_t)(ix->v.ek_mask + 1) / 8; }
+            else if (!strcmp(e, "fm")) { base = ix->v.fm; bytes = (size_t)ix->v.n_fm_blocks * sizeof(DsbFmBlock); }
+            else if (!strcmp(e, "sa")) { base = ix->v.sa; bytes = (size_t)ix->v.sa_n * 8; }
+            if (base && prop.persistingL2CacheMaxSize > 0) {
+                cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize);
+                cudaStreamAttrValue a;
+                memset(&a, 0, sizeof a);
+                a.accessPolicyWindow.base_ptr = const_cast<void *>(base);
+                a.accessPolicyWindow.num_bytes = bytes < (size_t)prop.accessPolicyMaxWindowSize ? bytes : (size_t)prop.accessPolicyMaxWindowSize;
+                const double r = (double)prop.persistingL2CacheMaxSize / (double)a.accessPolicyWindow.num_bytes;
+                a.accessPolicyWindow.hitRatio = (float)(r < 1.0 ? r : 1.0);
+                a.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                a.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                cudaError_t pe = cudaStreamSetAttribute(s->stream, cudaStreamAttributeAccessPolicyWindow, &a);
+                if (getenv("DSB_VERBOSE"))
+                    fprintf(stderr, "[dsb] L2 access-policy window on %s: %zu MB window, %d MB persisting, hit ratio %.2f (%s)\n", e,
+                            a.accessPolicyWindow.num_bytes >> 20, prop.persistingL2CacheMaxSize >> 20, a.accessPolicyWindow.hitRatio,
+                            cudaGetErrorString(pe));
+                cudaGetLastError();
+            }
+        }
     }
     s->cap_anchor = 2048;
     s->cap_sms = 8192;

@@ -44,6 +44,11 @@ typedef struct dsb_loaded_index {
     int32_t q_mem[2000];
     int32_t q_lv[400];
     int ek_len;
+    /* the big arrays are views into read-only mappings of the index files (no host copy is made): the views of `h`
+     * point into these; dsb_index_release_bulk unmaps them */
+    struct { void *p; size_t n; } maps[8];
+    int n_maps;
+    void *prefault;                /* helper threads that touch the mappings' pages ahead of the upload */
 } dsb_loaded_index;
 
 /* read the ten deSAMBA.* files of `dir`; min_len/min_score are MAP_opt.L_min_matching / min_score */

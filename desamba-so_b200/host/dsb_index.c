@@ -15,7 +15,12 @@
 #include <stdarg.h>
 #include <stdlib.h>
 #include <string.h>
+#include <fcntl.h>
+#include <pthread.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
 #include <sys/time.h>
+#include <unistd.h>
 
 void dsb_fatal(const char *fmt, ...)
 {
@@ -128,41 +133,86 @@ void dsb_mapq_tables(int32_t *q_mem, int32_t *q_lv, double P_E, uint64_t L_REF)
     }
 }
 
+/* ---- mapped index files ------------------------------------------------------------------
+ * The reference reads every file into a malloc'd array (src/idx.c:1103-1160, src/bwt.c:68-104).  Here the arrays go to
+ * the GPUs and the host never needs them again, so the files are only MAPPED: the views handed to dsb_index_upload point
+ * into the page cache, and a helper thread per file touches the pages ahead of the upload's staging copies. */
+typedef struct prefault_job { const volatile char *p; size_t n; pthread_t th; } prefault_job;
+typedef struct prefault_set { prefault_job job[8]; int n; } prefault_set;
+
+static void *prefault_thread(void *arg)
+{
+    prefault_job *j = (prefault_job *)arg;
+    char sink = 0;
+    for (size_t i = 0; i < j->n; i += 4096) sink ^= j->p[i];
+    (void)sink;
+    return NULL;
+}
+
+static const uint8_t *map_part(dsb_loaded_index *ix, const char *dir, const char *suffix, uint64_t *size)
+{
+    char path[4096];
+    snprintf(path, sizeof path, "%s/deSAMBA%s", dir, suffix);
+    int fd = open(path, O_RDONLY);
+    if (fd < 0) dsb_fatal("cannot open index file %s", path);
+    struct stat st;
+    if (fstat(fd, &st) != 0 || st.st_size < 8) dsb_fatal("index file %s is truncated", path);
+    void *p = mmap(NULL, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (p == MAP_FAILED) dsb_fatal("cannot map index file %s", path);
+    madvise(p, (size_t)st.st_size, MADV_WILLNEED);
+    if (ix->n_maps >= 8) dsb_fatal("too many mapped index files");
+    ix->maps[ix->n_maps].p = p;
+    ix->maps[ix->n_maps].n = (size_t)st.st_size;
+    ix->n_maps++;
+    prefault_set *ps = (prefault_set *)ix->prefault;
+    if (ps && ps->n < 8 && st.st_size > (16 << 20)) {
+        prefault_job *j = &ps->job[ps->n];
+        j->p = (const volatile char *)p;
+        j->n = (size_t)st.st_size;
+        if (pthread_create(&j->th, NULL, prefault_thread, j) == 0) ps->n++;
+    }
+    *size = (uint64_t)st.st_size;
+    return (const uint8_t *)p;
+}
+
+static uint64_t counted(const uint8_t *m, uint64_t size, uint64_t elem, const char *what)
+{
+    uint64_t n;
+    memcpy(&n, m, 8);
+    if (size < 8 || n > (size - 8) / elem) dsb_fatal("index file truncated while reading %s", what);
+    return n;
+}
+
 void dsb_index_load(dsb_loaded_index *ix, const char *dir, int min_len, int min_score)
 {
     memset(ix, 0, sizeof *ix);
+    ix->prefault = dsb_xcalloc(1, sizeof(prefault_set));
+    uint64_t sz;
+    const uint8_t *m;
     FILE *fp;
-    /* FM index */
-    fp = open_part(dir, ".bwt");
-    ix->h.bwt_bytes = read_u64(fp, ".bwt length");
-    ix->bwt_occ = (uint8_t *)dsb_xmalloc(ix->h.bwt_bytes + 168);
-    read_exact(ix->bwt_occ, 1, ix->h.bwt_bytes, fp, ".bwt blocks");
-    memset(ix->bwt_occ + ix->h.bwt_bytes, 0, 168);
-    read_exact(ix->h.rank, 8, 5, fp, ".bwt rank");
-    ix->h.rank[5] = ix->h.rank[0] - 1;
+    /* FM index: u64 byteLen | blocks | 5 x u64 rank | (2^26 + 1) x u64 prefix table */
+    m = map_part(ix, dir, ".bwt", &sz);
+    memcpy(&ix->h.bwt_bytes, m, 8);
     const uint64_t lut_n = ((uint64_t)1 << 26) + 1;
-    ix->hash_index = (uint64_t *)dsb_xmalloc(lut_n * 8);
-    read_exact(ix->hash_index, 8, lut_n, fp, ".bwt prefix table");
-    fclose(fp);
-    fp = open_part(dir, ".sa");
-    ix->h.sa_n = read_u64(fp, ".sa count");
-    ix->sa = (uint64_t *)dsb_xmalloc(ix->h.sa_n * 8);
-    read_exact(ix->sa, 8, ix->h.sa_n, fp, ".sa");
-    fclose(fp);
+    if (ix->h.bwt_bytes > sz || sz - ix->h.bwt_bytes < 8 + 40 + lut_n * 8) dsb_fatal("index file truncated while reading .bwt");
+    ix->h.bwt_occ = m + 8;
+    memcpy(ix->h.rank, m + 8 + ix->h.bwt_bytes, 40);
+    ix->h.rank[5] = ix->h.rank[0] - 1;
+    ix->h.hash_index = (const uint64_t *)(m + 8 + ix->h.bwt_bytes + 40);
+    m = map_part(ix, dir, ".sa", &sz);
+    ix->h.sa_n = counted(m, sz, 8, ".sa");
+    ix->h.sa_taxon = (const uint64_t *)(m + 8);
     /* exist k-mer tables */
     fp = open_part(dir, ".exki");
     ix->h.e_kmer_size = read_u64(fp, ".exki");
     fclose(fp);
     ix->ek_len = dsb_ekmer_len(ix->h.e_kmer_size);
-    ix->ek0 = (uint8_t *)dsb_xmalloc(ix->h.e_kmer_size);
-    ix->ek1 = (uint8_t *)dsb_xmalloc(ix->h.e_kmer_size);
-    fp = open_part(dir, ".exk0");
-    read_exact(ix->ek0, 1, ix->h.e_kmer_size, fp, ".exk0");
-    fclose(fp);
-    fp = open_part(dir, ".exk1");
-    read_exact(ix->ek1, 1, ix->h.e_kmer_size, fp, ".exk1");
-    fclose(fp);
-    /* unitigs (+ sentinel) */
+    ix->h.e_kmer0 = map_part(ix, dir, ".exk0", &sz);
+    if (sz < ix->h.e_kmer_size) dsb_fatal("index file truncated while reading .exk0");
+    ix->h.e_kmer1 = map_part(ix, dir, ".exk1", &sz);
+    if (sz < ix->h.e_kmer_size) dsb_fatal("index file truncated while reading .exk1");
+    /* unitigs (+ sentinel): the one array that gets an entry the file does not hold, so it is copied */
     fp = open_part(dir, ".unv");
     uint64_t n_uni = read_u64(fp, ".unv count");
     if (n_uni < 2) dsb_fatal("index has %llu unitigs", (unsigned long long)n_uni);
@@ -175,14 +225,13 @@ void dsb_index_load(dsb_loaded_index *ix, const char *dir, int min_len, int min_
         uint32_t sentinel_ref_list = last_ref_list + 1 + last_len;      /* src/idx.c:1127 */
         ix->unitig[n_uni] = (uint64_t)sentinel_ref_list;                /* length is uninitialised in the reference */
     }
+    ix->h.unitig = ix->unitig;
     ix->h.n_unitig = n_uni + 1;
     ix->h.dollar_pos = n_uni - 1 - 1;                                   /* src/idx.c:1128 */
     /* references */
-    fp = open_part(dir, ".ref_b");
-    ix->h.ref_bin_n = read_u64(fp, ".ref_b count");
-    ix->ref_bin = (uint8_t *)dsb_xmalloc(ix->h.ref_bin_n + 1);
-    read_exact(ix->ref_bin, 1, ix->h.ref_bin_n, fp, ".ref_b");
-    fclose(fp);
+    m = map_part(ix, dir, ".ref_b", &sz);
+    ix->h.ref_bin_n = counted(m, sz, 1, ".ref_b");
+    ix->h.ref_bin = m + 8;
     fp = open_part(dir, ".ref_i");
     ix->h.n_ref = read_u64(fp, ".ref_i count");
     ix->ref_info = (dsb_ref_info *)dsb_xmalloc(ix->h.n_ref * sizeof(dsb_ref_info));
@@ -195,26 +244,14 @@ void dsb_index_load(dsb_loaded_index *ix, const char *dir, int min_len, int min_
         ix->ref_len[i] = ix->ref_info[i].seq_l;
         ix->ref_info[i].ref_name[127] = 0;
     }
-    fp = open_part(dir, ".ref_p");
-    ix->h.n_ref_pos = read_u64(fp, ".ref_p count");
-    ix->ref_pos = (uint64_t *)dsb_xmalloc((ix->h.n_ref_pos + 1) * 8);
-    read_exact(ix->ref_pos, 8, ix->h.n_ref_pos, fp, ".ref_p");
-    ix->ref_pos[ix->h.n_ref_pos] = 0;
-    fclose(fp);
+    m = map_part(ix, dir, ".ref_p", &sz);
+    ix->h.n_ref_pos = counted(m, sz, 8, ".ref_p");
+    ix->h.ref_pos = (const uint64_t *)(m + 8);
     /* score tables and filters (src/cly_mt.c:518-524) */
     dsb_mapq_tables(ix->q_mem, ix->q_lv, 0.15, ix->h.ref_bin_n * 4);
     ix->h.filter_min_length = min_len;
     ix->h.filter_min_score = min_score;
     ix->h.filter_min_score_lv3 = min_score + 10;
-    /* views */
-    ix->h.bwt_occ = ix->bwt_occ;
-    ix->h.hash_index = ix->hash_index;
-    ix->h.sa_taxon = ix->sa;
-    ix->h.e_kmer0 = ix->ek0;
-    ix->h.e_kmer1 = ix->ek1;
-    ix->h.unitig = ix->unitig;
-    ix->h.ref_pos = ix->ref_pos;
-    ix->h.ref_bin = ix->ref_bin;
     ix->h.ref_seq_offset = ix->ref_off;
     ix->h.ref_seq_len = ix->ref_len;
     ix->h.q_mem = ix->q_mem;
@@ -223,14 +260,17 @@ void dsb_index_load(dsb_loaded_index *ix, const char *dir, int min_len, int min_
 
 void dsb_index_release_bulk(dsb_loaded_index *ix)
 {
-    free(ix->bwt_occ); ix->bwt_occ = NULL; ix->h.bwt_occ = NULL;
-    free(ix->hash_index); ix->hash_index = NULL; ix->h.hash_index = NULL;
-    free(ix->sa); ix->sa = NULL; ix->h.sa_taxon = NULL;
-    free(ix->ek0); ix->ek0 = NULL; ix->h.e_kmer0 = NULL;
-    free(ix->ek1); ix->ek1 = NULL; ix->h.e_kmer1 = NULL;
+    prefault_set *ps = (prefault_set *)ix->prefault;
+    if (ps) {
+        for (int i = 0; i < ps->n; i++) pthread_join(ps->job[i].th, NULL);
+        free(ps);
+        ix->prefault = NULL;
+    }
+    for (int i = 0; i < ix->n_maps; i++) munmap(ix->maps[i].p, ix->maps[i].n);
+    ix->n_maps = 0;
+    ix->h.bwt_occ = NULL; ix->h.hash_index = NULL; ix->h.sa_taxon = NULL; ix->h.e_kmer0 = NULL; ix->h.e_kmer1 = NULL;
+    ix->h.ref_pos = NULL; ix->h.ref_bin = NULL;
     free(ix->unitig); ix->unitig = NULL; ix->h.unitig = NULL;
-    free(ix->ref_pos); ix->ref_pos = NULL; ix->h.ref_pos = NULL;
-    free(ix->ref_bin); ix->ref_bin = NULL; ix->h.ref_bin = NULL;
 }
 
 void dsb_index_destroy(dsb_loaded_index *ix)
