@@ -226,7 +226,6 @@ struct DsbWork {
     DsbSms *sms;
     uint32_t n_sms, cap_sms;
     DsbSms *sms_stage;            // 32 lanes x DSB_SMS_LANE_CAP (dsb_sdp_match)
-    struct DsbCand *sdp_cand;     // DSB_SDP_CAND window k-mers with a hit: (first hit, segment range, key | tag, k-mer number)
     uint32_t *h_head[2];          // [0] forward strand table, [1] reverse; 2^key_len entries
     uint32_t *h_ent[2];           // L entries: (next position + 1) << 8 | (9-mer >> key_len); one load per chain step
     DsbScHash *sc_hash;           // 256 + 2*400
@@ -1604,7 +1603,8 @@ DSB_HD int dsb_read_hash_key_len(uint32_t L)
 // identical.  Tried on top and dropped, all slower in the same runs: first entry's tag + a has-next bit inlined in 32-bit
 // heads (one load instead of head -> entry for most look-ups: 190 ms, the heads double and the cursor grows), 4 / 8
 // segments built in an interleaved fashion (181 / 188 ms: register arrays under the kernel's 80-register cap), word-wide
-// exact-run extension of the hits (166.8 ms).
+// exact-run extension of the hits (166.8 ms), compaction of the window k-mers that have a hit before the divergent extension
+// phase (166.9 ms).
 //   head16[g * SEG + key] = (position inside the segment) + 1, 0 = empty bucket
 //   ent[p]                = (next position in the bucket + 1) << 8 | tag       (positions ascending along a chain)
 #ifndef DSB_SEG_BITS
@@ -1618,7 +1618,6 @@ DSB_HD int dsb_read_hash_key_len(uint32_t L)
 
 // cursor over the hits of one window 9-mer: ascending read positions p with 9-mer(p) == kmer and q_bg <= p <= q_ed
 struct DsbTabCur { uint32_t node, seg, seg_hi, key, tag; };
-struct alignas(16) DsbCand { uint32_t x, y, z, w; };
 
 // advance from the candidate c->node (0 = bucket exhausted) to the next entry that matches; returns position + 1 or 0
 DSB_HD uint32_t dsb_tab_settle(const uint16_t *head, const uint32_t *ent, DsbTabCur *c, uint32_t q_bg, uint32_t q_ed)
@@ -1807,7 +1806,6 @@ DSB_HD bool dsb_extend_hit(const uint8_t *q_str, const uint8_t *t_str, uint32_t 
 }
 
 #define DSB_SDP_STAGE 16         // staging slots per lane (dsb_sdp_match)
-#define DSB_SDP_CAND 544         // candidate list of one window: < 2000 / 4 k-mers (sdp_middle's windows are the longest) + one group
 
 DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8_t *q_str, const uint8_t *t_str,
                            uint32_t t_len, int key_len, int strand, uint32_t t_st, bool is_forward)
@@ -1826,40 +1824,6 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
         // exact-run extension, so the match-block list is identical to the reference's.
         const uint32_t lane = threadIdx.x & 31;
         const uint32_t n_i = (t_kmer_num > 4) ? ((t_kmer_num - 4 + 3) >> 2) : 0;     // i = 4, 8, ... < t_kmer_num
-#if !defined(DSB_NO_SDP_COMPACT)
-        // Phase A, all lanes busy: the first hit of every window k-mer (k-mer, bucket head, first entries).  Only ~40 % of the
-        // k-mers of a window have one, so the k-mers WITH a hit are compacted, in window order, into the warp's candidate
-        // list; phase B then runs the divergent part (exact-run extensions, further hits of the bucket) on full groups of 32
-        // candidates instead of on the ~12 lanes of 32 that had a hit in each group of 32 k-mers.
-        uint32_t n_cand = 0;
-        DsbCand *cand = w->sdp_cand;
-        for (uint32_t base = 0; base < n_i; base += 32) {
-            const uint32_t mine = base + lane;
-            const int i_a = 4 + 4 * (int)mine;
-            const long off_a = is_forward ? (long)i_a : ((long)t_len - DSB_KMER9 - (long)i_a);
-            uint32_t nd = 0;
-            DsbTabCur ca = {0, 0, 0, 0, 0};
-            if (mine < n_i) nd = dsb_tab_first(head, ent, &ca, dsb_kmer9(t_str + off_a), q_bg, q_ed, n_pos);
-            const uint32_t hit = __ballot_sync(0xffffffffu, nd != 0);
-            if (nd != 0 && n_cand + 32 <= DSB_SDP_CAND)
-                cand[n_cand + (uint32_t)__popc(hit & ((1u << lane) - 1u))] =
-                    DsbCand{nd, ca.seg | (ca.seg_hi << 16), ca.key | (ca.tag << 16), (uint32_t)i_a};
-            if (hit && n_cand + 32 > DSB_SDP_CAND) { w->overflow = 1; return; }     // cannot happen: windows hold < 2000 bases
-            n_cand += (uint32_t)__popc(hit);
-        }
-        __syncwarp();
-        for (uint32_t base = 0; base < n_cand; base += 32) {
-            const bool have = base + lane < n_cand;
-            uint32_t node = 0;
-            int i_l = 4;
-            DsbTabCur cur = {0, 0, 0, 0, 0};
-            if (have) {
-                const DsbCand c = cand[base + lane];
-                node = c.x; cur.node = c.x; cur.seg = c.y & 0xffffu; cur.seg_hi = c.y >> 16; cur.key = c.z & 0xffffu; cur.tag = c.z >> 16;
-                i_l = (int)c.w;
-            }
-            const long off_l = is_forward ? (long)i_l : ((long)t_len - DSB_KMER9 - (long)i_l);
-#else
         for (uint32_t base = 0; base < n_i; base += 32) {
             const uint32_t mine = base + lane;
             const int i_l = 4 + 4 * (int)mine;
@@ -1868,7 +1832,6 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             DsbTabCur cur = {0, 0, 0, 0, 0};
             if (mine < n_i) node = dsb_tab_first(head, ent, &cur, dsb_kmer9(t_str + off_l), q_bg, q_ed, n_pos);
             if (!__any_sync(0xffffffffu, node != 0)) continue;
-#endif
             // Every hit is an independent computation (two exact-run extensions); only the ORDER of the
             // match-block list couples them (window position, then bucket order).  So each lane extends
             // all hits of its own k-mer alone into a small staging area, and the warp then appends the
@@ -1906,7 +1869,7 @@ DSB_HDN void dsb_sdp_match(DsbWork *w, uint32_t q_bg, uint32_t q_ed, const uint8
             uint32_t act = __ballot_sync(0xffffffffu, node != 0);
             while (act) {
                 const int l = __ffs((int)act) - 1;
-                const int i = __shfl_sync(0xffffffffu, i_l, l);
+                const int i = 4 + 4 * (int)(base + (uint32_t)l);
                 const long c_off = is_forward ? (long)i : ((long)t_len - DSB_KMER9 - (long)i);
                 const uint8_t *c_t_str = t_str + c_off;
                 for (;;) {

@@ -45,7 +45,7 @@ struct DsbScratchDims {
     uint32_t cap_stage;     // anchors one lane may stage during fast seeding
     // byte offsets inside a slice
     size_t o_seeds0, o_seeds1, o_anchors, o_anchors_tmp, o_chains, o_chains_tmp, o_sort_a, o_sort_b, o_score_v,
-        o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms_stage, o_sdp_cand, o_sms, o_head0, o_head1, o_ent0, o_ent1, o_sc_hash, o_ref_mid, o_ref_ext;
+        o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms_stage, o_sms, o_head0, o_head1, o_ent0, o_ent1, o_sc_hash, o_ref_mid, o_ref_ext;
     size_t bytes;           // slice size (multiple of 256)
 };
 
@@ -79,7 +79,6 @@ static inline void dsb_scratch_dims(DsbScratchDims *d, uint32_t Lmax, uint32_t c
     DSB_TAKE(o_stage, (size_t)32 * d->cap_stage * sizeof(DsbAnchor));
     DSB_TAKE(o_lane_priv, (size_t)32 * DSB_LANE_PRIV_BYTES);
     DSB_TAKE(o_sms_stage, (size_t)32 * DSB_SDP_STAGE * sizeof(DsbSms));
-    DSB_TAKE(o_sdp_cand, (size_t)DSB_SDP_CAND * 16);
     DSB_TAKE(o_sms, (size_t)cap_sms * sizeof(DsbSms));
     DSB_TAKE(o_head0, (size_t)d->head_entries * 2 + 64);
     DSB_TAKE(o_head1, (size_t)d->head_entries * 2 + 64);
@@ -115,7 +114,6 @@ DSB_HD void dsb_bind_scratch(DsbWork *w, uint8_t *base, const DsbScratchDims *d)
     w->solo = 0;
     w->sms = (DsbSms *)(base + d->o_sms);
     w->sms_stage = (DsbSms *)(base + d->o_sms_stage);
-    w->sdp_cand = (DsbCand *)(base + d->o_sdp_cand);
     w->cap_sms = d->cap_sms;
     w->h_head[0] = (uint32_t *)(base + d->o_head0);
     w->h_head[1] = (uint32_t *)(base + d->o_head1);
