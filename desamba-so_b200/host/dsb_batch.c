@@ -75,11 +75,14 @@ struct dsb_session {
     dsb_history *hist;
     fmt_pool pool;                  /* formatter helpers (used by the drain thread) */
     fmt_worker_arg pool_arg[MAX_FMT_THREADS];
+    fmt_pool spool;                 /* splice helpers (used by the splice thread: SAM_FULL text into the caller's block) */
+    fmt_worker_arg spool_arg[MAX_FMT_THREADS];
     fmt_pool cpool;                 /* staging-copy helpers (used by the producer) */
     fmt_worker_arg cpool_arg[MAX_FMT_THREADS];
     const char ***copy_src;         /* [slot][read]: where the read's bases still have to be copied from (NULL: already in staging) */
-    dsb_strbuf fmt_buf[MAX_FMT_THREADS + 1];
-    size_t *fmt_ins, *fmt_end;      /* per read of the batch being formatted (SAM_FULL, direct mode): splice point / end of its fields */
+    /* two banks: while the splice thread moves batch b's text, the drain thread formats the fields of batch b + 1 */
+    dsb_strbuf fmt_buf[2][MAX_FMT_THREADS + 1];
+    size_t *fmt_ins[2], *fmt_end[2];   /* per read of the batch being formatted (SAM_FULL, direct mode): splice point / end of its fields */
     /* a record that did not fit the previous batch */
     int have_carry;
     dsb_rec_view carry;
@@ -239,9 +242,12 @@ dsb_session *dsb_session_create(dsb_engine *e)
         s->meta[k].qual_off = (uint64_t *)dsb_xmalloc((size_t)e->batch_reads * 8);
     }
     s->hist = dsb_history_new();
-    s->fmt_ins = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
-    s->fmt_end = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
+    for (int b = 0; b < 2; b++) {
+        s->fmt_ins[b] = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
+        s->fmt_end[b] = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
+    }
     pool_start(&s->pool, s->pool_arg, e->fmt_threads - 1);
+    pool_start(&s->spool, s->spool_arg, e->fmt_threads - 1);
     pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > 6 ? 6 : e->fmt_threads) - 1);
     s->copy_src = (const char ***)dsb_xcalloc((size_t)s->n_slots, sizeof(char **));
     for (int k = 0; k < s->n_slots; k++) s->copy_src[k] = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
@@ -260,6 +266,7 @@ void dsb_session_destroy(dsb_session *s)
 {
     if (!s) return;
     pool_stop(&s->pool);
+    pool_stop(&s->spool);
     pool_stop(&s->cpool);
     for (int k = 0; k < s->n_slots; k++) free(s->copy_src[k]);
     free(s->copy_src);
@@ -271,9 +278,11 @@ void dsb_session_destroy(dsb_session *s)
         free(s->meta[k].qual_ptr);
         free(s->meta[k].qual_off);
     }
-    for (int i = 0; i <= MAX_FMT_THREADS; i++) free(s->fmt_buf[i].s);
-    free(s->fmt_ins);
-    free(s->fmt_end);
+    for (int b = 0; b < 2; b++) {
+        for (int i = 0; i <= MAX_FMT_THREADS; i++) free(s->fmt_buf[b][i].s);
+        free(s->fmt_ins[b]);
+        free(s->fmt_end[b]);
+    }
     free(s->slots);
     free(s->meta);
     dsb_history_free(s->hist);
@@ -397,6 +406,8 @@ typedef struct fmt_job {
     char *dst;                             /* direct mode: where part p's text goes = dst + off[p] */
     size_t off[MAX_FMT_THREADS + 2];
     size_t len[MAX_FMT_THREADS + 2];       /* SAM_FULL direct mode: bytes part p will write */
+    int bank;                              /* which fmt_buf / fmt_ins / fmt_end bank holds this batch's fields */
+    int parts;
 } fmt_job;
 
 static void fmt_part(void *arg, int part, int n_parts)
@@ -404,7 +415,7 @@ static void fmt_part(void *arg, int part, int n_parts)
     (void)n_parts;
     fmt_job *j = (fmt_job *)arg;
     const batch_meta *m = j->m;
-    dsb_strbuf *text = &j->s->fmt_buf[part];
+    dsb_strbuf *text = &j->s->fmt_buf[j->bank][part];
     text->l = 0;
     for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
         const char *q = m->qual_ptr[i];
@@ -422,14 +433,14 @@ static void fmt_fields_part(void *arg, int part, int n_parts)
     (void)n_parts;
     fmt_job *j = (fmt_job *)arg;
     const batch_meta *m = j->m;
-    dsb_strbuf *text = &j->s->fmt_buf[part];
+    dsb_strbuf *text = &j->s->fmt_buf[j->bank][part];
     text->l = 0;
     size_t total = 0;
     for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
         const int has_q = m->qual_ptr[i] || m->qual_off[i] != UINT64_MAX;
         dsb_format_sam_full_fields(text, j->s->e->ix, j->o, m->names.s + m->name_off[i], j->desc[i].len, &j->res[i],
-                                   j->hits + j->res[i].hit_off, &j->s->fmt_ins[i]);
-        j->s->fmt_end[i] = text->l;
+                                   j->hits + j->res[i].hit_off, &j->s->fmt_ins[j->bank][i]);
+        j->s->fmt_end[j->bank][i] = text->l;
         total += (size_t)j->desc[i].len + 1 + (has_q ? (size_t)j->desc[i].len : 6);
     }
     j->len[part] = text->l + total;
@@ -440,11 +451,11 @@ static void splice_part(void *arg, int part, int n_parts)
     (void)n_parts;
     fmt_job *j = (fmt_job *)arg;
     const batch_meta *m = j->m;
-    const char *text = j->s->fmt_buf[part].s;
+    const char *text = j->s->fmt_buf[j->bank][part].s;
     char *d = j->dst + j->off[part];
     size_t from = 0;
     for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
-        const size_t ins = j->s->fmt_ins[i], end = j->s->fmt_end[i];
+        const size_t ins = j->s->fmt_ins[j->bank][i], end = j->s->fmt_end[j->bank][i];
         const uint32_t L = j->desc[i].len;
         const char *q = m->qual_ptr[i];
         if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
@@ -462,79 +473,13 @@ static void copy_part(void *arg, int part, int n_parts)
 {
     (void)n_parts;
     fmt_job *j = (fmt_job *)arg;
-    const dsb_strbuf *text = &j->s->fmt_buf[part];
+    const dsb_strbuf *text = &j->s->fmt_buf[j->bank][part];
     if (text->l) memcpy(j->dst + j->off[part], text->s, text->l);
 }
 
-static void drain_slot(dsb_session *s, int k, const dsb_out_opt *o, dsb_sink_fn sink, void *ctx, dsb_run_stats *st, double t_start)
-{
-    batch_meta *m = &s->meta[k];
-    fmt_job j;
-    uint32_t n_hits;
-    dsb_counters c;
-    double t0 = dsb_now();
-    if (dsb_slot_wait(s->slots[k], &j.res, &j.hits, &n_hits, &c) != 0) dsb_fatal("GPU batch failed: %s", dsb_last_error());
-    double t1 = dsb_now();
-    char *seq;
-    dsb_read_desc *desc;
-    uint8_t *edge;
-    dsb_slot_staging(s->slots[k], &seq, &desc, &edge);
-    /* the reference worker's max_read_l, in read order: batches are drained in submission order */
-    for (uint32_t i = 0; i < m->n_reads; i++)
-        if (desc[i].len >= 510) dsb_history_note_result(s->hist, desc[i].len, (j.res[i].fast_classify & DSB_RES_HAD_CHAIN) != 0);
-    j.s = s; j.m = m; j.o = o; j.seq = seq; j.desc = desc;
-    /* contiguous read ranges of about equal size in bases, one per formatter thread, sunk in order */
-    const int parts = s->pool.n + 1;
-    j.cut[0] = 0;
-    {
-        uint32_t i = 0;
-        for (int p = 1; p < parts; p++) {
-            const uint64_t target = m->n_bases * (uint64_t)p / (uint64_t)parts;
-            while (i < m->n_reads && desc[i].seq_off < target) i++;
-            j.cut[p] = i;
-        }
-        j.cut[parts] = m->n_reads;
-    }
-    const int splice = (!sink && o->format == DSB_OUT_SAM_FULL);
-    pool_run(&s->pool, splice ? fmt_fields_part : fmt_part, &j);
-    const double t_f = dsb_now();
-    if (splice) {
-        dsb_strbuf *out = (dsb_strbuf *)ctx;
-        size_t total = 0;
-        for (int p = 0; p < parts; p++) { j.off[p] = total; total += j.len[p]; }
-        dsb_strbuf_reserve(out, total);
-        j.dst = out->s + out->l;
-        pool_run(&s->pool, splice_part, &j);
-        out->l += total;
-    } else if (sink) {
-        for (int p = 0; p < parts; p++)
-            if (s->fmt_buf[p].l) sink(ctx, s->fmt_buf[p].s, s->fmt_buf[p].l);
-    } else {
-        /* direct mode: ctx is the caller's dsb_strbuf; every thread copies its own part, so the page
-         * faults of the fresh output block are taken in parallel too */
-        dsb_strbuf *out = (dsb_strbuf *)ctx;
-        size_t total = 0;
-        for (int p = 0; p < parts; p++) { j.off[p] = total; total += s->fmt_buf[p].l; }
-        dsb_strbuf_reserve(out, total);
-        j.dst = out->s + out->l;
-        pool_run(&s->pool, copy_part, &j);
-        out->l += total;
-    }
-    double t2 = dsb_now();
-    if (st) {
-        float a = 0, b = 0, d = 0;
-        dsb_slot_timing(s->slots[k], &a, &b, &d);
-        st->gpu_ms_total += a; st->gpu_ms_exist += b; st->gpu_ms_classify += d;
-        st->t_gpu_wait += t1 - t0;
-        st->t_format += t2 - t1;
-        if (getenv("DSB_VERBOSE"))
-            fprintf(stderr, "[dsb]   slot %d: wait %.1f ms, format %.1f ms, sink %.1f ms | gpu %.2f ms | t: waited from %.2f, results at %.2f, text at %.2f, sunk at %.2f\n",
-                    k, 1e3 * (t1 - t0), 1e3 * (t_f - t1), 1e3 * (t2 - t_f), a, 1e3 * (t0 - t_start), 1e3 * (t1 - t_start), 1e3 * (t_f - t_start), 1e3 * (t2 - t_start));
-        add_counters(&st->counters, &c);
-    }
-}
-
-/* ---- the pipeline: producer (caller's thread) parses + submits, a drain thread waits + formats ---- */
+/* ---- the pipeline: producer (caller's thread) parses, a submit thread stages + launches, a drain thread waits for the
+ * results and formats the record fields, and -- for SAM_FULL straight into the caller's block -- a splice thread moves
+ * fields, SEQ and QUAL to their final place while the drain thread is already on the next batch ---- */
 typedef struct run_ctx {
     dsb_session *s;
     const dsb_out_opt *o;
@@ -545,41 +490,178 @@ typedef struct run_ctx {
     pthread_cond_t cv;
     uint64_t filled, submitted, drained;
     int fill_done, done;
-    char *prefault_lo;              /* direct mode: region of the caller's output block to touch before the first batch is back */
+    /* splice stage (direct SAM_FULL mode only) */
+    int splice_mode;
+    fmt_job sj[2];                  /* bank b & 1 holds batch b between its field pass and its splice */
+    uint64_t formatted, spliced;
+    int format_done;
+    /* direct mode: the caller's output block is fresh memory; helper threads touch its pages in the background */
+    char *prefault_lo;
     size_t prefault_n;
+    volatile int prefault_stop;
+    int prefault_threads;
+    pthread_t prefault_th[8];
     double t_start;
     int verbose;
 } run_ctx;
 
-static void prefault_part(void *arg, int part, int n_parts)
+typedef struct prefault_arg { run_ctx *r; int id; } prefault_arg;
+
+/* Touch the pages of the output block front to back, PREFAULT_CHUNK at a time, thread t taking every n-th chunk.  The touch
+ * is an atomic OR of zero: it allocates the page without changing a byte, so it is safe next to the splice threads that are
+ * already writing text into the same block. */
+#define PREFAULT_CHUNK ((size_t)2 << 20)
+static void *prefault_thread(void *argp)
 {
-    run_ctx *r = (run_ctx *)arg;
-    const size_t page = 4096;
-    const size_t lo = r->prefault_n * (size_t)part / (size_t)n_parts, hi = r->prefault_n * (size_t)(part + 1) / (size_t)n_parts;
-    volatile char *p = r->prefault_lo;
-    for (size_t i = (lo + page - 1) & ~(page - 1); i < hi; i += page) p[i] = 0;
+    prefault_arg *a = (prefault_arg *)argp;
+    run_ctx *r = a->r;
+    const size_t page = 4096, n_chunks = (r->prefault_n + PREFAULT_CHUNK - 1) / PREFAULT_CHUNK;
+    for (size_t c = (size_t)a->id; c < n_chunks && !r->prefault_stop; c += (size_t)r->prefault_threads) {
+        const size_t lo = c * PREFAULT_CHUNK, hi = lo + PREFAULT_CHUNK < r->prefault_n ? lo + PREFAULT_CHUNK : r->prefault_n;
+        for (size_t i = lo; i < hi; i += page) __atomic_fetch_or(r->prefault_lo + i, 0, __ATOMIC_RELAXED);
+    }
+    return NULL;
+}
+
+static void prefault_join(run_ctx *r)
+{
+    r->prefault_stop = 1;
+    for (int i = 0; i < r->prefault_threads; i++) pthread_join(r->prefault_th[i], NULL);
+    r->prefault_threads = 0;
+}
+
+/* wait for batch b in slot k, format its records; direct SAM_FULL mode hands the second pass to the splice thread */
+static void drain_slot(run_ctx *r, uint64_t b, int k)
+{
+    dsb_session *s = r->s;
+    const dsb_out_opt *o = r->o;
+    dsb_run_stats *st = r->stats;
+    batch_meta *m = &s->meta[k];
+    const int bank = (int)(b & 1);
+    if (r->splice_mode) {                          /* bank b & 1 is free once batch b - 2 has been spliced */
+        pthread_mutex_lock(&r->mu);
+        while (b >= r->spliced + 2) pthread_cond_wait(&r->cv, &r->mu);
+        pthread_mutex_unlock(&r->mu);
+    }
+    fmt_job *jp = &r->sj[bank];
+    fmt_job local;
+    if (!r->splice_mode) jp = &local;
+    uint32_t n_hits;
+    dsb_counters c;
+    double t0 = dsb_now();
+    if (dsb_slot_wait(s->slots[k], &jp->res, &jp->hits, &n_hits, &c) != 0) dsb_fatal("GPU batch failed: %s", dsb_last_error());
+    double t1 = dsb_now();
+    char *seq;
+    dsb_read_desc *desc;
+    uint8_t *edge;
+    dsb_slot_staging(s->slots[k], &seq, &desc, &edge);
+    /* the reference worker's max_read_l, in read order: batches are drained in submission order */
+    for (uint32_t i = 0; i < m->n_reads; i++)
+        if (desc[i].len >= 510) dsb_history_note_result(s->hist, desc[i].len, (jp->res[i].fast_classify & DSB_RES_HAD_CHAIN) != 0);
+    jp->s = s; jp->m = m; jp->o = o; jp->seq = seq; jp->desc = desc; jp->bank = bank;
+    /* contiguous read ranges of about equal size in bases, one per formatter thread, sunk in order */
+    const int parts = s->pool.n + 1;
+    jp->parts = parts;
+    jp->cut[0] = 0;
+    {
+        uint32_t i = 0;
+        for (int p = 1; p < parts; p++) {
+            const uint64_t target = m->n_bases * (uint64_t)p / (uint64_t)parts;
+            while (i < m->n_reads && desc[i].seq_off < target) i++;
+            jp->cut[p] = i;
+        }
+        jp->cut[parts] = m->n_reads;
+    }
+    pool_run(&s->pool, r->splice_mode ? fmt_fields_part : fmt_part, jp);
+    const double t_f = dsb_now();
+    if (r->splice_mode) {
+        dsb_strbuf *out = (dsb_strbuf *)r->ctx;
+        size_t total = 0;
+        for (int p = 0; p < parts; p++) { jp->off[p] = total; total += jp->len[p]; }
+        if (out->l + total + 1 > out->m) {
+            /* the block must grow (the size of the input was unknown or the estimate short): nobody may be writing into it */
+            prefault_join(r);
+            pthread_mutex_lock(&r->mu);
+            while (r->spliced < b) pthread_cond_wait(&r->cv, &r->mu);
+            pthread_mutex_unlock(&r->mu);
+            dsb_strbuf_reserve(out, total);
+        }
+        jp->dst = out->s + out->l;
+        out->l += total;
+        pthread_mutex_lock(&r->mu);
+        r->formatted = b + 1;
+        pthread_cond_broadcast(&r->cv);
+        pthread_mutex_unlock(&r->mu);
+    } else if (r->sink) {
+        for (int p = 0; p < parts; p++)
+            if (s->fmt_buf[bank][p].l) r->sink(r->ctx, s->fmt_buf[bank][p].s, s->fmt_buf[bank][p].l);
+    } else {
+        /* direct mode: ctx is the caller's dsb_strbuf; every thread copies its own part */
+        dsb_strbuf *out = (dsb_strbuf *)r->ctx;
+        size_t total = 0;
+        for (int p = 0; p < parts; p++) { jp->off[p] = total; total += s->fmt_buf[bank][p].l; }
+        if (out->l + total + 1 > out->m) prefault_join(r);
+        dsb_strbuf_reserve(out, total);
+        jp->dst = out->s + out->l;
+        pool_run(&s->pool, copy_part, jp);
+        out->l += total;
+    }
+    double t2 = dsb_now();
+    if (st) {
+        float a = 0, bb = 0, d = 0;
+        dsb_slot_timing(s->slots[k], &a, &bb, &d);
+        st->gpu_ms_total += a; st->gpu_ms_exist += bb; st->gpu_ms_classify += d;
+        st->t_gpu_wait += t1 - t0;
+        st->t_format += t2 - t1;
+        if (r->verbose)
+            fprintf(stderr, "[dsb]   slot %d: wait %.1f ms, format %.1f ms, sink %.1f ms | gpu %.2f ms | t: waited from %.2f, results at %.2f, text at %.2f, sunk at %.2f\n",
+                    k, 1e3 * (t1 - t0), 1e3 * (t_f - t1), 1e3 * (t2 - t_f), a, 1e3 * (t0 - r->t_start), 1e3 * (t1 - r->t_start), 1e3 * (t_f - r->t_start), 1e3 * (t2 - r->t_start));
+        add_counters(&st->counters, &c);
+    }
 }
 
 static void *drain_thread(void *argp)
 {
     run_ctx *r = (run_ctx *)argp;
-    if (r->prefault_n) {
-        /* not before the first batch is on its way: until then the copy pool's work is on the critical path */
-        pthread_mutex_lock(&r->mu);
-        while (r->submitted == 0 && !r->done) pthread_cond_wait(&r->cv, &r->mu);
-        pthread_mutex_unlock(&r->mu);
-        const double t0 = dsb_now();
-        pool_run(&r->s->pool, prefault_part, r);
-        if (r->verbose) fprintf(stderr, "[dsb]   output block touched: %.1f MB in %.2f ms (until %.2f ms)\n", r->prefault_n / 1e6, 1e3 * (dsb_now() - t0), 1e3 * (dsb_now() - r->t_start));
-    }
     for (uint64_t b = 0;; b++) {
         pthread_mutex_lock(&r->mu);
         while (r->submitted <= b && !r->done) pthread_cond_wait(&r->cv, &r->mu);
         const int have = r->submitted > b;
         pthread_mutex_unlock(&r->mu);
-        if (!have) return NULL;
-        drain_slot(r->s, (int)(b % (uint64_t)r->s->n_slots), r->o, r->sink, r->ctx, r->stats, r->t_start);
+        if (!have) break;
+        drain_slot(r, b, (int)(b % (uint64_t)r->s->n_slots));
+        if (!r->splice_mode) {
+            pthread_mutex_lock(&r->mu);
+            r->drained = b + 1;
+            pthread_cond_broadcast(&r->cv);
+            pthread_mutex_unlock(&r->mu);
+        }
+    }
+    pthread_mutex_lock(&r->mu);
+    r->format_done = 1;
+    pthread_cond_broadcast(&r->cv);
+    pthread_mutex_unlock(&r->mu);
+    return NULL;
+}
+
+/* second pass of the direct SAM_FULL mode: fields, SEQ and QUAL of batch b to their final place in the caller's block; the
+ * slot (its pinned staging holds the bases) is free for the producer once this is done */
+static void *splice_thread(void *argp)
+{
+    run_ctx *r = (run_ctx *)argp;
+    for (uint64_t b = 0;; b++) {
         pthread_mutex_lock(&r->mu);
+        while (r->formatted <= b && !r->format_done) pthread_cond_wait(&r->cv, &r->mu);
+        const int have = r->formatted > b;
+        pthread_mutex_unlock(&r->mu);
+        if (!have) return NULL;
+        const double t0 = dsb_now();
+        pool_run(&r->s->spool, splice_part, &r->sj[b & 1]);
+        if (r->verbose)
+            fprintf(stderr, "[dsb]   batch %llu spliced %.2f..%.2f ms\n", (unsigned long long)b, 1e3 * (t0 - r->t_start), 1e3 * (dsb_now() - r->t_start));
+        if (r->stats) r->stats->t_format += dsb_now() - t0;
+        pthread_mutex_lock(&r->mu);
+        r->spliced = b + 1;
         r->drained = b + 1;
         pthread_cond_broadcast(&r->cv);
         pthread_mutex_unlock(&r->mu);
@@ -637,8 +719,9 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     r.verbose = getenv("DSB_VERBOSE") != NULL;
     pthread_mutex_init(&r.mu, NULL);
     pthread_cond_init(&r.cv, NULL);
-    pthread_t th, th_submit;
+    pthread_t th, th_submit, th_splice;
     int eof = 0;
+    r.splice_mode = (!sink && o->format == DSB_OUT_SAM_FULL);
     s->have_carry = 0;
     /* a call that is only a few batches long (in-memory input of known size, ~2 bytes per base) uses the small batch
      * size: the device starts earlier and the last batch's text is shorter */
@@ -647,22 +730,34 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
         const uint64_t bytes = dsb_fq_remaining_bytes(f);
         if (bytes != UINT64_MAX && bytes / 2 <= 4 * s->e->batch_small) call_batch = s->e->batch_small;
     }
-    if (!sink && s->e->fmt_threads > 1) {
-        /* direct mode: the caller's output block is fresh memory; the formatter helpers, idle until the first batch
-         * comes back from the device, touch its pages now instead of faulting them in on the critical path */
-        dsb_strbuf *out = (dsb_strbuf *)ctx;
-        if (out->m - out->l >= ((size_t)8 << 20)) {
-            r.prefault_lo = out->s + out->l;
-            r.prefault_n = out->m - out->l;
-        }
-    }
     {
         double t0 = dsb_now();
         dsb_fq_prescan(f, s->e->scan_threads);
         stats->t_parse += dsb_now() - t0;
         if (r.verbose) fprintf(stderr, "[dsb]   prescan done at %.2f ms\n", 1e3 * (dsb_now() - t_start));
     }
+    prefault_arg pf_arg[8];
+    if (!sink && s->e->fmt_threads > 1) {
+        /* direct mode: the caller's output block is fresh memory.  A few threads touch its pages front to back in the
+         * background, so that neither the first drain waits for 4 GB of page faults (64 ms on the 2-GPU trace of round 2)
+         * nor the splice threads take them one by one */
+        dsb_strbuf *out = (dsb_strbuf *)ctx;
+        if (out->m - out->l >= ((size_t)8 << 20)) {
+            r.prefault_lo = out->s + out->l;
+            r.prefault_n = out->m - out->l;
+            int n = s->e->fmt_threads / 3;
+            if (n < 1) n = 1;
+            if (n > 4) n = 4;
+            for (int i = 0; i < n; i++) {
+                pf_arg[i].r = &r;
+                pf_arg[i].id = i;
+                r.prefault_threads = n;
+                if (pthread_create(&r.prefault_th[i], NULL, prefault_thread, &pf_arg[i]) != 0) { r.prefault_threads = i; break; }
+            }
+        }
+    }
     /* the helpers start once the pre-scan (which uses every core) is over */
+    if (r.splice_mode && pthread_create(&th_splice, NULL, splice_thread, &r) != 0) dsb_fatal("pthread_create failed");
     if (pthread_create(&th, NULL, drain_thread, &r) != 0) dsb_fatal("pthread_create failed");
     if (pthread_create(&th_submit, NULL, submit_thread, &r) != 0) dsb_fatal("pthread_create failed");
     for (uint64_t b = 0; !eof; b++) {
@@ -717,6 +812,8 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     pthread_mutex_unlock(&r.mu);
     pthread_join(th_submit, NULL);
     pthread_join(th, NULL);
+    if (r.splice_mode) pthread_join(th_splice, NULL);
+    prefault_join(&r);
     dsb_history_end_batch(s->hist);
     dsb_history_all_drained(s->hist);
     pthread_mutex_destroy(&r.mu);
