@@ -187,6 +187,7 @@ struct DsbReadSeeds {             // per read, written by k_islands
 
 struct DsbStats {
     unsigned long long occ, lut, sa, unitig, refpos, ref_bytes, mem_search, map_seed, sdp_win, slow;
+    uint32_t ex0, ex1;            // exist-table probes of the on-demand island scan (the warp's)
     unsigned long long cyc[8];    // SM cycles per phase (device only; see dsb_counters.phase_cycles)
 };
 
@@ -524,6 +525,34 @@ DSB_HD uint8_t dsb_exist_kmer(const DsbIndexView *ix, const uint8_t *s, uint32_t
 // islands (restates search_exist_kmer_M2 src/cly.c:1066-1155 and the `top` marking of
 // get_seed_vector_M2 src/cly.c:1157-1229).  ex[i] = exist bit of k-mer i, n = L-k+1.
 // ------------------------------------------------------------------------------------------
+// top 1 island per 100 bp window of the ns islands in w->seeds[strand] (the `top` marking of get_seed_vector_M2
+// src/cly.c:1157-1229), and the strand's score
+DSB_HDO void dsb_islands_mark(DsbWork *w, int strand, uint32_t ns)
+{
+    const uint32_t n = w->L - (uint32_t)w->ix->ek_len + 1;
+    DsbSeed *sv = w->seeds[strand];
+    // top 1 island per 100 bp window (SURVEY.md Q4: replayed literally)
+    uint32_t total = 0, max_index = 0, max_length = 0, index_end = DSB_SEED_RANGE;
+    for (uint32_t m = 0; m < ns; m++) {
+        sv[m].top = 0;
+        const uint32_t key = (strand == 0) ? sv[m].offset : (n - sv[m].offset - sv[m].len);
+        if (key < index_end) {
+            if (max_length < sv[m].len) { max_length = sv[m].len; max_index = m; }
+            sv[max_index].top = 0;
+        } else {
+            sv[max_index].top = 1;
+            index_end += DSB_SEED_RANGE;
+            total += max_length;
+            max_index = m;
+            max_length = sv[m].len;
+        }
+    }
+    sv[max_index].top = 1;      // also executed with ns == 0 in the reference (harmless there too)
+    total += max_length;
+    w->n_seeds[strand] = ns;
+    w->total_score[strand] = total;
+}
+
 DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
 {
     const uint8_t *ex = w->exist[strand];
@@ -621,26 +650,82 @@ DSB_HDO void dsb_islands(DsbWork *w, int strand /*0 fwd, 1 rev*/)
         }
     }
 #endif
-    // top 1 island per 100 bp window (SURVEY.md Q4: replayed literally)
-    uint32_t total = 0, max_index = 0, max_length = 0, index_end = DSB_SEED_RANGE;
-    for (uint32_t m = 0; m < ns; m++) {
-        sv[m].top = 0;
-        const uint32_t key = (strand == 0) ? sv[m].offset : (n - sv[m].offset - sv[m].len);
-        if (key < index_end) {
-            if (max_length < sv[m].len) { max_length = sv[m].len; max_index = m; }
-            sv[max_index].top = 0;
-        } else {
-            sv[max_index].top = 1;
-            index_end += DSB_SEED_RANGE;
-            total += max_length;
-            max_index = m;
-            max_length = sv[m].len;
+    dsb_islands_mark(w, strand, ns);
+}
+
+#if defined(DSB_DEVICE_CODE)
+// The island scan of BOTH strands with the exist tables probed on demand: no exist byte is computed for a k-mer the scan
+// never looks at.  The reference probes every third k-mer and, around a hit, its neighbours (search_exist_kmer_M2
+// src/cly.c:1066-1155); a probe is a pure function of the k-mer, so which positions are probed besides those does not
+// change the islands.  Half a warp per strand, both halves in lock step (one converged probe per round):
+//   lattice round : 16 candidates u, u+3, ..., u+45 -- none set: u += 48
+//   first run round: the two k-mers before the hit and the 14 behind it
+//   more run rounds: 16 further k-mers each, until one is clear or the island is 61 long
+// u counts k-mers in scan direction: the reverse strand is scanned from its last k-mer downwards (u = n-1-i), which makes
+// its scan the forward scan of the mirrored exist row.
+__device__ __noinline__ void dsb_islands_probe(DsbWork *w)
+{
+    const int lane = (int)(threadIdx.x & 31);
+    const int h = lane >> 4, tl = lane & 15;
+    const int nn = (int)(w->L - (uint32_t)w->ix->ek_len + 1);
+    const uint8_t *s = w->bin + (h ? w->L : 0);
+    DsbSeed *sv = w->seeds[h];
+    uint32_t ns = 0, p0 = 0, p1 = 0;
+    int u = DSB_STEP_EK - 1;
+    int mode = (u < nn) ? 0 : 3;          // 0 lattice, 1 first run round, 2 further run rounds, 3 done
+    int ui = 0, b1 = 0, b2 = 0, run = 0;
+    while (__any_sync(0xffffffffu, mode != 3)) {
+        int q = -1;
+        if (mode == 0) q = u + DSB_STEP_EK * tl;
+        else if (mode == 1) q = (tl < 2) ? ui - 1 - tl : ui + tl - 1;
+        else if (mode == 2) q = ui + 1 + run + tl;
+        uint8_t e = 0;
+        if (q >= 0 && q < nn) e = dsb_exist_kmer(w->ix, s + (h ? nn - 1 - q : q), &p0, &p1);
+        const uint32_t hb = (__ballot_sync(0xffffffffu, e == 1) >> (16 * h)) & 0xffffu;
+        bool close = false;
+        if (mode == 0) {
+            if (!hb) { u += DSB_STEP_EK * 16; if (u >= nn) mode = 3; }
+            else { ui = u + DSB_STEP_EK * (__ffs((int)hb) - 1); mode = 1; }
+        } else if (mode == 1) {
+            b1 = (int)(hb & 1u);
+            b2 = b1 & (int)((hb >> 1) & 1u);
+            const uint32_t fw = hb >> 2;                  // 14 k-mers behind the hit
+            if (fw == 0x3fffu) { run = 14; mode = 2; }
+            else { run = __ffs((int)~fw) - 1; close = true; }
+        } else if (mode == 2) {
+            if (hb == 0xffffu) { run += 16; close = run >= 61 - (1 + b1 + b2); }
+            else { run += __ffs((int)~hb) - 1; close = true; }
+        }
+        if (close) {
+            const int len0 = 1 + b1 + b2;
+            const int len = len0 + DSB_MIN(run, 61 - len0);       // the reference stops right after len reaches 61
+            const int uoff = ui - b1 - b2;
+            if (tl == 0) {
+                sv[ns].offset = (uint32_t)(h ? nn - uoff - len : uoff);
+                sv[ns].len = (uint32_t)len;
+            }
+            ns++;
+            u = uoff + len + DSB_STEP_EK;
+            mode = (u < nn) ? 0 : 3;
         }
     }
-    sv[max_index].top = 1;      // also executed with ns == 0 in the reference (harmless there too)
-    total += max_length;
-    w->n_seeds[strand] = ns;
-    w->total_score[strand] = total;
+    w->st.ex0 += __reduce_add_sync(0xffffffffu, p0);      // the warp's probes, the same in every lane
+    w->st.ex1 += __reduce_add_sync(0xffffffffu, p1);
+    __syncwarp();
+    const uint32_t ns0 = __shfl_sync(0xffffffffu, ns, 0), ns1 = __shfl_sync(0xffffffffu, ns, 16);
+    dsb_islands_mark(w, 0, ns0);
+    dsb_islands_mark(w, 1, ns1);
+}
+#endif
+
+// islands of both strands: from the exist bytes where the caller computed them, else by probing on demand
+DSB_HDO void dsb_islands_both(DsbWork *w)
+{
+#if defined(DSB_DEVICE_CODE)
+    if (!w->exist[0]) { dsb_islands_probe(w); return; }
+#endif
+    dsb_islands(w, 0);
+    dsb_islands(w, 1);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -2585,10 +2670,7 @@ DSB_HDN void dsb_classify_tail(DsbWork *w, int dir0, int dir1, bool both_directi
     if (run_slow_mode && !w->overflow) {
         w->st.slow++;
         w->n_anchor = 0;
-        if (!have_islands) {                                                // split pipeline: the islands stayed in k_islands
-            dsb_islands(w, 0);
-            dsb_islands(w, 1);
-        }
+        if (!have_islands) dsb_islands_both(w);                             // split pipeline: the islands stayed in k_islands
         dsb_slow_classify(w, dir0);
         dsb_resolve_tree(w);
         if (both_direction || w->n_chain <= 0 || (w->chains[0].anchor_number < 5)) {
@@ -2613,8 +2695,7 @@ DSB_HDN void dsb_classify_read(DsbWork *w)
     w->had_chain = 0;
     if (w->L < 40) return;                                                  // MIN_READ_LEN
     DSB_PHASE_BEGIN();
-    dsb_islands(w, 0);
-    dsb_islands(w, 1);
+    dsb_islands_both(w);
     DSB_PHASE_END(w, 0);
     // search_dir[0] = forward unless the reverse strand scores strictly higher
     int dir0 = 0, dir1 = 1;

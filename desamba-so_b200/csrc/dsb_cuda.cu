@@ -91,6 +91,7 @@ struct dsb_slot {
     size_t scratch_bytes;
     // split pipeline (k_islands -> k_seed -> k_classify)
     bool split;
+    bool exist_bytes;        // k_exist writes one byte per k-mer first (default); DSB_EXIST_ON_DEMAND=1: the island scan probes the tables itself
     DsbReadSeeds *d_rinfo;
     DsbSeedJob *d_jobs;
     DsbAnchor *d_pool;
@@ -828,10 +829,9 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_island
             const long long t0 = clock64();
             w.bin = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
             w.L = d.len;
-            w.exist[0] = exist + 2 * d.seq_off;
-            w.exist[1] = w.exist[0] + d.len;
-            dsb_islands(&w, 0);
-            dsb_islands(&w, 1);
+            w.exist[0] = exist ? exist + 2 * d.seq_off : nullptr;     // no exist bytes: the scan probes the tables itself
+            w.exist[1] = exist ? w.exist[0] + d.len : nullptr;
+            dsb_islands_both(&w);
             rs.total_score[0] = w.total_score[0];
             rs.total_score[1] = w.total_score[1];
             int dir0 = 0, dir1 = 1;
@@ -883,6 +883,10 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_island
         __syncwarp();
     }
     if (lane == 0 && cyc) atomicAdd((unsigned long long *)&ctrl->counters.phase_cycles[0], cyc);
+    if (lane == 0 && w.st.ex0) {
+        atomicAdd((unsigned long long *)&ctrl->counters.exist_probes0, (unsigned long long)w.st.ex0);
+        atomicAdd((unsigned long long *)&ctrl->counters.exist_probes1, (unsigned long long)w.st.ex1);
+    }
 }
 
 // persistent warps, ONE LANE PER ISLAND of the whole batch
@@ -960,8 +964,8 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
         w.bin = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
         w.L = d.len;
         w.is_2g = (d.flags & DSB_READ_2G) ? 1u : 0u;
-        w.exist[0] = exist + 2 * d.seq_off;
-        w.exist[1] = w.exist[0] + d.len;
+        w.exist[0] = exist ? exist + 2 * d.seq_off : nullptr;
+        w.exist[1] = exist ? w.exist[0] + d.len : nullptr;
         w.overflow = 0;
         memset(&w.st, 0, sizeof w.st);
 #if defined(DSB_READ_CYCLES)
@@ -1012,6 +1016,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
             DSB_ADD(ref_window_bytes, w.st.ref_bytes); DSB_ADD(mem_searches, w.st.mem_search);
             DSB_ADD(map_seeds, w.st.map_seed); DSB_ADD(sdp_windows, w.st.sdp_win);
             DSB_ADD(anchors, w.n_anchor); DSB_ADD(slow_reads, w.st.slow);
+            DSB_ADD(exist_probes0, w.st.ex0); DSB_ADD(exist_probes1, w.st.ex1);
             for (int ph = 0; ph < 8; ph++) DSB_ADD(phase_cycles[ph], w.st.cyc[ph]);
 #undef DSB_ADD
         }
@@ -1489,7 +1494,14 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
     TRY(cudaMalloc((void **)&s->d_desc, (size_t)max_reads * sizeof(dsb_read_desc)));
     TRY(cudaMalloc((void **)&s->d_edge, edge_bytes));
     TRY(cudaMalloc((void **)&s->d_bin, dsb_bin_bytes(max_bases, max_reads)));
-    TRY(cudaMalloc((void **)&s->d_exist, 2 * max_bases + 64));
+    {
+        // A/B on cfg3 (profiles/ab_r02.txt): probing on demand saves only 16 % of the first-table probes -- on a 1 Gbp index
+        // one 17-mer in ten passes both tables, so the scan meets an island every ~30 positions and looks at most of the row
+        // anyway -- and turns a bandwidth-bound pass into a latency-bound one: 72.7 ms against 49.8 + 9.7 ms
+        const char *e = getenv("DSB_EXIST_ON_DEMAND");
+        s->exist_bytes = !(e && atoi(e) != 0);
+    }
+    if (s->exist_bytes) TRY(cudaMalloc((void **)&s->d_exist, 2 * max_bases + 64));
     TRY(cudaMalloc((void **)&s->d_results, (size_t)max_reads * sizeof(dsb_read_result)));
     TRY(cudaMalloc((void **)&s->d_ctrl, sizeof(DsbCtrl)));
     TRY(cudaMalloc((void **)&s->d_order, (size_t)max_reads * 4));
@@ -1596,7 +1608,7 @@ static int launch_kernels(dsb_slot *s)
     const uint32_t grid_r = n < (uint32_t)(sm * 8) ? n : (uint32_t)(sm * 8);
     k_encode<<<grid_r, 256, 0, s->stream>>>(s->d_seq, s->d_desc, s->d_edge, s->d_bin, n);
     CU(cudaEventRecord(s->ev[1], s->stream));
-    k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
+    if (s->exist_bytes) k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
     CU(cudaEventRecord(s->ev[2], s->stream));
     // small batches: no more warps than reads (the other slots' kernels fill the rest of the device)
     const int warps_per_block = s->threads / 32;
@@ -1621,7 +1633,7 @@ static int launch_kernels(dsb_slot *s)
     }
     CU(cudaEventRecord(s->ev[3], s->stream));
     CU(cudaGetLastError());
-    g_launches += 3;
+    g_launches += s->exist_bytes ? 3 : 2;
     CU(cudaMemcpyAsync(s->h_ctrl, s->d_ctrl, sizeof(DsbCtrl), cudaMemcpyDeviceToHost, s->stream));
     CU(cudaMemcpyAsync(s->h_results, s->d_results, (size_t)n * sizeof(dsb_read_result), cudaMemcpyDeviceToHost, s->stream));
     return 0;

@@ -283,6 +283,14 @@ def test_resident_index_repeated_batches_with_meta_analysis(api, mixed, have_ref
     assert rss1 - rss0 <= (64 << 20), (rss0, rss1)             # host: allocator noise only
 
 
+@pytest.mark.parametrize("name", ["tiny", "mixed", "cfg2"])
+def test_exist_on_demand_equals_exist_bytes(name, request):
+    """DSB_EXIST_ON_DEMAND=1: no k_exist pass, the island scan of k_islands (and of the slow path in k_classify) probes the
+    exist tables itself, half a warp per strand.  A probe is a pure function of the k-mer, so the output must not change."""
+    ds = request.getfixturevalue(name)
+    assert run_cli(ds["idx"], ds["reads"], env={"DSB_EXIST_ON_DEMAND": "1"}) == run_cli(ds["idx"], ds["reads"])
+
+
 def test_device_reblocking_equals_host_reblocking(tiny):
     """Index upload: k_fm_reblock (device) writes the same FM blocks, byte for byte, as the host re-blocking function
     that the host simulator uses (DSB_VERIFY_REBLOCK makes dsb_index_upload compare them and fail otherwise)."""
