@@ -621,7 +621,7 @@ def inproc_leg(meta, n_gpu, e2e_per_gpu):
     for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
         env.pop(k, None)
     r = subprocess.run([sys.executable, "-c", INPROC_CHILD, ROOT, meta["idx"], meta["reads"], sample, str(n_gpu), "3"],
-                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env)
+                       stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=env, timeout=900)
     m = re.search(r"^INPROC (.*)$", r.stdout.decode(errors="replace"), re.M)
     if r.returncode != 0 or not m:
         raise RuntimeError("in-process leg failed: " + r.stderr.decode(errors="replace")[-600:])

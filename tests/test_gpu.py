@@ -287,7 +287,9 @@ def test_resident_index_repeated_batches_with_meta_analysis(api, mixed, have_ref
 def test_exist_on_demand_equals_exist_bytes(name, request):
     """DSB_EXIST_ON_DEMAND=1: no k_exist pass, the island scan of k_islands (and of the slow path in k_classify) probes the
     exist tables itself, half a warp per strand.  A probe is a pure function of the k-mer, so the output must not change."""
-    ds = request.getfixturevalue(name)
+    request.getfixturevalue("tiny")                 # the build and the reference binary
+    import dataset
+    ds = dataset.build(name)
     assert run_cli(ds["idx"], ds["reads"], env={"DSB_EXIST_ON_DEMAND": "1"}) == run_cli(ds["idx"], ds["reads"])
 
 
