@@ -1,13 +1,18 @@
 // dsb_cuda.cu -- sm_100a kernels + the C-ABI of include/dsb_cuda.h (libdsb_cuda.so).
 //
-// Three kernels per batch, all integer / byte work bounded by random HBM sector traffic
-// (DESIGN.md "kernels"):
+// Five kernels per batch, all integer / byte work bounded by random HBM traffic:
 //   k_encode   : ASCII -> 2-bit codes, both strands, plus the head/tail margins of the history model
-//   k_exist    : one thread per k-mer position and strand: rolling-free k-mer, low-complexity mask,
-//                two hash probes into the exist-k-mer bit tables (reference src/cly.c:951-967)
-//   k_classify : persistent grid, ONE WARP PER READ pulling reads from an atomic queue; runs
-//                dsb_classify_read (dsb_core.cuh) = islands -> FM seeding -> LV anchors -> chaining
-//                -> sparse match-block scoring -> filters -> PRI/SEC/SUP
+//   k_exist    : one thread per k-mer position and strand: k-mer, low-complexity mask, two hash probes into the
+//                exist-k-mer bit tables (reference src/cly.c:951-967)
+//   k_islands  : warp per read: the island scan of both strands over the exist bytes, `top` marking, one job per top
+//                island into the batch-wide job list (src/cly.c:1066-1229)
+//   k_seed     : persistent grid, ONE LANE PER ISLAND of the whole batch, lanes in lock step: FM backward search, locate,
+//                Landau-Vishkin anchors into the batch-wide anchor pool (src/cly.c:1339-1541, 701-934)
+//   k_classify : persistent grid, ONE WARP PER READ pulling reads from an atomic queue: chaining, sparse match-block
+//                scoring, filters, PRI/SEC/SUP; the slow path (no usable chain) re-seeds the read inside the warp
+// DSB_SPLIT=0 runs islands + seeding inside k_classify (round 1's form, kept for the parity tests of both forms);
+// DSB_EXIST_ON_DEMAND=1 drops k_exist and lets the island scan probe the tables itself.  The index builder's kernels live
+// in dsb_build.cu.
 // There is no CPU path in this file: every entry point fails with an error when CUDA fails.
 #include <cuda_runtime.h>
 #include <stdio.h>

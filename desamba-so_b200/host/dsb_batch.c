@@ -2,15 +2,22 @@
  * pipeline (reference src/cly_mt.c:29-43 read_reads, :352-381 worker_for / classify_pipeline,
  * src/lib/kthread.c kt_for / kt_pipeline).
  *
- *   parse (host, kseq semantics) -> pinned staging of slot k -> dsb_slot_submit (async H2D,
- *   kernels, D2H on the slot's stream) -> while the GPU works, parse the next batch into slot
- *   k+1 -> dsb_slot_wait(k) -> format records in input order -> sink.
+ * Threads of one dsb_session_run():
+ *   producer (the caller's thread): record loop over the pre-scanned text (kseq semantics), history bytes and the
+ *            2G / 3G class of every read in read order (dsb_history.c), descriptors into the slot's pinned staging;
+ *   submit : gathers the bases of the batch into the pinned block (helper pool), dsb_slot_submit = async H2D, five
+ *            kernels, D2H on the slot's stream;
+ *   drain  : dsb_slot_wait in submission order, formats the record fields (helper pool) -- pass 1 of the output;
+ *   splice : (SAM_FULL written straight into the caller's block) moves fields + SEQ + QUAL to their final place -- pass 2,
+ *            pipelined behind the drain thread over two banks of field text;
+ *   prefault: up to four threads touch the pages of the caller's output block ahead of the writers.
  *
- * Every GPU holds a replica of the index and two slots (double buffering); batches go to the
- * devices round-robin, results are collected in submission order, so the output order is the
- * input order and no device-to-device communication exists.  Batch boundaries
- * do not change results: the history-dependent bytes are computed on the host,
- * in read order, before a read is handed to any device (dsb_history.c).
+ * Every GPU holds a replica of the index and SLOTS_PER_GPU slots; batches go to the devices round-robin, results are
+ * collected in submission order, so the output order is the input order and no device-to-device communication exists
+ * (SURVEY.md 8e).  Batch boundaries do not change results: the history-dependent bytes are computed on
+ * the host, in read order, before a read is handed to any device; the one value that depends on RESULTS (max_read_l,
+ * reference src/cly.c:2884-2885,2953) is resolved on the host too, and the producer waits for the batches in flight
+ * only when the class of a short read hangs on them.
  */
 #include "dsb_host.h"
 #include <pthread.h>
