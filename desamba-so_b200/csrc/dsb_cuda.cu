@@ -1533,6 +1533,8 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
         int per_sm_seed = 0;
         TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_seed, k_seed, DSB_CLASSIFY_THREADS, 0));
         if (per_sm_seed < 1) per_sm_seed = 1;
+        const char *es = getenv("DSB_SEED_BLOCKS_PER_SM");
+        if (es && atoi(es) > 0 && atoi(es) < per_sm_seed) per_sm_seed = atoi(es);
         s->seed_blocks = per_sm_seed * ix->sm_count;
         if (s->seed_blocks * (DSB_CLASSIFY_THREADS / 32) > s->n_warps) s->n_warps = s->seed_blocks * (DSB_CLASSIFY_THREADS / 32);
     }

@@ -24,6 +24,41 @@
 #include <stdlib.h>
 #include <string.h>
 #include <unistd.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
+
+/* Bulk copies of the pipeline (bases into the pinned staging block, SEQ and QUAL into the caller's output block) write
+ * memory nobody reads again soon: the GPU's copy engine and the caller come much later, when a 33 MB batch has long left
+ * the caches.  Streaming stores skip the read-for-ownership of every destination line (1/3 of such a copy's memory traffic)
+ * and leave the caches to the text being parsed.  From four GPUs on the host's memory bandwidth is the bound of the whole
+ * call.  DSB_NT_COPY=0 goes back to memcpy. */
+static int g_nt_copy = -1;
+static inline void copy_stream(char *dst, const char *src, size_t n)
+{
+#if defined(__SSE2__)
+    if (g_nt_copy && n >= 256) {
+        const size_t head = (size_t)(-(uintptr_t)dst & 15u);
+        if (head) { memcpy(dst, src, head); dst += head; src += head; n -= head; }
+        size_t k = n >> 6;
+        while (k--) {
+            const __m128i a = _mm_loadu_si128((const __m128i *)src), b = _mm_loadu_si128((const __m128i *)(src + 16));
+            const __m128i c = _mm_loadu_si128((const __m128i *)(src + 32)), d = _mm_loadu_si128((const __m128i *)(src + 48));
+            _mm_stream_si128((__m128i *)dst, a); _mm_stream_si128((__m128i *)(dst + 16), b);
+            _mm_stream_si128((__m128i *)(dst + 32), c); _mm_stream_si128((__m128i *)(dst + 48), d);
+            src += 64; dst += 64;
+        }
+        n &= 63;
+    }
+#endif
+    if (n) memcpy(dst, src, n);
+}
+static inline void copy_stream_done(void)
+{
+#if defined(__SSE2__)
+    _mm_sfence();          /* streaming stores become visible before the pool reports the part as done */
+#endif
+}
 
 #define SLOTS_PER_GPU 4          /* default; DSB_SLOTS overrides (1..8) */
 #define MAX_FMT_THREADS 32
@@ -152,6 +187,7 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     if (share > 1) ncpu = ncpu / share > 0 ? ncpu / share : 1;
     /* formatter / copy helpers: all but a few cores (producer, submit and drain threads, the CUDA driver's own) up to 12:
      * 16 cores: 8 -> 12 helpers took 1.4 ms off a 22 ms call */
+    if (g_nt_copy < 0) g_nt_copy = env_u64("DSB_NT_COPY", 1) != 0;
     e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 12 ? (ncpu - 4 > 12 ? 12 : ncpu - 4) : (ncpu > 8 ? 8 : ncpu)));
     e->scan_threads = (int)(ncpu > 32 ? 32 : ncpu);
     if (e->fmt_threads < 1) e->fmt_threads = 1;
@@ -306,7 +342,8 @@ static void copy_seq_part(void *arg, int part, int n_parts)
     uint32_t a = 0, b = j->n;
     while (a < b) { const uint32_t mid = (a + b) / 2; if (j->desc[mid].seq_off < lo) a = mid + 1; else b = mid; }
     for (uint32_t i = a; i < j->n && j->desc[i].seq_off < hi; i++)
-        if (j->src[i]) memcpy(j->seq + j->desc[i].seq_off, j->src[i], j->desc[i].len);
+        if (j->src[i]) copy_stream(j->seq + j->desc[i].seq_off, j->src[i], j->desc[i].len);
+    copy_stream_done();
 }
 
 /* Record loop of one batch: descriptors, history bytes, names, quality views of up to one batch go into slot k's staging,
@@ -467,13 +504,14 @@ static void splice_part(void *arg, int part, int n_parts)
         const char *q = m->qual_ptr[i];
         if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
         memcpy(d, text + from, ins - from); d += ins - from;
-        memcpy(d, j->seq + j->desc[i].seq_off, L); d += L;
+        copy_stream(d, j->seq + j->desc[i].seq_off, L); d += L;
         *d++ = '\t';
-        if (q) { memcpy(d, q, L); d += L; }
+        if (q) { copy_stream(d, q, L); d += L; }
         else { memcpy(d, "(null)", 6); d += 6; }
         memcpy(d, text + ins, end - ins); d += end - ins;
         from = end;
     }
+    copy_stream_done();
 }
 
 static void copy_part(void *arg, int part, int n_parts)
