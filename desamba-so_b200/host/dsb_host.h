@@ -85,6 +85,7 @@ int64_t dsb_fq_next_view(dsb_fq *f, dsb_rec_view *v);
 /* memory mode: find the records of the whole block with n_threads threads ahead of time (same records, same order
  * as the sequential reader; see dsb_fastq.c); a no-op for streams */
 void dsb_fq_prescan(dsb_fq *f, int n_threads);
+int dsb_fq_scan_pieces(const dsb_fq *f);     /* pieces the pre-scan has gone through so far */
 
 /* ---- worker-buffer history ------------------------------------------- */
 typedef struct dsb_history dsb_history;

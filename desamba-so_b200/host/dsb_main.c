@@ -44,7 +44,7 @@ static int classify_main(int argc, char *argv[])
     FILE *outfile = stdout;
     while ((c = getopt(argc, argv, "ht:l:r:f:o:s:g:")) >= 0) {
         if (c == 'h') { classify_usage(); return 0; }
-        else if (c == 't') { (void)atoi(optarg); }
+        else if (c == 't') { /* accepted and ignored: results are those of -t 1 */ }
         else if (c == 'l') L_min_matching = atoi(optarg);
         else if (c == 'r') max_sec_N = atoi(optarg);
         else if (c == 'o') { outfile = fopen(optarg, "w"); if (!outfile) dsb_fatal("cannot open %s", optarg); }

@@ -233,6 +233,7 @@ def _records(lib, text, threads):
             break
         out.append((C.string_at(v.name, v.name_l), C.string_at(v.seq, v.seq_l),
                     C.string_at(v.qual, v.seq_l) if v.qual else None, v.is_fastq))
+    _records.pieces = lib.dsb_fq_scan_pieces(C.c_void_p(f))
     lib.dsb_fq_close(f)
     return out
 
@@ -269,6 +270,18 @@ def test_parallel_fastq_prescan_equals_sequential_reader(built):
     clean = "".join(p for p in parts if p.startswith("@r")).encode()
     assert _records(lib, clean, 8) == _records(lib, clean, 0)
     assert _records(lib, clean[:-7], 8) == _records(lib, clean[:-7], 0)
+    # the block is scanned piece by piece (the first batch starts after the first piece): several pieces, then a rest too
+    # small for the threads, then -- in the mixed text -- a piece that ends at a record the fast recogniser refuses
+    os.environ["DSB_SCAN_PIECE"] = str(1 << 20)
+    try:
+        big = clean * 3
+        want_big = _records(lib, big, 0)
+        for threads in (1, 3, 8):
+            assert _records(lib, big, threads) == want_big
+            assert _records.pieces >= 5
+        assert _records(lib, clean * 2 + text, 4) == _records(lib, clean * 2 + text, 0)
+    finally:
+        del os.environ["DSB_SCAN_PIECE"]
 
 
 def test_resident_index_call_sequence_through_hostsim(mixed, have_ref_binary):
