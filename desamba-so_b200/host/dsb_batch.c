@@ -188,7 +188,10 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     /* formatter / copy helpers: all but a few cores (producer, submit and drain threads, the CUDA driver's own) up to 12:
      * 16 cores: 8 -> 12 helpers took 1.4 ms off a 22 ms call */
     if (g_nt_copy < 0) g_nt_copy = env_u64("DSB_NT_COPY", 1) != 0;
-    e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 12 ? (ncpu - 4 > 12 ? 12 : ncpu - 4) : (ncpu > 8 ? 8 : ncpu)));
+    /* one process driving four or more GPUs: the splice stage alone has to move ~4 bytes per base of every device's output
+     * (12 helpers: 2.9 ms per 33.5 Mbase batch = 11.7 Gbases/s, the bound of the 4-GPU trace); up to 24 helpers there */
+    const long cap = e->n_gpu >= 4 ? 24 : 12;
+    e->fmt_threads = (int)env_u64("DSB_FORMAT_THREADS", (uint64_t)(ncpu > 12 ? (ncpu - 4 > cap ? cap : ncpu - 4) : (ncpu > 8 ? 8 : ncpu)));
     e->scan_threads = (int)(ncpu > 32 ? 32 : ncpu);
     if (e->fmt_threads < 1) e->fmt_threads = 1;
     if (e->fmt_threads > MAX_FMT_THREADS) e->fmt_threads = MAX_FMT_THREADS;
@@ -291,7 +294,10 @@ dsb_session *dsb_session_create(dsb_engine *e)
     }
     pool_start(&s->pool, s->pool_arg, e->fmt_threads - 1);
     pool_start(&s->spool, s->spool_arg, e->fmt_threads - 1);
-    pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > 6 ? 6 : e->fmt_threads) - 1);
+    {
+        const int ccap = e->n_gpu >= 4 ? 12 : 6;       /* the submit thread's gather: 2.0 ms per batch with 6, next in line after the splice */
+        pool_start(&s->cpool, s->cpool_arg, (e->fmt_threads > ccap ? ccap : e->fmt_threads) - 1);
+    }
     s->copy_src = (const char ***)dsb_xcalloc((size_t)s->n_slots, sizeof(char **));
     for (int k = 0; k < s->n_slots; k++) s->copy_src[k] = (const char **)dsb_xmalloc((size_t)e->batch_reads * sizeof(char *));
     return s;
