@@ -88,6 +88,9 @@ struct dsb_slot {
     uint8_t *d_edge;
     uint8_t *d_bin;
     uint8_t *d_exist;
+    uint32_t *d_h1, *d_h2;      // the two exist hashes of every k-mer (sliced probing)
+    int exist_slices;           // > 0: k_exist_hash + 2 x exist_slices launches of k_exist_pass instead of k_exist
+    uint32_t exist_slice_shift;
     dsb_read_result *d_results;
     dsb_hit *d_hits;
     DsbCtrl *d_ctrl;
@@ -169,6 +172,154 @@ __global__ void __launch_bounds__(256) k_exist(const __grid_constant__ DsbIndexV
         if (p0) atomicAdd((unsigned long long *)&ctrl->counters.exist_probes0, (unsigned long long)p0);
         if (p1) atomicAdd((unsigned long long *)&ctrl->counters.exist_probes1, (unsigned long long)p1);
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// The exist probes in HASH-RANGE PASSES.  k_exist above sends every k-mer's probe wherever its hash points: two tables of
+// 256 MiB .. 4 GiB, far beyond the L2, so every probe is one 128-byte DRAM fetch (B200 fetches 128 B per random access) and
+// the kernel sits at the random-access roofline of the DRAM (49 G probes/s).  Random gathers from a table that FITS the L2
+// run at 176 G/s (<= 64 MiB; 110 G/s at 128 MiB: profiles/l2_fit_r02.txt).  So:
+//   k_exist_hash : every k-mer once, rolling (one base in, one base out): low-complexity mask, both hashes, stored 32 bits
+//                  each; the exist byte becomes "pending" (plus the hash bits above 32)
+//   k_exist_pass : one launch per table slice (stage 0: first table, stage 1: second table, for the k-mers whose first
+//                  bit was set): streams the exist bytes, probes the k-mers whose hash falls into THIS slice -- the slice
+//                  stays in the L2 for the whole launch -- and writes the outcome back into the exist byte
+// After the last pass an exist byte is 0 or 1 exactly as k_exist would have written it (a probe is a pure function of the
+// k-mer; the order of the probes is free).
+//   exist byte while in flight: bit 7 pending, bit 6 stage, bits 5..3 / 2..0 = bits 32.. of the first / second hash
+// ------------------------------------------------------------------------------------------
+#define DSB_EX_PENDING 0x80u
+#define DSB_EX_STAGE1 0x40u
+#define DSB_EX_RUN 16            // consecutive k-mers per thread in k_exist_hash
+#ifndef DSB_EX_ILP
+#define DSB_EX_ILP 8             // k-mers per thread and step in k_exist_pass
+#endif
+
+// where the hashes of read r's strand live: 16-entry aligned, so that a thread's run is one 64-byte store target
+static __device__ __forceinline__ size_t dsb_hash_base(uint64_t seq_off, uint32_t r, uint32_t L, uint32_t strand)
+{
+    const size_t b0 = (2 * (size_t)seq_off + 32 * (size_t)r + 15) & ~(size_t)15;
+    return strand ? ((b0 + L + 15) & ~(size_t)15) : b0;
+}
+
+__global__ void __launch_bounds__(256) k_exist_hash(const __grid_constant__ DsbIndexView ix,
+                                                    const dsb_read_desc *__restrict__ desc, const uint8_t *__restrict__ bin,
+                                                    uint8_t *__restrict__ exist, uint32_t *__restrict__ h1v,
+                                                    uint32_t *__restrict__ h2v, uint32_t n_reads)
+{
+    const int k = ix.ek_len;
+    const uint64_t kmask = (k >= 32) ? ~0ull : ((1ull << (2 * k)) - 1ull);
+    // counts of the four bases in four byte lanes; a lane reaches 0x80 when its count reaches single_base_max
+    const uint32_t bias = (uint32_t)(128 - ix.single_base_max) * 0x01010101u;
+    for (uint32_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
+        const dsb_read_desc d = desc[r];
+        const uint32_t L = d.len;
+        if (L < 40) continue;                                   // never classified (src/cly.c:3084)
+        const uint8_t *F = bin + dsb_bin_off(d.seq_off, r) + DSB_HEAD_PAD;
+        const uint32_t n = L - (uint32_t)k + 1;
+        const uint32_t runs = (n + DSB_EX_RUN - 1) / DSB_EX_RUN;             // per strand
+        for (uint32_t u = threadIdx.x; u < 2 * runs; u += blockDim.x) {
+            const uint32_t strand = (u >= runs) ? 1u : 0u;
+            const uint32_t base = (u - strand * runs) * DSB_EX_RUN;
+            const uint32_t m = DSB_MIN((uint32_t)DSB_EX_RUN, n - base);
+            const uint8_t *sq = F + strand * L + base;
+            uint8_t *ex = exist + 2 * d.seq_off + strand * L + base;
+            const size_t hb = dsb_hash_base(d.seq_off, r, L, strand) + base;
+            uint64_t kmer = 0;
+            uint32_t cnt = 0;
+            for (int i = 0; i < k - 1; i++) {
+                const uint32_t b = sq[i] & 3u;
+                kmer = (kmer << 2) | b;
+                cnt += 1u << (8 * b);
+            }
+            uint32_t a1[4], a2[4];
+#pragma unroll 1
+            for (uint32_t j0 = 0; j0 < m; j0 += 4) {
+#pragma unroll
+                for (uint32_t jj = 0; jj < 4; jj++) {
+                    const uint32_t j = j0 + jj;
+                    uint32_t e = 0, v1 = 0, v2 = 0;
+                    if (j < m) {
+                        const uint32_t b = sq[j + k - 1] & 3u;
+                        kmer = ((kmer << 2) | b) & kmask;
+                        cnt += 1u << (8 * b);
+                        if ((((cnt + bias) & 0x80808080u) == 0) && kmer != 0) {
+                            const uint64_t g1 = dsb_hash64_1(kmer) & ix.ek_mask, g2 = dsb_hash64_2(kmer) & ix.ek_mask;
+                            v1 = (uint32_t)g1; v2 = (uint32_t)g2;
+                            e = DSB_EX_PENDING | ((uint32_t)(g1 >> 32) << 3) | (uint32_t)(g2 >> 32);
+                        }
+                        __stcs(ex + j, (uint8_t)e);
+                        cnt -= 1u << (8 * (uint32_t)((kmer >> (2 * k - 2)) & 3u));       // the base that leaves next
+                    }
+                    a1[jj] = v1; a2[jj] = v2;
+                }
+                __stcs(reinterpret_cast<uint4 *>(h1v + hb + j0), make_uint4(a1[0], a1[1], a1[2], a1[3]));
+                __stcs(reinterpret_cast<uint4 *>(h2v + hb + j0), make_uint4(a2[0], a2[1], a2[2], a2[3]));
+            }
+        }
+    }
+}
+
+// one slice of one table: stage 0 = first table (pending k-mers), stage 1 = second table (k-mers whose first bit was set)
+__global__ void __launch_bounds__(256) k_exist_pass(const __grid_constant__ DsbIndexView ix,
+                                                    const dsb_read_desc *__restrict__ desc, uint8_t *__restrict__ exist,
+                                                    const uint32_t *__restrict__ hv, uint32_t n_reads, uint32_t stage,
+                                                    uint32_t slice, uint32_t slice_shift, DsbCtrl *ctrl)
+{
+    uint32_t probes = 0;
+    const uint32_t k = (uint32_t)ix.ek_len;
+    const uint8_t *__restrict__ table = stage ? ix.ek1 : ix.ek0;
+    const uint32_t want = DSB_EX_PENDING | (stage ? DSB_EX_STAGE1 : 0u);
+    for (uint32_t r = blockIdx.x; r < n_reads; r += gridDim.x) {
+        const dsb_read_desc d = desc[r];
+        const uint32_t L = d.len;
+        if (L < 40) continue;
+        const uint32_t n = L - k + 1;
+        uint8_t *ex0 = exist + 2 * d.seq_off;
+        const size_t hb0 = dsb_hash_base(d.seq_off, r, L, 0), hb1 = dsb_hash_base(d.seq_off, r, L, 1);
+        // DSB_EX_ILP k-mers per thread and step, in phases (flags, hashes, table bytes, write-back): the loads of a phase are
+        // independent, so a thread keeps DSB_EX_ILP of them in flight (one byte per thread and step left the launch
+        // latency-bound: 7-8 ms per pass over 2 G k-mers instead of the 1.5 ms its 10 GB of streaming take)
+        for (uint32_t t0 = threadIdx.x; t0 < 2 * n; t0 += blockDim.x * DSB_EX_ILP) {
+            uint8_t *ex[DSB_EX_ILP];
+            uint32_t e[DSB_EX_ILP], lo[DSB_EX_ILP];
+            size_t hx[DSB_EX_ILP];
+            bool go[DSB_EX_ILP];
+#pragma unroll
+            for (int u = 0; u < DSB_EX_ILP; u++) {
+                const uint32_t t = t0 + (uint32_t)u * blockDim.x;
+                const uint32_t strand = (t >= n) ? 1u : 0u;
+                const uint32_t p = t - strand * n;
+                ex[u] = ex0 + strand * L + p;
+                hx[u] = (strand ? hb1 : hb0) + p;
+                e[u] = (t < 2 * n) ? (uint32_t)__ldcs(ex[u]) : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < DSB_EX_ILP; u++) {
+                go[u] = (e[u] & (DSB_EX_PENDING | DSB_EX_STAGE1)) == want;
+                lo[u] = go[u] ? __ldcs(hv + hx[u]) : 0u;
+            }
+            uint64_t h[DSB_EX_ILP];
+            uint32_t byte[DSB_EX_ILP];
+#pragma unroll
+            for (int u = 0; u < DSB_EX_ILP; u++) {
+                const uint64_t hi = stage ? (e[u] & 7u) : ((e[u] >> 3) & 7u);
+                h[u] = (hi << 32) | lo[u];
+                go[u] = go[u] && (uint32_t)(h[u] >> slice_shift) == slice;
+                byte[u] = go[u] ? (uint32_t)table[h[u] >> 3] : 0u;
+            }
+#pragma unroll
+            for (int u = 0; u < DSB_EX_ILP; u++) {
+                if (!go[u]) continue;
+                probes++;
+                const uint32_t bit = (byte[u] >> (7 - (uint32_t)(h[u] & 7))) & 1u;
+                __stcs(ex[u], (uint8_t)(stage ? bit : (bit ? (e[u] | DSB_EX_STAGE1) : 0u)));
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) probes += __shfl_down_sync(0xffffffffu, probes, o);
+    if ((threadIdx.x & 31) == 0 && probes)
+        atomicAdd((unsigned long long *)(stage ? &ctrl->counters.exist_probes1 : &ctrl->counters.exist_probes0), (unsigned long long)probes);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1467,7 +1618,7 @@ void dsb_slot_free(dsb_slot *s)
     if (s->stream) cudaStreamSynchronize(s->stream);
     cudaFreeHost(s->h_seq); cudaFreeHost(s->h_desc); cudaFreeHost(s->h_edge); cudaFreeHost(s->h_results);
     cudaFreeHost(s->h_hits); cudaFreeHost(s->h_ctrl); cudaFreeHost(s->h_order);
-    cudaFree(s->d_seq); cudaFree(s->d_desc); cudaFree(s->d_edge); cudaFree(s->d_bin); cudaFree(s->d_exist);
+    cudaFree(s->d_seq); cudaFree(s->d_desc); cudaFree(s->d_edge); cudaFree(s->d_bin); cudaFree(s->d_exist); cudaFree(s->d_h1); cudaFree(s->d_h2);
     cudaFree(s->d_results); cudaFree(s->d_hits); cudaFree(s->d_ctrl); cudaFree(s->d_order); cudaFree(s->d_scratch);
     cudaFree(s->d_rinfo); cudaFree(s->d_jobs); cudaFree(s->d_pool);
     for (int i = 0; i < 8; i++) if (s->ev[i]) cudaEventDestroy(s->ev[i]);
@@ -1507,6 +1658,24 @@ int dsb_slot_create(dsb_index *ix, uint64_t max_bases, uint32_t max_reads, dsb_s
         s->exist_bytes = !(e && atoi(e) != 0);
     }
     if (s->exist_bytes) TRY(cudaMalloc((void **)&s->d_exist, 2 * max_bases + 64));
+    if (s->exist_bytes) {
+        // probes in hash-range passes (see k_exist_hash): DSB_EXIST_SLICE_MB = slice size (a power of two); default 0 = the
+        // one-pass k_exist, which is still the faster one (profiles/ab_r02.txt)
+        const uint64_t table_bits = ix->v.ek_mask + 1;
+        uint64_t slice_mb = 0;
+        const char *e = getenv("DSB_EXIST_SLICE_MB");
+        if (e) slice_mb = (uint64_t)atoll(e);
+        s->exist_slices = 0;
+        if (slice_mb > 0 && (slice_mb & (slice_mb - 1)) == 0 && table_bits > (slice_mb << 23) && (table_bits >> 35) <= 1) {
+            uint32_t sh = 23;
+            while ((1ull << sh) < (slice_mb << 23)) sh++;
+            s->exist_slice_shift = sh;
+            s->exist_slices = (int)(table_bits >> sh);
+            const size_t n_h = 2 * (size_t)max_bases + 32 * (size_t)max_reads + 64;
+            TRY(cudaMalloc((void **)&s->d_h1, n_h * 4));
+            TRY(cudaMalloc((void **)&s->d_h2, n_h * 4));
+        }
+    }
     TRY(cudaMalloc((void **)&s->d_results, (size_t)max_reads * sizeof(dsb_read_result)));
     TRY(cudaMalloc((void **)&s->d_ctrl, sizeof(DsbCtrl)));
     TRY(cudaMalloc((void **)&s->d_order, (size_t)max_reads * 4));
@@ -1615,7 +1784,15 @@ static int launch_kernels(dsb_slot *s)
     const uint32_t grid_r = n < (uint32_t)(sm * 8) ? n : (uint32_t)(sm * 8);
     k_encode<<<grid_r, 256, 0, s->stream>>>(s->d_seq, s->d_desc, s->d_edge, s->d_bin, n);
     CU(cudaEventRecord(s->ev[1], s->stream));
-    if (s->exist_bytes) k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
+    if (s->exist_bytes && s->exist_slices > 0) {
+        k_exist_hash<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, s->d_h1, s->d_h2, n);
+        for (uint32_t stage = 0; stage < 2; stage++)
+            for (int sl = 0; sl < s->exist_slices; sl++)
+                k_exist_pass<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_exist, stage ? s->d_h2 : s->d_h1, n, stage,
+                                                            (uint32_t)sl, s->exist_slice_shift, s->d_ctrl);
+        g_launches += 2 * s->exist_slices;
+    } else if (s->exist_bytes)
+        k_exist<<<grid_r, 256, 0, s->stream>>>(s->ix->v, s->d_desc, s->d_bin, s->d_exist, n, s->d_ctrl);
     CU(cudaEventRecord(s->ev[2], s->stream));
     // small batches: no more warps than reads (the other slots' kernels fill the rest of the device)
     const int warps_per_block = s->threads / 32;
