@@ -195,7 +195,13 @@ struct DsbStats {
 #define DSB_PHASE_BEGIN() long long dsb_t0_ = clock64()
 #define DSB_PHASE_BEGIN2() dsb_t0_ = clock64()
 #define DSB_PHASE_END(w, ph) do { const long long t_ = clock64(); (w)->st.cyc[ph] += (unsigned long long)(t_ - dsb_t0_); dsb_t0_ = t_; } while (0)
+#define DSB_SUB_BEGIN() long long dsb_s0_ = clock64()
+#define DSB_SUB_BEGIN2() dsb_s0_ = clock64()
+#define DSB_SUB_END(w, ph) (w)->st.cyc[ph] += (unsigned long long)(clock64() - dsb_s0_)
 #else
+#define DSB_SUB_BEGIN() ((void)0)
+#define DSB_SUB_BEGIN2() ((void)0)
+#define DSB_SUB_END(w, ph) ((void)0)
 #define DSB_PHASE_BEGIN() ((void)0)
 #define DSB_PHASE_BEGIN2() ((void)0)
 #define DSB_PHASE_END(w, ph) ((void)0)
@@ -238,6 +244,7 @@ struct DsbWork {
     // fast seeding: islands are independent work items, one lane each (dsb_fast_seeding)
     uint32_t solo;                // 1 while this lane runs an island on its own (no warp-collective code)
     uint32_t *warp_ctr;           // the warp's job counter (shared memory on the device)
+    int *smax;                    // 32 ints of shared memory for the lock-step map_seed (device)
     DsbJob *jobs;
     uint32_t cap_jobs;
     DsbAnchor *stage;             // 32 lanes x cap_stage anchors
@@ -1304,125 +1311,11 @@ DSB_HD void dsb_sort_mems(DsbMem *m, int n)
     }
 }
 
-#if defined(DSB_DEVICE_CODE)
-// slow_classify with ONE LANE PER ISLAND, 32 islands of the strand at a time.  An island's work (its k-mer loop of
-// bwt_MEM_search calls with up to 8 rows each, the sort of its MEMs, map_seed on the best 8, the useless marks) touches
-// nothing outside the island: SP_SET restarts empty and the anchors are only appended -- so the islands of a wave run side
-// by side on private SP_SET / MEM list / anchor staging and their anchors are appended in island order afterwards, which is
-// the serial result.  The warp-serial form below spent ~14 ms on a 10 kb read without a usable chain (600 islands, every
-// search a chain of dependent rank queries with 32 lanes doing the same thing): 11 % of k_classify for 5 % of the reads, and
-// the kernel's tail.  Private MEM lists live in the match-block arena (not in use before scoring); a lane that would run out
-// of MEM slots or of anchor staging makes the whole strand fall back to the serial form (returns false, nothing changed).
+#if defined(__CUDACC__)
+// slow_classify with one lane per island, in lock step (dsb_cuda.cu, next to the lock-step seeding primitives it uses);
+// false = the strand has to go through the serial form below, nothing was changed
 #define DSB_SLOW_LANE_MEMS 120
-__device__ __noinline__ bool dsb_slow_seeding_lanes(DsbWork *w, int strand)
-{
-    if ((size_t)w->cap_sms * sizeof(DsbSms) < (size_t)32 * DSB_SLOW_LANE_MEMS * sizeof(DsbMem)) return false;
-    const uint32_t lane = threadIdx.x & 31;
-    const int l_ek = w->ix->ek_len;
-    const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
-    const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
-    const DsbSeed *sv = w->seeds[strand];
-    const uint32_t nsv = w->n_seeds[strand];
-    if (nsv == 0) return true;
-    const uint32_t first_top = sv[0].top;
-    const int min_match_len = DSB_MIN(20 - 1, l_ek + 1);
-    DsbAnchor *const main_anchors = w->anchors;
-    const uint32_t main_n = w->n_anchor, main_cap = w->cap_anchor;
-    const DsbStats snap = w->st;
-    __syncwarp();
-    uint8_t *priv = w->lane_priv + (size_t)lane * DSB_LANE_PRIV_BYTES;
-    DsbSpSet sp_set = {(uint64_t *)priv, 0, DSB_SP_SET_MAX, 1};
-    DsbMem *m_r = (DsbMem *)w->sms + (size_t)lane * DSB_SLOW_LANE_MEMS;
-    DsbAnchor *const my_stage = w->stage + (size_t)lane * w->cap_stage;
-    uint32_t merged = main_n;                   // anchors of the finished waves, in the main array
-    bool bail = false;
-    uint32_t cur = 0;
-    while (cur < nsv && !bail) {
-        // the next (up to) 32 islands that pass the filter (it looks at the FIRST seed's top), in order
-        int mine = -1;
-        uint32_t filled = 0;
-        while (filled < 32 && cur < nsv) {
-            const uint32_t c = cur + lane;
-            const bool q = c < nsv && !((int)sv[c].len < 3 && first_top == 0);
-            const uint32_t m = __ballot_sync(0xffffffffu, q);
-            const uint32_t cnt = (uint32_t)__popc(m), take = DSB_MIN(cnt, 32u - filled);
-            const int t = (int)lane - (int)filled;
-            if (t >= 0 && (uint32_t)t < take) mine = (int)(cur + __fns(m, 0, t + 1));
-            if (take < cnt) { cur += __fns(m, 0, (int)take) + 1; filled = 32; }
-            else { cur += 32; filled += take; }
-        }
-        if (cur > nsv) cur = nsv;
-        // the wave: every lane its island, private state
-        w->anchors = my_stage;
-        w->cap_anchor = w->cap_stage;
-        w->n_anchor = 0;
-        w->solo = 1;
-        bool have = mine >= 0;
-        DsbSeed sd = {0, 0, 0};
-        if (have) sd = sv[mine];
-        int j = (int)sd.len - 1, n_mem = 0, t_map = -1;          // t_map >= 0: the island is in its map_seed phase
-        sp_set.l = 0;
-        while (__any_sync(0xffffffffu, have)) {
-            if (have && t_map < 0) {
-                if (j < 1) {
-                    if (n_mem > 1) dsb_sort_mems(m_r, n_mem);
-                    t_map = 0;
-                } else if (n_mem + 8 > DSB_SLOW_LANE_MEMS) {
-                    bail = true; have = false;
-                } else {
-                    const int k_idx = (int)sd.offset + j;
-                    const int s_idx = k_idx + l_ek - 1;
-                    const uint64_t pre_v = dsb_prefix13(bin_read + s_idx);
-                    const int got = dsb_mem_search(w, bin_read + s_idx, pre_v, 8, min_match_len, s_idx, &sp_set, m_r + n_mem);
-                    for (int t = n_mem; t < n_mem + got; t++) m_r[t].read_offset = k_idx + l_ek - 1 - m_r[t].match_len;
-                    n_mem += got;
-                    j -= 2;
-                }
-            }
-            __syncwarp();
-            if (have && t_map >= 0) {
-                if (t_map < DSB_MIN(n_mem, 8)) {
-                    dsb_map_seed(w, m_r + t_map, bin_read, w->L, direction);
-                    t_map++;
-                } else {
-                    dsb_mark_useless(w, 0, w->n_anchor);
-                    have = false;
-                }
-            }
-            __syncwarp();
-        }
-        w->solo = 0;
-        const uint32_t my_cnt = w->n_anchor;
-        // a lane's staging (an eighth of the read's anchor arena) ran full: the serial form has the whole arena
-        bail = __any_sync(0xffffffffu, bail || w->overflow != 0);
-        w->overflow = 0;
-        w->anchors = main_anchors;
-        w->cap_anchor = main_cap;
-        if (bail) break;
-        // append the wave's anchors in island (= lane) order
-        uint32_t pre = my_cnt;
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
-            if ((int)lane >= o) pre += v;
-        }
-        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
-        if (merged + total > main_cap) { w->overflow = 1; w->n_anchor = main_n; break; }
-        for (uint32_t k = 0; k < my_cnt; k++) main_anchors[merged + (pre - my_cnt) + k] = my_stage[k];
-        merged += total;
-        __syncwarp();
-    }
-    w->anchors = main_anchors;
-    w->cap_anchor = main_cap;
-    w->solo = 0;
-    __syncwarp();
-    if (bail) { w->n_anchor = main_n; w->st = snap; return false; }
-#define DSB_FOLD(f) w->st.f = snap.f + __reduce_add_sync(0xffffffffu, (unsigned)(w->st.f - snap.f))
-    DSB_FOLD(occ); DSB_FOLD(lut); DSB_FOLD(sa); DSB_FOLD(unitig); DSB_FOLD(refpos); DSB_FOLD(ref_bytes);
-    DSB_FOLD(mem_search); DSB_FOLD(map_seed);
-#undef DSB_FOLD
-    if (!w->overflow) w->n_anchor = merged;
-    return true;
-}
+__device__ bool dsb_slow_seeding_lanes(DsbWork *w, int strand);
 #endif
 
 DSB_HDN void dsb_slow_classify(DsbWork *w, int strand)
@@ -2795,10 +2688,14 @@ DSB_HDN void dsb_classify_tail(DsbWork *w, int dir0, int dir1, bool both_directi
         w->st.slow++;
         w->n_anchor = 0;
         if (!have_islands) dsb_islands_both(w);                             // split pipeline: the islands stayed in k_islands
+        DSB_SUB_BEGIN();
         dsb_slow_classify(w, dir0);
+        DSB_SUB_END(w, 7);                                                  // phase 7 = the seeding part of phase 3
         dsb_resolve_tree(w);
         if (both_direction || w->n_chain <= 0 || (w->chains[0].anchor_number < 5)) {
+            DSB_SUB_BEGIN2();
             dsb_slow_classify(w, dir1);                                     // appends
+            DSB_SUB_END(w, 7);
             dsb_resolve_tree(w);
         }
         DSB_PHASE_END(w, 3);

@@ -850,6 +850,135 @@ static __device__ __noinline__ int32_t dsb_map_seed_ls(DsbWork *w, uint32_t mask
 // the number of top islands of a single read is (5 kb reads have a handful, which left 3-4 lanes of 32 busy).
 // A finished island's anchors move from the lane's staging area to the batch's anchor pool.
 // w: bound to the warp's scratch slice; bin_base / desc: the batch.  Returns through jobs[], pool, *n_pool, w->st.
+// slow_classify (dsb_core.cuh; reference src/cly.c:1545-1606) with ONE LANE PER ISLAND, 32 islands of the strand at a time, the
+// lanes in lock step through the same primitives as k_seed.  An island's work (its k-mer loop of bwt_MEM_search calls with up
+// to 8 rows each, the sort of its MEMs, map_seed on the best 8, the useless marks) touches nothing outside the island: SP_SET
+// restarts empty and the anchors are only appended -- so the islands of a wave run side by side on private SP_SET / MEM list /
+// anchor staging and their anchors are appended in island order afterwards, which is the serial result.  The warp-serial form
+// spent ~11 ms on a 10 kb read without a usable chain (600 islands, every search a chain of dependent rank queries with 32
+// lanes doing the same thing): 11 % of k_classify for 5 % of the reads, and the kernel's tail.  Private MEM lists live in the
+// match-block arena (not in use before scoring); a lane that would run out of MEM slots or of anchor staging makes the whole
+// strand fall back to the serial form (returns false, nothing changed).
+__device__ __noinline__ bool dsb_slow_seeding_lanes(DsbWork *w, int strand)
+{
+    if ((size_t)w->cap_sms * sizeof(DsbSms) < (size_t)32 * DSB_SLOW_LANE_MEMS * sizeof(DsbMem) || !w->smax) return false;
+    const uint32_t lane = threadIdx.x & 31;
+    const int l_ek = w->ix->ek_len;
+    const uint8_t *bin_read = w->bin + (strand ? w->L : 0);
+    const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
+    const DsbSeed *sv = w->seeds[strand];
+    const uint32_t nsv = w->n_seeds[strand];
+    if (nsv == 0) return true;
+    const uint32_t first_top = sv[0].top;
+    const int min_match_len = DSB_MIN(20 - 1, l_ek + 1);
+    DsbAnchor *const main_anchors = w->anchors;
+    const uint32_t main_n = w->n_anchor, main_cap = w->cap_anchor;
+    const DsbStats snap = w->st;
+    __syncwarp();
+    uint8_t *priv = w->lane_priv + (size_t)lane * DSB_LANE_PRIV_BYTES;
+    DsbSpSet sp_set = {(uint64_t *)priv, 0, DSB_SP_SET_MAX, 1};
+    DsbMem *m_r = (DsbMem *)w->sms + (size_t)lane * DSB_SLOW_LANE_MEMS;
+    DsbAnchor *const my_stage = w->stage + (size_t)lane * w->cap_stage;
+    uint32_t merged = main_n;                   // anchors of the finished waves, in the main array
+    bool bail = false;
+    uint32_t cur = 0;
+    while (cur < nsv && !bail) {
+        // the next (up to) 32 islands that pass the filter (it looks at the FIRST seed's top), in order
+        int mine = -1;
+        uint32_t filled = 0;
+        while (filled < 32 && cur < nsv) {
+            const uint32_t c = cur + lane;
+            // an island of one k-mer has no k-mer loop (j = len - 1 down to 1): no search, no MEM, no anchor -- it need not take a lane
+            const bool q = c < nsv && sv[c].len >= 2 && !((int)sv[c].len < 3 && first_top == 0);
+            const uint32_t m = __ballot_sync(0xffffffffu, q);
+            const uint32_t cnt = (uint32_t)__popc(m), take = DSB_MIN(cnt, 32u - filled);
+            const int t = (int)lane - (int)filled;
+            if (t >= 0 && (uint32_t)t < take) mine = (int)(cur + __fns(m, 0, t + 1));
+            if (take < cnt) { cur += __fns(m, 0, (int)take) + 1; filled = 32; }
+            else { cur += 32; filled += take; }
+        }
+        if (cur > nsv) cur = nsv;
+        // the wave: every lane its island, private state
+        w->anchors = my_stage;
+        w->cap_anchor = w->cap_stage;
+        w->n_anchor = 0;
+        w->solo = 1;
+        bool have = mine >= 0;
+        DsbSeed sd = {0, 0, 0};
+        if (have) sd = sv[mine];
+        int j = (int)sd.len - 1, n_mem = 0, t_map = -1;          // t_map >= 0: the island is in its map_seed phase
+        sp_set.l = 0;
+        while (__any_sync(0xffffffffu, have)) {
+            bool search = false;
+            int k_idx = 0, s_idx = 0;
+            uint64_t pre_v = 0;
+            if (have && t_map < 0) {
+                if (j < 1) {
+                    if (n_mem > 1) dsb_sort_mems(m_r, n_mem);
+                    t_map = 0;
+                } else if (n_mem + 8 > DSB_SLOW_LANE_MEMS) {
+                    bail = true; have = false;
+                } else {
+                    k_idx = (int)sd.offset + j;
+                    s_idx = k_idx + l_ek - 1;
+                    pre_v = dsb_prefix13(bin_read + s_idx);
+                    search = true;
+                }
+            }
+            if (__any_sync(0xffffffffu, search)) {
+                const int got = dsb_mem_search_ls(w, 0xffffffffu, search, bin_read + s_idx, pre_v, 8, min_match_len, s_idx, &sp_set,
+                                                  m_r + n_mem);
+                if (search) {
+                    for (int t = n_mem; t < n_mem + got; t++) m_r[t].read_offset = k_idx + l_ek - 1 - m_r[t].match_len;
+                    n_mem += got;
+                    j -= 2;
+                }
+                __syncwarp();
+            }
+            const bool mp = have && t_map >= 0 && t_map < DSB_MIN(n_mem, 8);
+            if (__any_sync(0xffffffffu, mp)) {
+                dsb_map_seed_ls(w, 0xffffffffu, mp, m_r + (mp ? t_map : 0), bin_read, w->L, direction, w->smax);
+                if (mp) t_map++;
+                __syncwarp();
+            }
+            if (have && t_map >= 0 && t_map >= DSB_MIN(n_mem, 8)) {
+                dsb_mark_useless(w, 0, w->n_anchor);
+                have = false;
+            }
+        }
+        w->solo = 0;
+        const uint32_t my_cnt = w->n_anchor;
+        // a lane's staging (an eighth of the read's anchor arena) ran full: the serial form has the whole arena
+        bail = __any_sync(0xffffffffu, bail || w->overflow != 0);
+        w->overflow = 0;
+        w->anchors = main_anchors;
+        w->cap_anchor = main_cap;
+        if (bail) break;
+        // append the wave's anchors in island (= lane) order
+        uint32_t pre = my_cnt;
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
+            if ((int)lane >= o) pre += v;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+        if (merged + total > main_cap) { w->overflow = 1; w->n_anchor = main_n; break; }
+        for (uint32_t k = 0; k < my_cnt; k++) main_anchors[merged + (pre - my_cnt) + k] = my_stage[k];
+        merged += total;
+        __syncwarp();
+    }
+    w->anchors = main_anchors;
+    w->cap_anchor = main_cap;
+    w->solo = 0;
+    __syncwarp();
+    if (bail) { w->n_anchor = main_n; w->st = snap; return false; }
+#define DSB_FOLD(f) w->st.f = snap.f + __reduce_add_sync(0xffffffffu, (unsigned)(w->st.f - snap.f))
+    DSB_FOLD(occ); DSB_FOLD(lut); DSB_FOLD(sa); DSB_FOLD(unitig); DSB_FOLD(refpos); DSB_FOLD(ref_bytes);
+    DSB_FOLD(mem_search); DSB_FOLD(map_seed);
+#undef DSB_FOLD
+    if (!w->overflow) w->n_anchor = merged;
+    return true;
+}
+
 static __device__ __noinline__ void dsb_seed_jobs(DsbWork *w, const dsb_read_desc *desc, uint8_t *bin_base, DsbSeedJob *jobs, uint32_t n_jobs,
                            uint32_t *next_job, DsbAnchor *pool, uint32_t cap_pool, uint32_t *n_pool, int *smax)
 {
@@ -1101,6 +1230,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
     const DsbReadSeeds *__restrict__ rinfo, const DsbSeedJob *__restrict__ jobs, const DsbAnchor *__restrict__ pool)
 {
     __shared__ uint32_t s_job_ctr[DSB_CLASSIFY_THREADS / 32];
+    __shared__ int s_seed_max[DSB_CLASSIFY_THREADS / 32][32];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (rinfo && (ctrl->overflow & 8u)) return; // job list or anchor pool overflowed upstream: the host regrows and re-runs the batch
@@ -1109,6 +1239,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
     w.ix = &ix;
     dsb_bind_scratch(&w, scratch + (size_t)warp * dims.bytes, &dims);
     w.warp_ctr = &s_job_ctr[threadIdx.x >> 5];
+    w.smax = s_seed_max[threadIdx.x >> 5];
     __syncwarp();
     for (;;) {
         uint32_t slot = 0;
