@@ -188,6 +188,7 @@ struct DsbReadSeeds {             // per read, written by k_islands
 struct DsbStats {
     unsigned long long occ, lut, sa, unitig, refpos, ref_bytes, mem_search, map_seed, sdp_win, slow;
     uint32_t ex0, ex1;            // exist-table probes of the on-demand island scan (the warp's)
+    uint32_t slow_serial;         // strands of the slow path that took the warp-serial form as the fallback
     unsigned long long cyc[8];    // SM cycles per phase (device only; see dsb_counters.phase_cycles)
 };
 
@@ -245,6 +246,7 @@ struct DsbWork {
     uint32_t solo;                // 1 while this lane runs an island on its own (no warp-collective code)
     uint32_t *warp_ctr;           // the warp's job counter (shared memory on the device)
     int *smax;                    // 32 ints of shared memory for the lock-step map_seed (device)
+    uint32_t slow_lane_mems;      // MEM slots of a lane of the slow path (0 = default)
     DsbJob *jobs;
     uint32_t cap_jobs;
     DsbAnchor *stage;             // 32 lanes x cap_stage anchors
@@ -1325,6 +1327,7 @@ DSB_HDN void dsb_slow_classify(DsbWork *w, int strand)
     const uint8_t direction = strand ? DSB_REVERSE : DSB_FORWARD;
 #if defined(DSB_DEVICE_CODE) && !defined(DSB_SLOW_SERIAL)
     if (dsb_slow_seeding_lanes(w, strand)) { w->fast_classify = 0; return; }
+    w->st.slow_serial++;
 #endif
     DsbSpSet sp_set = {w->sp_set, 0, DSB_SP_SET_MAX, 0};
     DsbMem *mem_rst = w->mems;

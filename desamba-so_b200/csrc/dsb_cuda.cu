@@ -879,6 +879,7 @@ __device__ __noinline__ bool dsb_slow_seeding_lanes(DsbWork *w, int strand)
     DsbSpSet sp_set = {(uint64_t *)priv, 0, DSB_SP_SET_MAX, 1};
     DsbMem *m_r = (DsbMem *)w->sms + (size_t)lane * DSB_SLOW_LANE_MEMS;
     DsbAnchor *const my_stage = w->stage + (size_t)lane * w->cap_stage;
+    const int lane_mems = w->slow_lane_mems ? (int)w->slow_lane_mems : DSB_SLOW_LANE_MEMS;
     uint32_t merged = main_n;                   // anchors of the finished waves, in the main array
     bool bail = false;
     uint32_t cur = 0;
@@ -916,7 +917,7 @@ __device__ __noinline__ bool dsb_slow_seeding_lanes(DsbWork *w, int strand)
                 if (j < 1) {
                     if (n_mem > 1) dsb_sort_mems(m_r, n_mem);
                     t_map = 0;
-                } else if (n_mem + 8 > DSB_SLOW_LANE_MEMS) {
+                } else if (n_mem + 8 > lane_mems) {
                     bail = true; have = false;
                 } else {
                     k_idx = (int)sd.offset + j;
@@ -1302,7 +1303,7 @@ __global__ void __launch_bounds__(DSB_CLASSIFY_THREADS, DSB_MIN_BLOCKS) k_classi
             DSB_ADD(unitig_reads, w.st.unitig); DSB_ADD(refpos_reads, w.st.refpos);
             DSB_ADD(ref_window_bytes, w.st.ref_bytes); DSB_ADD(mem_searches, w.st.mem_search);
             DSB_ADD(map_seeds, w.st.map_seed); DSB_ADD(sdp_windows, w.st.sdp_win);
-            DSB_ADD(anchors, w.n_anchor); DSB_ADD(slow_reads, w.st.slow);
+            DSB_ADD(anchors, w.n_anchor); DSB_ADD(slow_reads, w.st.slow); DSB_ADD(slow_serial_strands, w.st.slow_serial);
             DSB_ADD(exist_probes0, w.st.ex0); DSB_ADD(exist_probes1, w.st.ex1);
             for (int ph = 0; ph < 8; ph++) DSB_ADD(phase_cycles[ph], w.st.cyc[ph]);
 #undef DSB_ADD
@@ -1725,6 +1726,11 @@ static int ensure_scratch(dsb_slot *s, uint32_t Lmax)
         s->scratch_bytes = 0;
         CU(cudaMalloc((void **)&s->d_scratch, need));
         s->scratch_bytes = need;
+    }
+    {
+        // tests: a lane of the slow path gets so few MEM slots that strands fall back to the serial form (tests/test_gpu.py)
+        const char *e = getenv("DSB_TEST_SLOW_LANE_MEMS");
+        if (e && atoi(e) > 0) d.slow_lane_mems = (uint32_t)atoi(e);
     }
     s->dims = d;
     return 0;

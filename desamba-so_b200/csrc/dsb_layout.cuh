@@ -43,6 +43,7 @@ struct DsbScratchDims {
     uint32_t head_entries;  // 16-bit bucket heads of the position-blocked 9-mer table: Lmax rounded up to whole segments
     uint32_t cap_jobs;      // top islands of both strands (<= L/100 + 1 each)
     uint32_t cap_stage;     // anchors one lane may stage during fast seeding
+    uint32_t slow_lane_mems; // MEM slots of a lane of the slow path (0 = DSB_SLOW_LANE_MEMS; tests shrink it to force the serial fallback)
     // byte offsets inside a slice
     size_t o_seeds0, o_seeds1, o_anchors, o_anchors_tmp, o_chains, o_chains_tmp, o_sort_a, o_sort_b, o_score_v,
         o_sp_set, o_mems, o_jobs, o_stage, o_lane_priv, o_sms_stage, o_sms, o_head0, o_head1, o_ent0, o_ent1, o_sc_hash, o_ref_mid, o_ref_ext;
@@ -110,6 +111,7 @@ DSB_HD void dsb_bind_scratch(DsbWork *w, uint8_t *base, const DsbScratchDims *d)
     w->cap_jobs = d->cap_jobs;
     w->stage = (DsbAnchor *)(base + d->o_stage);
     w->cap_stage = d->cap_stage;
+    w->slow_lane_mems = d->slow_lane_mems;
     w->lane_priv = base + d->o_lane_priv;
     w->solo = 0;
     w->sms = (DsbSms *)(base + d->o_sms);

@@ -82,6 +82,8 @@ static int classify_main(int argc, char *argv[])
         fprintf(stderr, "  batches %llu  parse %.3fs  gpu-wait %.3fs  format %.3fs  gpu-time %.1f ms (exist %.1f, classify %.1f)\n",
                 (unsigned long long)st.n_batches, st.t_parse, st.t_gpu_wait, st.t_format, st.gpu_ms_total, st.gpu_ms_exist,
                 st.gpu_ms_classify);
+        fprintf(stderr, "  slow-path reads %llu (strands through the serial form: %llu)\n", (unsigned long long)st.counters.slow_reads,
+                (unsigned long long)st.counters.slow_serial_strands);
     }
     double sec = dsb_now() - t1;
     fflush(outfile);

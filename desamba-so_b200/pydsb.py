@@ -28,7 +28,7 @@ class Counters(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "exist_probes0", "exist_probes1", "occ_queries", "lut_lookups", "sa_lookups", "unitig_reads", "refpos_reads",
         "ref_window_bytes", "mem_searches", "map_seeds", "sdp_windows", "anchors", "slow_reads")] + [
-        ("phase_cycles", C.c_uint64 * 8), ("seed_occ_queries", C.c_uint64), ("seed_alg_bytes", C.c_uint64)]
+        ("phase_cycles", C.c_uint64 * 8), ("seed_occ_queries", C.c_uint64), ("seed_alg_bytes", C.c_uint64), ("slow_serial_strands", C.c_uint64)]
 
     def as_dict(self):
         d = {n: int(getattr(self, n)) for n, _ in self._fields_ if n != "phase_cycles"}

@@ -119,6 +119,9 @@ typedef struct dsb_counters {
     /* k_seed's own share of the counts above (the FM-search kernel of the split pipeline): its rank queries, and its
      * algorithmic bytes = 64 x rank queries + 16 x LUT pairs + 8 x (SA + unitig + REF_POS reads) + reference-window bytes */
     uint64_t seed_occ_queries, seed_alg_bytes;
+    /* strands of slow-path reads that went through the warp-serial seeding form because a lane of the lane-per-island form
+     * would have run out of MEM slots or anchor staging (normally 0) */
+    uint64_t slow_serial_strands;
 } dsb_counters;
 
 typedef struct dsb_slot dsb_slot;  /* one CUDA stream + pinned staging + device scratch */

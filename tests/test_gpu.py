@@ -293,6 +293,23 @@ def test_exist_on_demand_equals_exist_bytes(name, request):
     assert run_cli(ds["idx"], ds["reads"], env={"DSB_EXIST_ON_DEMAND": "1"}) == run_cli(ds["idx"], ds["reads"])
 
 
+@pytest.mark.parametrize("name", ["mixed", "cfg2"])
+def test_slow_path_serial_fallback_equals_lane_per_island(name, request):
+    """The slow path (reads without a usable chain) runs one lane per island; a lane that would run out of MEM slots sends
+    its strand through the warp-serial form instead.  DSB_TEST_SLOW_LANE_MEMS=8 makes that happen for every island with a
+    second search that follows a hit; the output must not change."""
+    import re
+    request.getfixturevalue("tiny")                 # the build and the reference binary
+    import dataset
+    ds = dataset.build(name)
+    e = dict(os.environ, DSB_TEST_SLOW_LANE_MEMS="8")
+    r = subprocess.run([CLI, "classify", "-g", "1", "-f", "SAM", ds["idx"], ds["reads"]], stdout=subprocess.PIPE, stderr=subprocess.PIPE, env=e)
+    assert r.returncode == 0, r.stderr.decode()[-2000:]
+    m = re.search(r"slow-path reads (\d+) \(strands through the serial form: (\d+)\)", r.stderr.decode())
+    assert m and int(m.group(1)) > 0 and int(m.group(2)) > 0, r.stderr.decode()[-600:]      # the fallback did run
+    assert r.stdout == run_cli(ds["idx"], ds["reads"])
+
+
 def test_device_reblocking_equals_host_reblocking(tiny):
     """Index upload: k_fm_reblock (device) writes the same FM blocks, byte for byte, as the host re-blocking function
     that the host simulator uses (DSB_VERIFY_REBLOCK makes dsb_index_upload compare them and fail otherwise)."""
