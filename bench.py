@@ -549,6 +549,17 @@ def run_ours(args):
         "counters": counters,
         "clocks": sampler.result(),
     }
+    # k_exist: one random bit per probe, and B200 moves 128 B of DRAM per random access: probes/s against
+    # hbm peak / 128 B, the rate at which the DRAM can serve distinct lines at all
+    try:
+        probes = counters["exist_probes0"] + counters["exist_probes1"]
+        ex_ms = ms_exist / args.steps
+        if ex_ms > 0:
+            line["exist_probe"] = {"kernel": "k_exist", "probes": probes, "ms": ex_ms, "achieved": probes / (ex_ms * 1e-3) / 1e9,
+                                   "unit": "G probes/s", "peak": hbm_peak / 128.0, "frac": probes / (ex_ms * 1e-3) / 1e9 / (hbm_peak / 128.0),
+                                   "peak_is": "MEASURED_PEAKS hbm GB/s / 128 B per random DRAM access"}
+    except Exception as e:
+        line["exist_probe"] = {"error": str(e)}
     if not args.no_fm_probe:
         try:
             ra = random_access_peak(LOCAL_RANK)
