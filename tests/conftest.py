@@ -208,3 +208,27 @@ def max_read_l_stream(src_fastq, dst_fastq, junk_first=True, seed=17):
     for k in range(60, 100):
         out += short(pool[k % len(pool)], k)
     open(dst_fastq, "w").write("\n".join(out) + "\n")
+
+
+def exact_copy_reads(meta, tmp_path, n=3, length=3000):
+    """FASTQ of error-free copies of the reference (an exact match of 2000 bases or more makes the reference
+    index past its Q_MEM table -- reference-undefined; this build scores such a seed like a 1999-base one)."""
+    ref = os.path.join(os.path.dirname(meta["idx"].rstrip("/")), "ref.fa")
+    seqs, cur = [], []
+    for line in open(ref):
+        if line.startswith(">"):
+            if cur:
+                seqs.append("".join(cur))
+            cur = []
+        else:
+            cur.append(line.strip())
+    seqs.append("".join(cur))
+    path = os.path.join(str(tmp_path), "exact.fq")
+    comp = str.maketrans("ACGT", "TGCA")
+    with open(path, "w") as f:
+        for i in range(n):
+            s = seqs[i % len(seqs)][5000 + 1000 * i:5000 + 1000 * i + length]
+            if i % 2:
+                s = s.translate(comp)[::-1]
+            f.write("@exact%d\n%s\n+\n%s\n" % (i, s, "I" * len(s)))
+    return path

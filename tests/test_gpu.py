@@ -443,3 +443,15 @@ def test_non_acgt_lower_case_and_short_reads_equal_reference(mixed, have_ref_bin
     odd_base_reads(mixed["reads"], fq)
     for fmt in ("SAM", "SAM_FULL"):
         assert run_cli(mixed["idx"], fq, fmt=fmt) == ref_cli(["-f", fmt, mixed["idx"] + "/", fq])
+
+
+def test_exact_matches_of_2000_bases_do_not_leave_the_score_table(tiny, tmp_path):
+    """SURVEY.md Q12 on the device (the host twin: tests/test_host.py): exact matches >= 2000 bases index Q_MEM[1999]
+    instead of running past the table; the run finishes, reports every read, and does not depend on the batching."""
+    from conftest import exact_copy_reads
+    fq = exact_copy_reads(tiny, tmp_path)
+    out = run_cli(tiny["idx"], fq)
+    recs = [ln.split(b"\t") for ln in out.split(b"\n") if ln.startswith(b"exact")]
+    assert {r[0] for r in recs} == {b"exact0", b"exact1", b"exact2"}
+    assert all(r[2] != b"*" for r in recs if int(r[1]) in (0, 16))
+    assert run_cli(tiny["idx"], fq, env={"DSB_BATCH_READS": "1"}) == out

@@ -517,3 +517,16 @@ def test_max_read_l_counts_only_reads_that_had_a_chain(mixed, have_ref_binary, t
     for env in ({}, {"DSB_BATCH_READS": "7"}, {"DSB_BATCH_READS": "1"}, {"DSB_BATCH_READS": "64", "DSB_HOSTSIM_GPUS": "2"}):
         assert run_sim(mixed["idx"], [fq], env=env) == want, env
         assert run_sim(mixed["idx"], [fq2], env=env) == other, env
+
+
+def test_exact_matches_of_2000_bases_do_not_leave_the_score_table(tiny, tmp_path):
+    """SURVEY.md Q12 on the host twin of the kernel source: error-free 3 kb copies of the reference give seeds with exact
+    matches >= 2000 bases; Q_MEM has 2000 entries and the reference reads past it (undefined).  Here the look-up is clamped:
+    the run finishes, every read is reported on its own genome, and the bytes do not depend on the batching."""
+    from conftest import exact_copy_reads
+    fq = exact_copy_reads(tiny, tmp_path)
+    out = run_sim(tiny["idx"], [fq])
+    recs = [ln.split(b"\t") for ln in out.split(b"\n") if ln.startswith(b"exact")]
+    assert {r[0] for r in recs} == {b"exact0", b"exact1", b"exact2"}
+    assert all(r[2] != b"*" for r in recs if int(r[1]) in (0, 16))
+    assert run_sim(tiny["idx"], [fq], env={"DSB_BATCH_READS": "1"}) == out
