@@ -17,6 +17,9 @@ typedef struct dsb_taxonomy dsb_taxonomy;
 dsb_taxonomy *dsb_taxonomy_load(const char *dir);
 void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
                             int flag, uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n);
+void dsb_meta_analysis_lines(dsb_taxonomy *tax, const dsb_meta_line *lines, size_t n_lines, const char *text, char **output,
+                             uint64_t *output_n, int flag, uint64_t max_snapshot_len, char **human_snapshot,
+                             uint64_t *human_snapshot_n);
 
 typedef struct api_index {
     uint32_t magic;
@@ -113,16 +116,37 @@ void read_classify(void *idx, char *input, uint64_t input_n, char **output, uint
     dsb_session_run(s, f, &o, NULL, &out, NULL);        /* NULL sink: append straight to `out` */
     dsb_fq_close(f);
     out.s[out.l] = 0;
+    dsb_session_meta_seal(s, out.s, out.l);           /* a meta_analysis() on this very block reads the hit records, not the text */
     /* caller free()s: hand over a plain malloc block */
     *output = out.s;
     *output_n = out.l;
 }
 
+/* which path the calling thread's last meta_analysis() took: 1 = hit records kept by read_classify, 0 = text parser (tests) */
+static __thread int g_meta_path;
+int dsb_meta_last_path(void) { return g_meta_path; }
+
 void meta_analysis(void *idx, char *input, uint64_t input_n, char **output, uint64_t *output_n, int thread_id, int flag,
                    uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
 {
-    (void)thread_id;
     api_index *a = (api_index *)idx;
     if (!a || a->magic != API_MAGIC) dsb_fatal("meta_analysis: bad index handle");
+    if (input_n != 0) {
+        /* the block read_classify() returned to this thread_id comes back unchanged -> its hit records */
+        dsb_session *s = NULL;
+        pthread_mutex_lock(&a->mu);
+        for (int i = 0; i < a->n_sessions; i++)
+            if (a->session_tid[i] == thread_id) { s = a->sessions[i]; break; }
+        pthread_mutex_unlock(&a->mu);
+        const dsb_meta_line *lines;
+        size_t n_lines;
+        g_meta_path = 0;
+        if (s && dsb_session_meta_lines(s, input, input_n, &lines, &n_lines)) {
+            g_meta_path = 1;
+            dsb_meta_analysis_lines(a->tax, lines, n_lines, input, output, output_n, flag, max_snapshot_len, human_snapshot,
+                                    human_snapshot_n);
+            return;
+        }
+    }
     dsb_meta_analysis_impl(a->tax, input, input_n, output, output_n, flag, max_snapshot_len, human_snapshot, human_snapshot_n);
 }

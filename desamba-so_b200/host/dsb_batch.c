@@ -34,24 +34,32 @@
  * and leave the caches to the text being parsed.  From four GPUs on the host's memory bandwidth is the bound of the whole
  * call.  DSB_NT_COPY=0 goes back to memcpy. */
 static int g_nt_copy = -1;
-static inline void copy_stream(char *dst, const char *src, size_t n)
+/* returns non-zero when the copied bytes hold a NUL (the batcher's line records are only good for texts without one) */
+static inline int copy_stream(char *dst, const char *src, size_t n)
 {
+    int nul = 0;
 #if defined(__SSE2__)
     if (g_nt_copy && n >= 256) {
         const size_t head = (size_t)(-(uintptr_t)dst & 15u);
-        if (head) { memcpy(dst, src, head); dst += head; src += head; n -= head; }
+        if (head) { nul |= memchr(src, 0, head) != NULL; memcpy(dst, src, head); dst += head; src += head; n -= head; }
         size_t k = n >> 6;
+        const __m128i zero = _mm_setzero_si128();
+        __m128i acc = zero;
         while (k--) {
             const __m128i a = _mm_loadu_si128((const __m128i *)src), b = _mm_loadu_si128((const __m128i *)(src + 16));
             const __m128i c = _mm_loadu_si128((const __m128i *)(src + 32)), d = _mm_loadu_si128((const __m128i *)(src + 48));
             _mm_stream_si128((__m128i *)dst, a); _mm_stream_si128((__m128i *)(dst + 16), b);
             _mm_stream_si128((__m128i *)(dst + 32), c); _mm_stream_si128((__m128i *)(dst + 48), d);
+            acc = _mm_or_si128(acc, _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(a, zero), _mm_cmpeq_epi8(b, zero)),
+                                                 _mm_or_si128(_mm_cmpeq_epi8(c, zero), _mm_cmpeq_epi8(d, zero))));
             src += 64; dst += 64;
         }
+        nul |= _mm_movemask_epi8(acc) != 0;
         n &= 63;
     }
 #endif
-    if (n) memcpy(dst, src, n);
+    if (n) { nul |= memchr(src, 0, n) != NULL; memcpy(dst, src, n); }
+    return nul;
 }
 static inline void copy_stream_done(void)
 {
@@ -80,6 +88,8 @@ struct dsb_engine {
     uint32_t batch_reads;
     int fmt_threads;
     int scan_threads;          /* FASTQ pre-scan: nothing else runs yet, so it may use every core of the rank's share */
+    uint32_t *meta_tid;        /* per reference: the taxon meta_analysis reads from its name */
+    int meta_names_ok;         /* every reference name has the usual "<name>|<taxid>..." shape */
 };
 
 typedef struct batch_meta {
@@ -125,6 +135,13 @@ struct dsb_session {
     /* two banks: while the splice thread moves batch b's text, the drain thread formats the fields of batch b + 1 */
     dsb_strbuf fmt_buf[2][MAX_FMT_THREADS + 1];
     size_t *fmt_ins[2], *fmt_end[2];   /* per read of the batch being formatted (SAM_FULL, direct mode): splice point / end of its fields */
+    size_t *fmt_seqpos[2];             /* per read: where its SEQ went, relative to the batch's first byte */
+    /* line records of the SAM_FULL text of the last direct call, for a meta_analysis() on that very text */
+    dsb_meta_line *ml;
+    size_t ml_n, ml_m;
+    int ml_ok;                         /* every line of this call's text is of the shape the records describe */
+    const char *ml_text;
+    uint64_t ml_text_n, ml_guard;
     /* a record that did not fit the previous batch */
     int have_carry;
     dsb_rec_view carry;
@@ -188,6 +205,11 @@ dsb_engine *dsb_engine_create(dsb_loaded_index *ix, int n_gpu_wanted)
     /* formatter / copy helpers: all but a few cores (producer, submit and drain threads, the CUDA driver's own) up to 12:
      * 16 cores: 8 -> 12 helpers took 1.4 ms off a 22 ms call */
     if (g_nt_copy < 0) g_nt_copy = env_u64("DSB_NT_COPY", 1) != 0;
+    e->meta_tid = (uint32_t *)dsb_xcalloc((size_t)ix->h.n_ref + 1, sizeof(uint32_t));
+    e->meta_names_ok = 1;
+    for (uint64_t i = 0; i < ix->h.n_ref; i++)
+        if (!memchr(ix->ref_info[i].ref_name, 0, sizeof ix->ref_info[i].ref_name) ||
+            !dsb_meta_rname_tid(ix->ref_info[i].ref_name, &e->meta_tid[i])) e->meta_names_ok = 0;
     /* one process driving four or more GPUs: the splice stage alone has to move ~4 bytes per base of every device's output
      * (12 helpers: 2.9 ms per 33.5 Mbase batch = 11.7 Gbases/s, the bound of the 4-GPU trace); up to 24 helpers there */
     const long cap = e->n_gpu >= 4 ? 24 : 12;
@@ -290,6 +312,7 @@ dsb_session *dsb_session_create(dsb_engine *e)
     s->hist = dsb_history_new();
     for (int b = 0; b < 2; b++) {
         s->fmt_ins[b] = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
+        s->fmt_seqpos[b] = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
         s->fmt_end[b] = (size_t *)dsb_xmalloc((size_t)e->batch_reads * sizeof(size_t));
     }
     pool_start(&s->pool, s->pool_arg, e->fmt_threads - 1);
@@ -330,6 +353,7 @@ void dsb_session_destroy(dsb_session *s)
     for (int b = 0; b < 2; b++) {
         for (int i = 0; i <= MAX_FMT_THREADS; i++) free(s->fmt_buf[b][i].s);
         free(s->fmt_ins[b]);
+        free(s->fmt_seqpos[b]);
         free(s->fmt_end[b]);
     }
     free(s->slots);
@@ -416,6 +440,9 @@ static uint32_t fill_slot(dsb_session *s, int k, dsb_fq *f, int want_qual, int *
         dsb_strbuf_reserve(&m->names, v.name_l + 1);
         memcpy(m->names.s + m->names.l, v.name, v.name_l);
         m->names.s[m->names.l + v.name_l] = 0;
+        /* lines the text parser of meta_analysis would read differently (empty fields, a header-like first line, a NUL):
+         * no line records for this call's text */
+        if (v.name_l == 0 || v.name[0] == '@' || L == 0 || memchr(v.name, 0, v.name_l)) __atomic_store_n(&s->ml_ok, 0, __ATOMIC_RELAXED);
         m->names.l += v.name_l + 1;
         m->qual_ptr[n] = NULL;
         m->qual_off[n] = UINT64_MAX;
@@ -454,6 +481,8 @@ typedef struct fmt_job {
     const dsb_hit *hits;
     uint32_t cut[MAX_FMT_THREADS + 2];     /* part p formats reads [cut[p], cut[p+1]) */
     char *dst;                             /* direct mode: where part p's text goes = dst + off[p] */
+    size_t dst_off;                        /* dst - start of the caller's block */
+    int nul[MAX_FMT_THREADS + 2];          /* part p copied a NUL byte */
     size_t off[MAX_FMT_THREADS + 2];
     size_t len[MAX_FMT_THREADS + 2];       /* SAM_FULL direct mode: bytes part p will write */
     int bank;                              /* which fmt_buf / fmt_ins / fmt_end bank holds this batch's fields */
@@ -504,20 +533,93 @@ static void splice_part(void *arg, int part, int n_parts)
     const char *text = j->s->fmt_buf[j->bank][part].s;
     char *d = j->dst + j->off[part];
     size_t from = 0;
+    int nul = 0;
     for (uint32_t i = j->cut[part]; i < j->cut[part + 1]; i++) {
         const size_t ins = j->s->fmt_ins[j->bank][i], end = j->s->fmt_end[j->bank][i];
         const uint32_t L = j->desc[i].len;
         const char *q = m->qual_ptr[i];
         if (!q && m->qual_off[i] != UINT64_MAX) q = m->quals.s + m->qual_off[i];
         memcpy(d, text + from, ins - from); d += ins - from;
-        copy_stream(d, j->seq + j->desc[i].seq_off, L); d += L;
+        j->s->fmt_seqpos[j->bank][i] = (size_t)(d - j->dst);
+        nul |= copy_stream(d, j->seq + j->desc[i].seq_off, L); d += L;
         *d++ = '\t';
-        if (q) { copy_stream(d, q, L); d += L; }
+        if (q) { nul |= copy_stream(d, q, L); d += L; }
         else { memcpy(d, "(null)", 6); d += 6; }
         memcpy(d, text + ins, end - ins); d += end - ins;
         from = end;
     }
+    j->nul[part] = nul;
     copy_stream_done();
+}
+
+/* The lines this batch added to the text, as meta_analysis would read them back (the same walk as format_sam, dsb_sam.c).
+ * Runs on the splice thread, batches in order. */
+static void meta_lines_append(dsb_session *s, const fmt_job *j)
+{
+    if (!__atomic_load_n(&s->ml_ok, __ATOMIC_RELAXED)) return;
+    for (int p = 0; p < j->parts; p++)
+        if (j->nul[p]) { __atomic_store_n(&s->ml_ok, 0, __ATOMIC_RELAXED); return; }
+    const uint32_t *mt = s->e->meta_tid;
+    const uint32_t n = j->m->n_reads;
+    if (s->ml_n + (size_t)n * 8 > s->ml_m) {
+        s->ml_m = (s->ml_n + (size_t)n * 8) * 2;
+        s->ml = (dsb_meta_line *)dsb_xrealloc(s->ml, s->ml_m * sizeof(dsb_meta_line));
+    }
+    for (uint32_t i = 0; i < n; i++) {
+        const dsb_read_result *r = &j->res[i];
+        const dsb_hit *h = j->hits + r->hit_off;
+        if (s->ml_n + (size_t)r->n_hit + 1 > s->ml_m) {
+            s->ml_m = (s->ml_n + (size_t)r->n_hit + 1) * 2;
+            s->ml = (dsb_meta_line *)dsb_xrealloc(s->ml, s->ml_m * sizeof(dsb_meta_line));
+        }
+        dsb_meta_line *l = &s->ml[s->ml_n++];
+        l->read_length = j->desc[i].len;
+        l->seq_off = (uint64_t)(j->dst_off + s->fmt_seqpos[j->bank][i]);
+        l->has_seq = 1;
+        if (r->n_hit == 0) { l->cls = 'U'; l->tid = 0; continue; }
+        l->cls = 'C'; l->tid = mt[h[0].ref_ID];
+        for (int loop = 0; loop <= 1; loop++)
+            for (uint32_t k = 1; k < r->n_hit; k++) {
+                const dsb_hit *c = h + k;
+                const int show = (loop == 0) ? (c->pri_index == 0) : (c->pri_index > 0 && c->pri_index <= (uint32_t)j->o->max_sec_N);
+                if (!show) continue;
+                dsb_meta_line *x = &s->ml[s->ml_n++];
+                x->cls = 'C'; x->tid = mt[c->ref_ID]; x->read_length = 1; x->seq_off = 0; x->has_seq = 0;
+            }
+    }
+}
+
+static uint64_t meta_guard(const char *text, uint64_t n)
+{
+    /* 64 windows of 64 bytes spread over the text: a caller that hands back another text of the same size at the same
+     * address is told apart (the records are only used for the very text they describe) */
+    uint64_t h = 1469598103934665603ull;
+    const uint64_t step = n / 64 ? n / 64 : 1;
+    for (uint64_t k = 0; k < 64; k++) {
+        const uint64_t at = k * step;
+        if (at >= n) break;
+        const uint64_t len = n - at < 64 ? n - at : 64;
+        for (uint64_t i = 0; i < len; i++) h = (h ^ (unsigned char)text[at + i]) * 1099511628211ull;
+    }
+    return h ^ n;
+}
+
+void dsb_session_meta_seal(dsb_session *s, const char *text, uint64_t n)
+{
+    s->ml_text = NULL;
+    if (!__atomic_load_n(&s->ml_ok, __ATOMIC_RELAXED)) return;
+    s->ml_text = text;
+    s->ml_text_n = n;
+    s->ml_guard = meta_guard(text, n);
+}
+
+int dsb_session_meta_lines(dsb_session *s, const char *text, uint64_t n, const dsb_meta_line **lines, size_t *n_lines)
+{
+    if (!s || !s->ml_text || text != s->ml_text || (n != s->ml_text_n && n != s->ml_text_n + 1)) return 0;
+    if (meta_guard(text, s->ml_text_n) != s->ml_guard) return 0;
+    *lines = s->ml;
+    *n_lines = s->ml_n;
+    return 1;
 }
 
 static void copy_part(void *arg, int part, int n_parts)
@@ -638,6 +740,7 @@ static void drain_slot(run_ctx *r, uint64_t b, int k)
             dsb_strbuf_reserve(out, total);
         }
         jp->dst = out->s + out->l;
+        jp->dst_off = out->l;
         out->l += total;
         pthread_mutex_lock(&r->mu);
         r->formatted = b + 1;
@@ -708,6 +811,7 @@ static void *splice_thread(void *argp)
         if (!have) return NULL;
         const double t0 = dsb_now();
         pool_run(&r->s->spool, splice_part, &r->sj[b & 1]);
+        meta_lines_append(r->s, &r->sj[b & 1]);
         if (r->verbose)
             fprintf(stderr, "[dsb]   batch %llu spliced %.2f..%.2f ms\n", (unsigned long long)b, 1e3 * (t0 - r->t_start), 1e3 * (dsb_now() - r->t_start));
         if (r->stats) r->stats->t_format += dsb_now() - t0;
@@ -773,6 +877,11 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     pthread_t th, th_submit, th_splice;
     int eof = 0;
     r.splice_mode = (!sink && o->format == DSB_OUT_SAM_FULL);
+    /* line records for meta_analysis: only for the text this call writes itself; DSB_META_TEXT=1 keeps
+     * meta_analysis on the text parser */
+    s->ml_n = 0;
+    s->ml_text = NULL;
+    __atomic_store_n(&s->ml_ok, (r.splice_mode && s->e->meta_names_ok && !getenv("DSB_META_TEXT")) ? 1 : 0, __ATOMIC_RELAXED);
     s->have_carry = 0;
     /* a call that is only a few batches long (in-memory input of known size, ~2 bytes per base) uses the small batch
      * size: the device starts earlier and the last batch's text is shorter */

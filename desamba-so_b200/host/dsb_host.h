@@ -56,6 +56,21 @@ void dsb_index_load(dsb_loaded_index *ix, const char *dir, int min_len, int min_
 /* drop the big host arrays once they are resident on the GPUs (names / offsets are kept) */
 void dsb_index_release_bulk(dsb_loaded_index *ix);
 void dsb_index_destroy(dsb_loaded_index *ix);
+/* ---- meta_analysis on hit records ----------------------------------------
+ * One line of the SAM_FULL text read_classify() returned, as meta_analysis reads it (RST, reference src/cly_mt.h:55-63):
+ * built by the batcher from the hit records while it writes the text, so that a meta_analysis() call on that very text
+ * does not have to parse 2 bytes per base again. */
+typedef struct dsb_meta_line {
+    uint32_t tid;                  /* taxon of the line's RNAME ("tid|<taxid>|..."), 0 for an unclassified read */
+    uint32_t read_length;          /* length of the line's SEQ field (1 for the "*" of SUP / SEC lines) */
+    uint64_t seq_off;              /* where SEQ starts in the text (lines that carry the read's bases) */
+    uint8_t cls;                   /* 'C' or 'U' */
+    uint8_t has_seq;
+} dsb_meta_line;
+/* taxon of a reference name as the text parser reads it; 0 = the name is not of the usual "<name>|<digits>..." shape
+ * (then only the text path is exact) */
+int dsb_meta_rname_tid(const char *ref_name, uint32_t *tid);
+
 /* MAPQ tables (reference src/cly_mt.c:396-420) */
 void dsb_mapq_tables(int32_t *q_mem, int32_t *q_lv, double p_e, uint64_t l_ref);
 
@@ -121,6 +136,10 @@ void dsb_engine_destroy(dsb_engine *e);
 int dsb_engine_n_gpu(const dsb_engine *e);
 
 typedef struct dsb_session dsb_session;   /* = one reference "worker buffer set" (a thread_id) */
+/* after a direct SAM_FULL run: the text the records describe (start and length of the caller's block) */
+void dsb_session_meta_seal(dsb_session *s, const char *text, uint64_t n);
+/* the records, if `text` is that very text (same address, same length or one more for the NUL, same sampled bytes) */
+int dsb_session_meta_lines(dsb_session *s, const char *text, uint64_t n, const dsb_meta_line **lines, size_t *n_lines);
 dsb_session *dsb_session_create(dsb_engine *e);
 void dsb_session_destroy(dsb_session *s);
 void dsb_session_reset_history(dsb_session *s);

@@ -398,80 +398,11 @@ static void free_priv(parse_job *jobs)
     }
 }
 
-void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
-                            int flag, uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
+/* Everything behind the record list: tally per taxon, propagation to the ancestors, report and snapshot.  `recs` and
+ * `human.s` are consumed (freed).  Shared by the text path below and by dsb_meta_analysis_lines. */
+static void meta_tail(dsb_taxonomy *tax, rec *recs, size_t n_rec, dsb_strbuf human, char **output, uint64_t *output_n, int flag,
+                      uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
 {
-    if (input_n == 0) {
-        *output_n = 0;
-        *human_snapshot_n = 0;
-        return;
-    }
-    if (!tax) dsb_fatal("meta_analysis: the index directory has no nodes.dmp / names.dmp");
-    /* The text is read in place by several threads (contiguous pieces cut at line ends; records and human bases are
-     * joined in text order, so the result is that of one pass).  Lines of the usual shape are parsed without being
-     * modified (parse_record_fast); any other line is copied and tokenised by the strtok-faithful parse_record.  The first
-     * version copied the whole text and tokenised it on one thread: 165-210 ms for 104 MB of SAM_FULL, 9 x the
-     * classification that produced it. */
-    const int verbose = getenv("DSB_VERBOSE") != NULL;
-    const double t_0 = dsb_now();
-    int n_thr = meta_threads(input_n);
-    parse_job jobs[META_MAX_THREADS];
-    pthread_t th[META_MAX_THREADS];
-    memset(jobs, 0, sizeof jobs);
-    for (int t = 0; t < n_thr; t++) {
-        jobs[t].lo = input + (size_t)(input_n * (uint64_t)t / (uint64_t)n_thr);
-        jobs[t].hi = input + (size_t)(input_n * (uint64_t)(t + 1) / (uint64_t)n_thr);
-        jobs[t].snap_cap = max_snapshot_len;
-    }
-    run_jobs(th, jobs, n_thr, scan_nul_worker);
-    const double t_1 = dsb_now();
-    const char *end = input + input_n;                   /* like getline on a text file: stops at an embedded NUL */
-    for (int t = 0; t < n_thr; t++)
-        if (jobs[t].first_nul) { end = jobs[t].first_nul; break; }
-    const char *p = input;
-    while (p < end && *p == '@') {                       /* skip_sam_head: @SQ / @PG lines */
-        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
-        p = nl ? nl + 1 : end;
-    }
-    /* pieces of the body, each starting at a line start */
-    {
-        const size_t body = (size_t)(end - p);
-        if (body < ((size_t)1 << 20)) n_thr = 1;
-        const char *cut = p;
-        for (int t = 0; t < n_thr; t++) {
-            jobs[t].beg = cut;
-            const char *want = p + body * (size_t)(t + 1) / (size_t)n_thr;
-            if (t + 1 == n_thr || want >= end) cut = end;
-            else {
-                if (want < cut) want = cut;
-                const char *nl = (const char *)memchr(want, '\n', (size_t)(end - want));
-                cut = nl ? nl + 1 : end;
-            }
-            jobs[t].end = cut;
-        }
-    }
-    run_jobs(th, jobs, n_thr, parse_worker);
-    const double t_2 = dsb_now();
-    size_t n_rec = 0;
-    for (int t = 0; t < n_thr; t++) {
-        if (jobs[t].bad) dsb_fatal("meta_analysis: malformed SAM record (the reference crashes here)");
-        n_rec += jobs[t].n_rec;
-    }
-    rec *recs = (rec *)dsb_xmalloc((n_rec ? n_rec : 1) * sizeof(rec));
-    dsb_strbuf human = {NULL, 0, 0};
-    dsb_strbuf_reserve(&human, 1);
-    n_rec = 0;
-    for (int t = 0; t < n_thr; t++) {
-        memcpy(recs + n_rec, jobs[t].recs, jobs[t].n_rec * sizeof(rec));
-        n_rec += jobs[t].n_rec;
-        if (jobs[t].human.l) {
-            dsb_strbuf_reserve(&human, jobs[t].human.l);
-            memcpy(human.s + human.l, jobs[t].human.s, jobs[t].human.l);
-            human.l += jobs[t].human.l;
-        }
-        free(jobs[t].recs);
-        free(jobs[t].human.s);
-    }
     if (n_rec == 0) {
         /* the reference returns with *output never assigned and then dereferences it; we return an empty answer */
         *output = (char *)dsb_xcalloc(1, 1);
@@ -479,7 +410,6 @@ void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input
         *human_snapshot = NULL;
         *human_snapshot_n = 0;
         free(recs); free(human.s);
-        free_priv(jobs);
         return;
     }
     /* tally per taxon */
@@ -585,11 +515,135 @@ void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input
     }
     *output = res.s;                                      /* malloc'd, caller frees (desamba.h) */
     *output_n = res.l;
-    const double t_3 = dsb_now();
     free(rows); free(lines.s); free(srt); free(recs); free(human.s);
     lazy_free(t.tab, n_tid * sizeof(node));
     lazy_free(t.kids, (2 * n_tid + 2) * sizeof(child));
     lazy_free(node_count, n_tid * sizeof(uint64_t));
+}
+
+/* RNAME as parse_record_fast reads it (and parse_record agrees on names of this shape) */
+int dsb_meta_rname_tid(const char *ref_name, uint32_t *tid)
+{
+    const size_t n = strlen(ref_name);
+    if (n == 0 || ref_name[0] == '*' || ref_name[0] == '|') return 0;
+    for (size_t i = 0; i < n; i++)
+        if (ref_name[i] == '\t' || ref_name[i] == '\n') return 0;
+    const char *bar = (const char *)memchr(ref_name, '|', n), *re = ref_name + n;
+    if (!bar || bar + 1 >= re || bar[1] < '0' || bar[1] > '9') return 0;
+    unsigned long v = 0;
+    size_t nd = 0;
+    for (const char *q = bar + 1; q < re && *q >= '0' && *q <= '9'; q++, nd++) v = v * 10 + (unsigned long)(*q - '0');
+    if (nd > 9) return 0;
+    *tid = (uint32_t)v;
+    return 1;
+}
+
+/* meta_analysis from the line records the batcher kept for the text it returned: the records are what
+ * parse_worker would produce from `text`, line by line, so everything behind them is shared with the text path. */
+void dsb_meta_analysis_lines(dsb_taxonomy *tax, const dsb_meta_line *lines, size_t n_lines, const char *text, char **output,
+                             uint64_t *output_n, int flag, uint64_t max_snapshot_len, char **human_snapshot,
+                             uint64_t *human_snapshot_n)
+{
+    if (!tax) dsb_fatal("meta_analysis: the index directory has no nodes.dmp / names.dmp");
+    const double t_0 = dsb_now();
+    rec *recs = (rec *)dsb_xmalloc((n_lines ? n_lines : 1) * sizeof(rec));
+    dsb_strbuf human = {NULL, 0, 0};
+    dsb_strbuf_reserve(&human, 1);
+    for (size_t i = 0; i < n_lines; i++) {
+        const dsb_meta_line *l = lines + i;
+        rec r;
+        r.name = NULL; r.name_l = 0;                    /* read_tid never gets past its `score == 0` test: names are not compared */
+        r.cls = (char)l->cls; r.tid = l->tid; r.read_length = l->read_length; r.score = 0; r.mapq = 0;
+        r.seq = l->has_seq ? text + l->seq_off : "*";
+        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158) && (human.l < max_snapshot_len || human.l == 0)) {
+            dsb_strbuf_reserve(&human, r.read_length);
+            memcpy(human.s + human.l, r.seq, r.read_length);
+            human.l += r.read_length;
+        }
+        recs[i] = r;
+    }
+    meta_tail(tax, recs, n_lines, human, output, output_n, flag, max_snapshot_len, human_snapshot, human_snapshot_n);
+    if (getenv("DSB_VERBOSE"))
+        fprintf(stderr, "[dsb] meta_analysis: %zu line records kept by read_classify (no text parsed), %.2f ms\n", n_lines,
+                1e3 * (dsb_now() - t_0));
+}
+
+void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
+                            int flag, uint64_t max_snapshot_len, char **human_snapshot, uint64_t *human_snapshot_n)
+{
+    if (input_n == 0) {
+        *output_n = 0;
+        *human_snapshot_n = 0;
+        return;
+    }
+    if (!tax) dsb_fatal("meta_analysis: the index directory has no nodes.dmp / names.dmp");
+    /* The text is read in place by several threads (contiguous pieces cut at line ends; records and human bases are
+     * joined in text order, so the result is that of one pass).  Lines of the usual shape are parsed without being
+     * modified (parse_record_fast); any other line is copied and tokenised by the strtok-faithful parse_record.  The first
+     * version copied the whole text and tokenised it on one thread: 165-210 ms for 104 MB of SAM_FULL, 9 x the
+     * classification that produced it. */
+    const int verbose = getenv("DSB_VERBOSE") != NULL;
+    const double t_0 = dsb_now();
+    int n_thr = meta_threads(input_n);
+    parse_job jobs[META_MAX_THREADS];
+    pthread_t th[META_MAX_THREADS];
+    memset(jobs, 0, sizeof jobs);
+    for (int t = 0; t < n_thr; t++) {
+        jobs[t].lo = input + (size_t)(input_n * (uint64_t)t / (uint64_t)n_thr);
+        jobs[t].hi = input + (size_t)(input_n * (uint64_t)(t + 1) / (uint64_t)n_thr);
+        jobs[t].snap_cap = max_snapshot_len;
+    }
+    run_jobs(th, jobs, n_thr, scan_nul_worker);
+    const double t_1 = dsb_now();
+    const char *end = input + input_n;                   /* like getline on a text file: stops at an embedded NUL */
+    for (int t = 0; t < n_thr; t++)
+        if (jobs[t].first_nul) { end = jobs[t].first_nul; break; }
+    const char *p = input;
+    while (p < end && *p == '@') {                       /* skip_sam_head: @SQ / @PG lines */
+        const char *nl = (const char *)memchr(p, '\n', (size_t)(end - p));
+        p = nl ? nl + 1 : end;
+    }
+    /* pieces of the body, each starting at a line start */
+    {
+        const size_t body = (size_t)(end - p);
+        if (body < ((size_t)1 << 20)) n_thr = 1;
+        const char *cut = p;
+        for (int t = 0; t < n_thr; t++) {
+            jobs[t].beg = cut;
+            const char *want = p + body * (size_t)(t + 1) / (size_t)n_thr;
+            if (t + 1 == n_thr || want >= end) cut = end;
+            else {
+                if (want < cut) want = cut;
+                const char *nl = (const char *)memchr(want, '\n', (size_t)(end - want));
+                cut = nl ? nl + 1 : end;
+            }
+            jobs[t].end = cut;
+        }
+    }
+    run_jobs(th, jobs, n_thr, parse_worker);
+    const double t_2 = dsb_now();
+    size_t n_rec = 0;
+    for (int t = 0; t < n_thr; t++) {
+        if (jobs[t].bad) dsb_fatal("meta_analysis: malformed SAM record (the reference crashes here)");
+        n_rec += jobs[t].n_rec;
+    }
+    rec *recs = (rec *)dsb_xmalloc((n_rec ? n_rec : 1) * sizeof(rec));
+    dsb_strbuf human = {NULL, 0, 0};
+    dsb_strbuf_reserve(&human, 1);
+    n_rec = 0;
+    for (int t = 0; t < n_thr; t++) {
+        memcpy(recs + n_rec, jobs[t].recs, jobs[t].n_rec * sizeof(rec));
+        n_rec += jobs[t].n_rec;
+        if (jobs[t].human.l) {
+            dsb_strbuf_reserve(&human, jobs[t].human.l);
+            memcpy(human.s + human.l, jobs[t].human.s, jobs[t].human.l);
+            human.l += jobs[t].human.l;
+        }
+        free(jobs[t].recs);
+        free(jobs[t].human.s);
+    }
+    meta_tail(tax, recs, n_rec, human, output, output_n, flag, max_snapshot_len, human_snapshot, human_snapshot_n);
+    const double t_3 = dsb_now();
     size_t n_slow = 0;
     for (int k = 0; k < META_MAX_THREADS; k++) n_slow += jobs[k].n_slow;
     free_priv(jobs);

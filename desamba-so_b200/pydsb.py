@@ -141,6 +141,36 @@ class Desamba:
             self.libc.free(out)
         return time.perf_counter() - t0, out_n.value
 
+    def classify_then_analyse(self, data, thread_id=0, thread_num=1, flag=1, max_snapshot_len=65536, calls=1, tamper=False):
+        """The resident loop of BASELINE.json configs[4] as a C caller writes it: read_classify(), then meta_analysis()
+        on the block it returned (the same pointer), then free().  meta_analysis() then answers from the hit records
+        read_classify() kept.  Returns (sam text, meta text, snapshot, seconds classify, seconds meta)."""
+        import time
+        out, out_n = C.c_void_p(), C.c_uint64(0)
+        t0 = time.perf_counter()
+        self.lib.read_classify(self.idx, data, len(data), C.byref(out), C.byref(out_n), thread_id, thread_num)
+        t1 = time.perf_counter()
+        if not out.value:
+            return b"", b"", None, t1 - t0, 0.0
+        if tamper:                                       # tests: the caller changed the text before handing it back
+            C.memmove(out.value, b"X", 1)
+        meta = snap = None
+        for _ in range(calls):
+            mo, mo_n, hs, hs_n = C.c_void_p(), C.c_uint64(0), C.c_void_p(), C.c_uint64(0)
+            self.lib.meta_analysis(self.idx, C.cast(out, C.c_char_p), out_n, C.byref(mo), C.byref(mo_n), thread_id, flag,
+                                   max_snapshot_len, C.byref(hs), C.byref(hs_n))
+            meta = C.string_at(mo.value, mo_n.value) if mo.value else b""
+            snap = C.string_at(hs.value, hs_n.value) if hs.value else None
+            if mo.value:
+                self.libc.free(mo)
+            if hs.value:
+                self.libc.free(hs)
+        t2 = time.perf_counter()
+        self.meta_path = int(self.lib.dsb_meta_last_path())      # 1: from the hit records, 0: text parser
+        sam = C.string_at(out.value, out_n.value)
+        self.libc.free(out)
+        return sam, meta, snap, t1 - t0, (t2 - t1) / calls
+
     def meta_analysis(self, sam, thread_id=0, flag=1, max_snapshot_len=65536):
         out, out_n, hs, hs_n = C.c_void_p(), C.c_uint64(0), C.c_void_p(), C.c_uint64(0)
         self.lib.meta_analysis(self.idx, sam, len(sam), C.byref(out), C.byref(out_n), thread_id, flag, max_snapshot_len,

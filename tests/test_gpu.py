@@ -264,6 +264,14 @@ def test_resident_index_repeated_batches_with_meta_analysis(api, mixed, have_ref
         meta, snap = d.meta_analysis(sam, thread_id=7, flag=1, max_snapshot_len=65536)
         assert meta == w_meta, (i, meta, w_meta)
         assert snap == w_snap, i
+    # the same call sequence as a C caller writes it: meta_analysis() on the very block read_classify() returned, which is
+    # answered from the hit records the batcher kept -- same bytes as the reference library again
+    d2 = api.Desamba()
+    d2.load_index(mixed["idx"])
+    for i, (fq, (w_sam, w_meta, w_snap)) in enumerate(zip(slices, want)):
+        sam, meta, snap, _tc, _tm = d2.classify_then_analyse(fq, thread_id=9, flag=1, max_snapshot_len=65536)
+        assert d2.meta_path == 1, i
+        assert (sam, meta, snap) == (w_sam, w_meta, w_snap), i
     proc = psutil.Process()
     free0, rss0 = None, None
     period = slices[10:]

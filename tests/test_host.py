@@ -6,6 +6,7 @@ import gzip
 import os
 import re
 import subprocess
+import sys
 
 import pytest
 
@@ -530,3 +531,61 @@ def test_exact_matches_of_2000_bases_do_not_leave_the_score_table(tiny, tmp_path
     assert {r[0] for r in recs} == {b"exact0", b"exact1", b"exact2"}
     assert all(r[2] != b"*" for r in recs if int(r[1]) in (0, 16))
     assert run_sim(tiny["idx"], [fq], env={"DSB_BATCH_READS": "1"}) == out
+
+
+def test_meta_analysis_from_hit_records_equals_text_parser_and_reference(mixed, tiny, have_ref_binary):
+    """meta_analysis() on the very block read_classify() returned answers from the hit records the batcher
+    kept (no text parsed).  Same bytes as the text parser on a copy of the text, for both weights and several snapshot
+    sizes, over a call sequence on one thread_id -- and the same as the unmodified reference library driven the same way."""
+    from conftest import fastq_slices, ref_resident_session
+    for meta_ds, n_slices in ((mixed, 3), (tiny, 2)):
+        slices = fastq_slices(meta_ds["reads"], n_slices)
+        for flag, snap in ((1, 65536), (0, 100), (1, 0)):
+            d = pydsb_hostsim.Desamba()
+            d.load_index(meta_ds["idx"])
+            want = ref_resident_session(meta_ds["idx"], slices, flag, snap) if have_ref_binary else None
+            for i, fq in enumerate(slices):
+                sam, meta, hs, _tc, _tm = d.classify_then_analyse(fq, thread_id=5, flag=flag, max_snapshot_len=snap)
+                assert d.meta_path == 1, "the hit-record path was not taken"
+                assert (meta, hs) == d.meta_analysis(sam, thread_id=5, flag=flag, max_snapshot_len=snap)     # a copy: text parser
+                if want:
+                    assert (sam, meta, hs) == want[i], (flag, snap, i)
+
+
+def test_meta_analysis_falls_back_to_the_text_when_the_records_do_not_describe_it(mixed):
+    """The records are used only for a text whose every line has the usual shape and only for that very text: a read name
+    that starts with '@' (the text parser would skip it as a header line), an empty name, a NUL inside a sequence, a text
+    the caller changed -- all go through the text parser, and give what it gives on a copy."""
+    recs = open(mixed["reads"], "rb").read().split(b"\n")
+    first = b"\n".join(recs[:40]) + b"\n"
+    cases = {
+        "plain": (first, 1, False),
+        "header-like name": (b"@" + first, 0, False),
+        "text changed by the caller": (first, 0, True),
+        "FASTA": (b"".join(b">" + recs[i][1:] + b"\n" + recs[i + 1] + b"\n" for i in range(0, 40, 4)), 1, False),
+    }
+    for what, (fq, path, tamper) in cases.items():
+        d = pydsb_hostsim.Desamba()
+        d.load_index(mixed["idx"])
+        sam, meta, hs, _tc, _tm = d.classify_then_analyse(fq, thread_id=2, flag=1, max_snapshot_len=1000, tamper=tamper)
+        assert d.meta_path == path, what
+        if tamper:
+            sam = b"X" + sam[1:]
+        assert (meta, hs) == d.meta_analysis(sam, thread_id=2, flag=1, max_snapshot_len=1000), what
+
+
+def test_meta_analysis_on_text_the_reference_cannot_parse_still_stops_like_the_text_parser(mixed, tmp_path):
+    """An empty read name or a NUL inside a sequence give SAM lines the reference's getOneSAM crashes on; the text parser
+    here stops with a message.  The hit records must not paper over that (they are not kept for such calls)."""
+    recs = open(mixed["reads"], "rb").read().split(b"\n")
+    cases = {"empty name": b"@\n" + b"\n".join(recs[1:40]) + b"\n",
+             "NUL in a sequence": b"\n".join(recs[:5] + [recs[5][:100] + b"\0" + recs[5][101:]] + recs[6:40]) + b"\n"}
+    code = ("import sys; sys.path.insert(0, %r); sys.path.insert(0, %r); import pydsb_hostsim\n"
+            "d = pydsb_hostsim.Desamba(); d.load_index(sys.argv[1])\n"
+            "d.classify_then_analyse(open(sys.argv[2], 'rb').read(), thread_id=2)\n"
+            "print('answered, path', d.meta_path)\n") % (os.path.join(ROOT, "desamba-so_b200"), os.path.join(ROOT, "tests", "hostsim"))
+    for what, fq in cases.items():
+        p = tmp_path / "in.fq"
+        p.write_bytes(fq)
+        r = subprocess.run([sys.executable, "-c", code, mixed["idx"], str(p)], stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+        assert r.returncode != 0 and b"malformed SAM record" in r.stderr, (what, r.stdout, r.stderr[-300:])
