@@ -412,6 +412,8 @@ static void meta_tail(dsb_taxonomy *tax, rec *recs, size_t n_rec, dsb_strbuf hum
         free(recs); free(human.s);
         return;
     }
+    const int tv_ = getenv("DSB_VERBOSE") != NULL;
+    const double tt0_ = dsb_now();
     /* tally per taxon */
     const size_t n_tid = (size_t)tax->max_tid + 1;
     /* the tables span the taxonomy's whole id range (millions); calloc hands them out as untouched zero pages, so only
@@ -430,6 +432,7 @@ static void meta_tail(dsb_taxonomy *tax, rec *recs, size_t n_rec, dsb_strbuf hum
         }
         node_count[tid] += w;
     }
+    const double tt1_ = dsb_now();
     qsort(seen, n_seen, sizeof(uint32_t), cmp_u32);       /* ascending id: the order the range scan produced (ties of the count sort) */
     size_t n_sort = 0;
     count_sort *srt = (count_sort *)dsb_xmalloc((n_seen + 1) * sizeof(count_sort));
@@ -465,12 +468,14 @@ static void meta_tail(dsb_taxonomy *tax, rec *recs, size_t n_rec, dsb_strbuf hum
             c = par;
         }
     }
+    const double tt2_ = dsb_now();
     dsb_strbuf lines = {NULL, 0, 0};
     dsb_strbuf_reserve(&lines, 1);
     lines.s[0] = 0;
     t.out = &lines;
     print_leaves(&t, 0);
     print_leaves(&t, 1);
+    const double tt3_ = dsb_now();
     /* ---- meta_analysis proper: snapshot + top-3 table ---------------------------------------- */
     if (human.l == 0) {
         *human_snapshot = NULL;
@@ -515,10 +520,14 @@ static void meta_tail(dsb_taxonomy *tax, rec *recs, size_t n_rec, dsb_strbuf hum
     }
     *output = res.s;                                      /* malloc'd, caller frees (desamba.h) */
     *output_n = res.l;
+    const double tt4_ = dsb_now();
     free(rows); free(lines.s); free(srt); free(recs); free(human.s);
     lazy_free(t.tab, n_tid * sizeof(node));
     lazy_free(t.kids, (2 * n_tid + 2) * sizeof(child));
     lazy_free(node_count, n_tid * sizeof(uint64_t));
+    if (tv_)
+        fprintf(stderr, "[dsb]   meta tail: tally %.2f ms, sort + propagate %.2f ms, leaves %.2f ms, report %.2f ms, free %.2f ms\n",
+                1e3 * (tt1_ - tt0_), 1e3 * (tt2_ - tt1_), 1e3 * (tt3_ - tt2_), 1e3 * (tt4_ - tt3_), 1e3 * (dsb_now() - tt4_));
 }
 
 /* RNAME as parse_record_fast reads it (and parse_record agrees on names of this shape) */
@@ -552,20 +561,22 @@ void dsb_meta_analysis_lines(dsb_taxonomy *tax, const dsb_meta_line *lines, size
     for (size_t i = 0; i < n_lines; i++) {
         const dsb_meta_line *l = lines + i;
         rec r;
-        r.name = NULL; r.name_l = 0;                    /* read_tid never gets past its `score == 0` test: names are not compared */
+        r.name = ""; r.name_l = 0;                      /* read_tid never gets past its `score == 0` test: names are not compared */
         r.cls = (char)l->cls; r.tid = l->tid; r.read_length = l->read_length; r.score = 0; r.mapq = 0;
         r.seq = l->has_seq ? text + l->seq_off : "*";
-        if (r.seq[0] != '*' && (r.tid == 9606 || r.tid == 63221 || r.tid == 741158) && (human.l < max_snapshot_len || human.l == 0)) {
+        /* the taxon first: the text (2 bytes per base, written with streaming stores) is only touched for human reads */
+        if ((r.tid == 9606 || r.tid == 63221 || r.tid == 741158) && r.seq[0] != '*' && (human.l < max_snapshot_len || human.l == 0)) {
             dsb_strbuf_reserve(&human, r.read_length);
             memcpy(human.s + human.l, r.seq, r.read_length);
             human.l += r.read_length;
         }
         recs[i] = r;
     }
+    const double t_1 = dsb_now();
     meta_tail(tax, recs, n_lines, human, output, output_n, flag, max_snapshot_len, human_snapshot, human_snapshot_n);
     if (getenv("DSB_VERBOSE"))
-        fprintf(stderr, "[dsb] meta_analysis: %zu line records kept by read_classify (no text parsed), %.2f ms\n", n_lines,
-                1e3 * (dsb_now() - t_0));
+        fprintf(stderr, "[dsb] meta_analysis: %zu line records kept by read_classify (no text parsed): records %.2f ms, tally + report %.2f ms\n",
+                n_lines, 1e3 * (t_1 - t_0), 1e3 * (dsb_now() - t_1));
 }
 
 void dsb_meta_analysis_impl(dsb_taxonomy *tax, const char *input, uint64_t input_n, char **output, uint64_t *output_n,
