@@ -225,6 +225,7 @@ void dsb_engine_destroy(dsb_engine *e)
     if (!e) return;
     for (int g = 0; g < e->n_gpu; g++) dsb_index_free(e->dev[g]);
     free(e->dev);
+    free(e->meta_tid);
     free(e);
 }
 
@@ -342,6 +343,7 @@ void dsb_session_destroy(dsb_session *s)
     pool_stop(&s->cpool);
     for (int k = 0; k < s->n_slots; k++) free(s->copy_src[k]);
     free(s->copy_src);
+    free(s->ml);
     for (int k = 0; k < s->n_slots; k++) {
         dsb_slot_free(s->slots[k]);
         free(s->meta[k].names.s);
