@@ -647,6 +647,7 @@ typedef struct run_ctx {
     int fill_done, done;
     /* splice stage (direct SAM_FULL mode only) */
     int splice_mode;
+    double t_splice;               /* seconds the splice thread worked (under mu) */
     fmt_job sj[2];                  /* bank b & 1 holds batch b between its field pass and its splice */
     uint64_t formatted, spliced;
     int format_done;
@@ -816,8 +817,9 @@ static void *splice_thread(void *argp)
         meta_lines_append(r->s, &r->sj[b & 1]);
         if (r->verbose)
             fprintf(stderr, "[dsb]   batch %llu spliced %.2f..%.2f ms\n", (unsigned long long)b, 1e3 * (t0 - r->t_start), 1e3 * (dsb_now() - r->t_start));
-        if (r->stats) r->stats->t_format += dsb_now() - t0;
+        const double dt = dsb_now() - t0;
         pthread_mutex_lock(&r->mu);
+        r->t_splice += dt;                           /* added to stats->t_format when the run ends (the drain thread owns that field) */
         r->spliced = b + 1;
         r->drained = b + 1;
         pthread_cond_broadcast(&r->cv);
@@ -975,6 +977,7 @@ void dsb_session_run(dsb_session *s, dsb_fq *f, const dsb_out_opt *o, dsb_sink_f
     pthread_join(th_submit, NULL);
     pthread_join(th, NULL);
     if (r.splice_mode) pthread_join(th_splice, NULL);
+    if (r.stats) r.stats->t_format += r.t_splice;
     prefault_join(&r);
     dsb_history_end_batch(s->hist);
     dsb_history_all_drained(s->hist);

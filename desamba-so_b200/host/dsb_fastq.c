@@ -443,10 +443,13 @@ static void fq_prescan_piece(dsb_fq *f)
         n++;
     }
     for (int t = 0; t < n; t++) jobs[t].limit = (t + 1 < n) ? jobs[t + 1].start : hi;
-    for (int t = 1; t < n; t++)
-        if (pthread_create(&th[t], NULL, scan_worker, &jobs[t]) != 0) { jobs[t].ok = -1; }
+    int started[32] = {0};
+    for (int t = 1; t < n; t++) started[t] = pthread_create(&th[t], NULL, scan_worker, &jobs[t]) == 0;
     scan_worker(&jobs[0]);
-    for (int t = 1; t < n; t++) if (jobs[t].ok != -1) pthread_join(th[t], NULL);
+    for (int t = 1; t < n; t++) {
+        if (started[t]) pthread_join(th[t], NULL);
+        else jobs[t].ok = -1;                       /* no thread: its piece (and what follows) goes to the sequential parser */
+    }
     f->scan_pieces++;
     /* accept the verified prefix */
     size_t total = 0;
