@@ -163,6 +163,11 @@ def test_msort_model_matches_libc_qsort(orc):
     libc = C.CDLL(None)
     CMP = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p)
     CMPI = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_uint32, C.c_uint32)
+    # without argtypes ctypes passes a Python int as a C int: a buffer above 4 GB (a grown heap) arrives truncated
+    libc.qsort.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, CMP]
+    libc.qsort.restype = None
+    orc.orc_msort_idx.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, CMPI, C.c_void_p]
+    orc.orc_msort_idx.restype = None
     rng = np.random.default_rng(5)
     for trial in range(300):
         n = int(rng.integers(1, 60))
